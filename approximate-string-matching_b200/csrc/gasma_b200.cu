@@ -1,0 +1,478 @@
+// gasma_b200.cu -- the C ABI of libgasma_b200.so (include/gasma_b200.h) on top of the sm_100a kernels.
+// Plain CUDA runtime; no torch types, no CPU compute path: every result is produced by a kernel.
+#include "../../include/gasma_b200.h"
+
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <string>
+
+#include "kernels.cuh"
+#include "generate.cuh"
+
+using namespace gasma;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+};
+
+}  // namespace
+
+struct gasma_ctx {
+    gasma_params params;
+    KParams kp;
+    int W = 2;
+    int device = 0;
+    cudaStream_t stream = nullptr;      // stream all work goes to
+    cudaStream_t own_stream = nullptr;  // created by us
+    int64_t launches = 0;
+    std::string err;
+    // device scratch
+    DevBuf ops_stage, nops, tile_sums, tile_bases, misc;  // misc: [0] status u32, [1] total ops u32, [2..3] step counter u64
+    // device mirrors for the host-pointer entry points
+    DevBuf d_reads, d_refs, d_read_off, d_ref_off, d_cost, d_ops, d_op_off, d_p0, d_p1;
+    DevBuf gen_len;
+    uint32_t* h_misc = nullptr;  // pinned, 4 words
+};
+
+namespace {
+
+int fail(gasma_ctx* c, int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (c) c->err = buf; else g_create_error = buf;
+    return code;
+}
+
+#define CU(call)                                                                                          \
+    do {                                                                                                  \
+        cudaError_t _e = (call);                                                                          \
+        if (_e != cudaSuccess)                                                                            \
+            return fail(ctx, GASMA_E_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(_e), __FILE__, __LINE__); \
+    } while (0)
+
+int reserve(gasma_ctx* ctx, DevBuf& b, size_t bytes) {
+    if (bytes <= b.cap) return GASMA_OK;
+    if (b.p) { CU(cudaStreamSynchronize(ctx->stream)); CU(cudaFree(b.p)); b.p = nullptr; b.cap = 0; }
+    size_t want = bytes + bytes / 4 + 256;
+    CU(cudaMalloc(&b.p, want));
+    b.cap = want;
+    return GASMA_OK;
+}
+
+int validate_params(const gasma_params* p, std::string& why) {
+    if (!p) { why = "params is null"; return GASMA_E_ARG; }
+    if (p->max_length != 64 && p->max_length != 128 && p->max_length != 192 && p->max_length != 256) {
+        why = "max_length must be 64, 128, 192 or 256 (thread-per-pair kernels)";
+        return GASMA_E_UNSUPPORTED;
+    }
+    if (p->k < 0 || p->k > GASMA_MAX_K) { why = "k outside [0, MAX_K=50]"; return GASMA_E_BAND; }
+    if (p->alignment_type != GASMA_GLOBAL && p->alignment_type != GASMA_SEMI_GLOBAL) {
+        why = "alignment_type must be GLOBAL or SEMI_GLOBAL (LOCAL is unsupported in the reference too)";
+        return GASMA_E_UNSUPPORTED;
+    }
+    if (p->x < 0 || p->o < 0 || p->e < 0 || p->x > 1000 || p->o > 1000 || p->e > 1000) { why = "penalties must be in [0,1000]"; return GASMA_E_ARG; }
+    if (!(p->match_prob > 0) || !(p->mismatch_prob > 0) || !(p->indel_prob > 0)) { why = "probabilities must be > 0"; return GASMA_E_ARG; }
+    return GASMA_OK;
+}
+
+void derive(gasma_ctx* c) {
+    const gasma_params& p = c->params;
+    c->W = p.max_length / 64;
+    c->kp.k = p.k; c->kp.x = p.x; c->kp.o = p.o; c->kp.e = p.e;
+    c->kp.global = p.alignment_type == GASMA_GLOBAL ? 1 : 0;
+    // hurdle_matrix.h:536-538, host libm so the constants are the reference's bit for bit
+    c->kp.ms = log(p.match_prob / 0.25);
+    c->kp.mms = log(p.mismatch_prob / 0.25);
+    c->kp.ids = log(p.indel_prob / 2 / 0.25);
+}
+
+constexpr size_t kMaxSmem = 227 * 1024;
+
+template <int W>
+int tile_threads_for(int k) {
+    if (greedy_smem_bytes<W>(128, k) <= kMaxSmem) return 128;
+    if (greedy_smem_bytes<W>(32, k) <= kMaxSmem) return 32;
+    return 0;
+}
+
+template <int W, int T>
+int launch_greedy_t(gasma_ctx* ctx, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, const uint32_t* foff,
+                    int64_t n, int32_t* cost, uint16_t* stage, int stride, uint32_t* nops, uint32_t* tile_sums,
+                    uint32_t* status, unsigned long long* steps) {
+    const size_t smem = greedy_smem_bytes<W>(T, ctx->kp.k);
+    auto kern = greedy_kernel<W, T>;
+    CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const unsigned grid = (unsigned)((n + T - 1) / T);
+    kern<<<grid, T, smem, ctx->stream>>>(ctx->kp, reads, roff, refs, foff, (long long)n, cost, stage, stride, nops,
+                                         tile_sums, status, steps);
+    CU(cudaGetLastError());
+    ctx->launches++;
+    return GASMA_OK;
+}
+
+template <int W>
+int launch_greedy_w(gasma_ctx* ctx, int T, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs,
+                    const uint32_t* foff, int64_t n, int32_t* cost, uint16_t* stage, int stride, uint32_t* nops,
+                    uint32_t* tile_sums, uint32_t* status, unsigned long long* steps) {
+    if (T == 128) return launch_greedy_t<W, 128>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, tile_sums, status, steps);
+    return launch_greedy_t<W, 32>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, tile_sums, status, steps);
+}
+
+int greedy_tile_threads(const gasma_ctx* c) {
+    switch (c->W) {
+        case 1: return tile_threads_for<1>(c->kp.k);
+        case 2: return tile_threads_for<2>(c->kp.k);
+        case 3: return tile_threads_for<3>(c->kp.k);
+        default: return tile_threads_for<4>(c->kp.k);
+    }
+}
+
+int check_status(gasma_ctx* ctx, uint32_t st) {
+    if (st & (kStatusLength | kStatusTile)) return fail(ctx, GASMA_E_LENGTH, "a string is longer than max_length=%d", ctx->params.max_length);
+    if (st & kStatusBand) return fail(ctx, GASMA_E_BAND, "|ref_len - read_len| > MAX_K=%d (out of bounds in the reference)", GASMA_MAX_K);
+    if (st & kStatusSteps) return fail(ctx, GASMA_E_INTERNAL, "greedy traversal hit the step limit");
+    return GASMA_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+void gasma_default_params(gasma_params* p) {
+    if (!p) return;
+    p->alignment_type = GASMA_GLOBAL;
+    p->x = p->o = p->e = 1;       // benchmark.cpp:22, hurdle_matrix.h:554-556
+    p->k = 3;
+    p->max_length = 128;          // utils.h:23-25
+    p->match_prob = 0.80;         // hurdle_matrix.h:557-559
+    p->mismatch_prob = 0.20 / 3;
+    p->indel_prob = 0.40 / 3;
+}
+
+int gasma_create(const gasma_params* params, int device, gasma_ctx** out) {
+    gasma_ctx* ctx = nullptr;  // so CU() reports into g_create_error
+    if (!out) return fail(nullptr, GASMA_E_ARG, "out is null");
+    *out = nullptr;
+    std::string why;
+    int rc = validate_params(params, why);
+    if (rc) return fail(nullptr, rc, "%s", why.c_str());
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(nullptr, GASMA_E_CUDA, "no CUDA device (%s); libgasma_b200 has no CPU path", cudaGetErrorString(e));
+    if (device < 0 || device >= ndev) return fail(nullptr, GASMA_E_ARG, "device %d out of range (%d devices)", device, ndev);
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10)
+        return fail(nullptr, GASMA_E_CUDA, "device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
+    CU(cudaSetDevice(device));
+    gasma_ctx* c = new gasma_ctx();
+    c->params = *params;
+    c->device = device;
+    derive(c);
+    if (greedy_tile_threads(c) == 0) {
+        delete c;
+        return fail(nullptr, GASMA_E_UNSUPPORTED, "k=%d with max_length=%d does not fit the thread-per-pair kernel", params->k, params->max_length);
+    }
+    cudaError_t e2 = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
+    if (e2 != cudaSuccess) { delete c; return fail(nullptr, GASMA_E_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(e2)); }
+    c->stream = c->own_stream;
+    if (cudaMalloc(&c->misc.p, 64) != cudaSuccess || cudaMemset(c->misc.p, 0, 64) != cudaSuccess ||
+        cudaMallocHost((void**)&c->h_misc, 64) != cudaSuccess) {
+        gasma_destroy(c);
+        return fail(nullptr, GASMA_E_CUDA, "allocating context scratch failed");
+    }
+    c->misc.cap = 64;
+    *out = c;
+    return GASMA_OK;
+}
+
+void gasma_destroy(gasma_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    DevBuf* bufs[] = {&c->ops_stage, &c->nops, &c->tile_sums, &c->tile_bases, &c->misc, &c->d_reads, &c->d_refs,
+                      &c->d_read_off, &c->d_ref_off, &c->d_cost, &c->d_ops, &c->d_op_off, &c->d_p0, &c->d_p1, &c->gen_len};
+    for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
+    if (c->h_misc) cudaFreeHost(c->h_misc);
+    if (c->own_stream) cudaStreamDestroy(c->own_stream);
+    delete c;
+}
+
+const char* gasma_last_error(const gasma_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+int gasma_set_band(gasma_ctx* ctx, int k) {
+    if (!ctx) return GASMA_E_ARG;
+    if (k < 0 || k > GASMA_MAX_K) return fail(ctx, GASMA_E_BAND, "k=%d outside [0, %d]", k, GASMA_MAX_K);
+    int old = ctx->params.k;
+    ctx->params.k = k;
+    derive(ctx);
+    if (greedy_tile_threads(ctx) == 0) {
+        ctx->params.k = old;
+        derive(ctx);
+        return fail(ctx, GASMA_E_UNSUPPORTED, "k=%d with max_length=%d does not fit the thread-per-pair kernel", k, ctx->params.max_length);
+    }
+    return GASMA_OK;
+}
+
+int gasma_set_stream(gasma_ctx* ctx, void* cuda_stream) {
+    if (!ctx) return GASMA_E_ARG;
+    CU(cudaStreamSynchronize(ctx->stream));
+    ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
+    return GASMA_OK;
+}
+
+int gasma_synchronize(gasma_ctx* ctx) {
+    if (!ctx) return GASMA_E_ARG;
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaMemcpyAsync(ctx->h_misc, ctx->misc.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaMemsetAsync(ctx->misc.p, 0, 4, ctx->stream));  // status is consumed by this call
+    CU(cudaStreamSynchronize(ctx->stream));
+    return check_status(ctx, ctx->h_misc[0]);
+}
+
+int64_t gasma_launch_count(const gasma_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int gasma_render_cigar(const gasma_cigar_op* ops, int n_ops, char* out, int cap) {
+    static const char letters[] = "MID=X???";
+    int pos = 0;
+    for (int i = 0; i < n_ops; ++i) {
+        char tmp[16];
+        int c = snprintf(tmp, sizeof tmp, "%d%c", (int)GASMA_OP_LEN(ops[i]), letters[GASMA_OP_CODE(ops[i])]);
+        for (int j = 0; j < c; ++j)
+            if (out && pos + j < cap - 1) out[pos + j] = tmp[j];
+        pos += c;
+    }
+    if (out && cap > 0) out[pos < cap - 1 ? pos : cap - 1] = '\0';
+    return pos;
+}
+
+}  // extern "C"
+
+// =================================================================================================
+// K1 / K2+K3 entry points
+// =================================================================================================
+namespace {
+
+bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+template <int W>
+int launch_pack_w(gasma_ctx* ctx, const uint8_t* seqs, const uint32_t* off, int64_t n, uint64_t* p0, uint64_t* p1) {
+    const unsigned grid = (unsigned)((n + kTile - 1) / kTile);
+    pack2bit_kernel<W, kTile><<<grid, kTile, 0, ctx->stream>>>(seqs, off, (long long)n, p0, p1, (uint32_t*)ctx->misc.p);
+    CU(cudaGetLastError());
+    ctx->launches++;
+    return GASMA_OK;
+}
+
+int greedy_dev_impl(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_read_off, const char* d_refs,
+                    const uint32_t* d_ref_off, int64_t n, int32_t* d_cost, gasma_cigar_op* d_ops, int64_t ops_cap,
+                    uint32_t* d_op_off) {
+    if (!ctx) return GASMA_E_ARG;
+    if (n < 0 || n > (int64_t)1 << 31) return fail(ctx, GASMA_E_ARG, "n_pairs out of range");
+    if (!d_read_off || !d_ref_off || !d_cost) return fail(ctx, GASMA_E_ARG, "null offsets/cost pointer");
+    if ((d_ops != nullptr) != (d_op_off != nullptr)) return fail(ctx, GASMA_E_ARG, "ops and op_off must be given together");
+    if (!aligned16(d_reads) || !aligned16(d_refs)) return fail(ctx, GASMA_E_ARG, "sequence buffers must be 16-byte aligned");
+    CU(cudaSetDevice(ctx->device));
+    if (n == 0) {
+        if (d_op_off) CU(cudaMemsetAsync(d_op_off, 0, 4, ctx->stream));
+        return GASMA_OK;
+    }
+    const int T = greedy_tile_threads(ctx);
+    const int64_t ntiles = (n + T - 1) / T;
+    const int stride = 2 * ctx->params.max_length + 8;
+    uint32_t* misc = (uint32_t*)ctx->misc.p;
+    const bool want_ops = d_ops != nullptr;
+    int rc;
+    if (want_ops) {
+        if ((rc = reserve(ctx, ctx->ops_stage, (size_t)n * stride * sizeof(uint16_t)))) return rc;
+        if ((rc = reserve(ctx, ctx->nops, (size_t)n * 4))) return rc;
+        if ((rc = reserve(ctx, ctx->tile_sums, (size_t)ntiles * 4))) return rc;
+        if ((rc = reserve(ctx, ctx->tile_bases, (size_t)ntiles * 4))) return rc;
+    }
+    uint16_t* stage = want_ops ? (uint16_t*)ctx->ops_stage.p : nullptr;
+    uint32_t* nops = want_ops ? (uint32_t*)ctx->nops.p : nullptr;
+    uint32_t* tsum = want_ops ? (uint32_t*)ctx->tile_sums.p : nullptr;
+    const uint8_t* r = (const uint8_t*)d_reads;
+    const uint8_t* f = (const uint8_t*)d_refs;
+    unsigned long long* steps = (unsigned long long*)(misc + 2);
+    switch (ctx->W) {
+        case 1: rc = launch_greedy_w<1>(ctx, T, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, tsum, misc, steps); break;
+        case 2: rc = launch_greedy_w<2>(ctx, T, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, tsum, misc, steps); break;
+        case 3: rc = launch_greedy_w<3>(ctx, T, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, tsum, misc, steps); break;
+        default: rc = launch_greedy_w<4>(ctx, T, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, tsum, misc, steps); break;
+    }
+    if (rc) return rc;
+    if (want_ops) {
+        scan_tiles_kernel<<<1, 1024, 0, ctx->stream>>>(tsum, (uint32_t*)ctx->tile_bases.p, (int)ntiles, misc + 1);
+        CU(cudaGetLastError());
+        ctx->launches++;
+        if (T == 128)
+            compact_ops_kernel<128><<<(unsigned)ntiles, 128, 0, ctx->stream>>>(stage, stride, nops, (uint32_t*)ctx->tile_bases.p,
+                                                                             (long long)n, d_ops, (long long)ops_cap, d_op_off);
+        else
+            compact_ops_kernel<32><<<(unsigned)ntiles, 32, 0, ctx->stream>>>(stage, stride, nops, (uint32_t*)ctx->tile_bases.p,
+                                                                           (long long)n, d_ops, (long long)ops_cap, d_op_off);
+        CU(cudaGetLastError());
+        ctx->launches++;
+    }
+    return GASMA_OK;
+}
+
+// host-side validation of a CSR offset array
+int check_offsets(gasma_ctx* ctx, const uint32_t* off, int64_t n, const char* what) {
+    for (int64_t i = 0; i < n; ++i)
+        if (off[i + 1] < off[i]) return fail(ctx, GASMA_E_ARG, "%s offsets are not non-decreasing at %lld", what, (long long)i);
+    return GASMA_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int gasma_pack2bit_batch_dev(gasma_ctx* ctx, const char* d_seqs, const uint32_t* d_off, int64_t n,
+                             uint64_t* d_plane0, uint64_t* d_plane1) {
+    if (!ctx) return GASMA_E_ARG;
+    if (n < 0 || !d_off || !d_plane0 || !d_plane1) return fail(ctx, GASMA_E_ARG, "bad argument");
+    if (!aligned16(d_seqs)) return fail(ctx, GASMA_E_ARG, "sequence buffer must be 16-byte aligned");
+    CU(cudaSetDevice(ctx->device));
+    if (n == 0) return GASMA_OK;
+    const uint8_t* s = (const uint8_t*)d_seqs;
+    switch (ctx->W) {
+        case 1: return launch_pack_w<1>(ctx, s, d_off, n, d_plane0, d_plane1);
+        case 2: return launch_pack_w<2>(ctx, s, d_off, n, d_plane0, d_plane1);
+        case 3: return launch_pack_w<3>(ctx, s, d_off, n, d_plane0, d_plane1);
+        default: return launch_pack_w<4>(ctx, s, d_off, n, d_plane0, d_plane1);
+    }
+}
+
+int gasma_pack2bit_batch(gasma_ctx* ctx, const char* seqs, const uint32_t* off, int64_t n, uint64_t* plane0,
+                         uint64_t* plane1) {
+    if (!ctx) return GASMA_E_ARG;
+    if (n < 0 || !off || !plane0 || !plane1) return fail(ctx, GASMA_E_ARG, "bad argument");
+    if (n == 0) return GASMA_OK;
+    int rc = check_offsets(ctx, off, n, "seq");
+    if (rc) return rc;
+    CU(cudaSetDevice(ctx->device));
+    const size_t bytes = off[n], pb = (size_t)n * ctx->W * 8;
+    if ((rc = reserve(ctx, ctx->d_reads, bytes + 16))) return rc;
+    if ((rc = reserve(ctx, ctx->d_read_off, (size_t)(n + 1) * 4))) return rc;
+    if ((rc = reserve(ctx, ctx->d_p0, pb))) return rc;
+    if ((rc = reserve(ctx, ctx->d_p1, pb))) return rc;
+    if (bytes) CU(cudaMemcpyAsync(ctx->d_reads.p, seqs, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemcpyAsync(ctx->d_read_off.p, off, (size_t)(n + 1) * 4, cudaMemcpyHostToDevice, ctx->stream));
+    rc = gasma_pack2bit_batch_dev(ctx, (const char*)ctx->d_reads.p, (const uint32_t*)ctx->d_read_off.p, n,
+                                  (uint64_t*)ctx->d_p0.p, (uint64_t*)ctx->d_p1.p);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(plane0, ctx->d_p0.p, pb, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaMemcpyAsync(plane1, ctx->d_p1.p, pb, cudaMemcpyDeviceToHost, ctx->stream));
+    return gasma_synchronize(ctx);
+}
+
+int gasma_greedy_batch_dev(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_read_off, const char* d_refs,
+                           const uint32_t* d_ref_off, int64_t n_pairs, int32_t* d_cost, gasma_cigar_op* d_ops,
+                           int64_t ops_cap, uint32_t* d_op_off) {
+    return greedy_dev_impl(ctx, d_reads, d_read_off, d_refs, d_ref_off, n_pairs, d_cost, d_ops, ops_cap, d_op_off);
+}
+
+int gasma_greedy_batch(gasma_ctx* ctx, const char* reads, const uint32_t* read_off, const char* refs,
+                       const uint32_t* ref_off, int64_t n, int32_t* cost, gasma_cigar_op* ops, int64_t ops_cap,
+                       uint32_t* op_off) {
+    if (!ctx) return GASMA_E_ARG;
+    if (n < 0 || !read_off || !ref_off || !cost) return fail(ctx, GASMA_E_ARG, "bad argument");
+    if ((ops != nullptr) != (op_off != nullptr)) return fail(ctx, GASMA_E_ARG, "ops and op_off must be given together");
+    if (n == 0) { if (op_off) op_off[0] = 0; return GASMA_OK; }
+    int rc;
+    if ((rc = check_offsets(ctx, read_off, n, "read"))) return rc;
+    if ((rc = check_offsets(ctx, ref_off, n, "ref"))) return rc;
+    CU(cudaSetDevice(ctx->device));
+    const size_t rb = read_off[n], fb = ref_off[n], ob = (size_t)(n + 1) * 4;
+    if ((rc = reserve(ctx, ctx->d_reads, rb + 16))) return rc;
+    if ((rc = reserve(ctx, ctx->d_refs, fb + 16))) return rc;
+    if ((rc = reserve(ctx, ctx->d_read_off, ob))) return rc;
+    if ((rc = reserve(ctx, ctx->d_ref_off, ob))) return rc;
+    if ((rc = reserve(ctx, ctx->d_cost, (size_t)n * 4))) return rc;
+    if (ops) {
+        if ((rc = reserve(ctx, ctx->d_op_off, ob))) return rc;
+        if ((rc = reserve(ctx, ctx->d_ops, (size_t)(ops_cap > 0 ? ops_cap : 1) * 2))) return rc;
+    }
+    if (rb) CU(cudaMemcpyAsync(ctx->d_reads.p, reads, rb, cudaMemcpyHostToDevice, ctx->stream));
+    if (fb) CU(cudaMemcpyAsync(ctx->d_refs.p, refs, fb, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemcpyAsync(ctx->d_read_off.p, read_off, ob, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemcpyAsync(ctx->d_ref_off.p, ref_off, ob, cudaMemcpyHostToDevice, ctx->stream));
+    rc = greedy_dev_impl(ctx, (const char*)ctx->d_reads.p, (const uint32_t*)ctx->d_read_off.p, (const char*)ctx->d_refs.p,
+                         (const uint32_t*)ctx->d_ref_off.p, n, (int32_t*)ctx->d_cost.p,
+                         ops ? (gasma_cigar_op*)ctx->d_ops.p : nullptr, ops_cap, ops ? (uint32_t*)ctx->d_op_off.p : nullptr);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(cost, ctx->d_cost.p, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    if (ops) CU(cudaMemcpyAsync(op_off, ctx->d_op_off.p, ob, cudaMemcpyDeviceToHost, ctx->stream));
+    if ((rc = gasma_synchronize(ctx))) return rc;
+    if (ops) {
+        const int64_t total = op_off[n];
+        if (total > ops_cap) return fail(ctx, GASMA_E_CAPACITY, "ops buffer holds %lld ops, %lld needed", (long long)ops_cap, (long long)total);
+        if (total) CU(cudaMemcpyAsync(ops, ctx->d_ops.p, (size_t)total * 2, cudaMemcpyDeviceToHost, ctx->stream));
+        CU(cudaStreamSynchronize(ctx->stream));
+    }
+    return GASMA_OK;
+}
+
+}  // extern "C"
+
+// =================================================================================================
+// synthetic inputs
+// =================================================================================================
+extern "C" {
+
+int64_t gasma_generate_ref_capacity(const gasma_gen_config* cfg, int64_t n_pairs) {
+    if (!cfg || n_pairs < 0) return -1;
+    GenCfg c{cfg->seed, cfg->length, cfg->mode, cfg->num_errors, cfg->thr_mismatch, cfg->thr_sub, cfg->thr_ins, cfg->thr_del};
+    return (int64_t)gen_ref_capacity(c) * n_pairs + 16;
+}
+
+int gasma_generate_dev(gasma_ctx* ctx, const gasma_gen_config* cfg, uint64_t first_pair, int64_t n,
+                       char* d_reads, uint32_t* d_read_off, char* d_refs, uint32_t* d_ref_off) {
+    if (!ctx) return GASMA_E_ARG;
+    if (!cfg || n < 0 || !d_reads || !d_read_off || !d_refs || !d_ref_off) return fail(ctx, GASMA_E_ARG, "bad argument");
+    if (cfg->length < 0 || cfg->length > 1024 || cfg->num_errors < 0 || cfg->num_errors > 1024 || cfg->mode < 0 || cfg->mode > 2)
+        return fail(ctx, GASMA_E_ARG, "generator: length/num_errors must be in [0,1024], mode in {0,1,2}");
+    if ((int64_t)gasma_generate_ref_capacity(cfg, n) >= ((int64_t)1 << 32))
+        return fail(ctx, GASMA_E_ARG, "generator: batch exceeds 4 GiB of bases");
+    CU(cudaSetDevice(ctx->device));
+    if (n == 0) { CU(cudaMemsetAsync(d_read_off, 0, 4, ctx->stream)); CU(cudaMemsetAsync(d_ref_off, 0, 4, ctx->stream)); return GASMA_OK; }
+    GenCfg c{cfg->seed, cfg->length, cfg->mode, cfg->num_errors, cfg->thr_mismatch, cfg->thr_sub, cfg->thr_ins, cfg->thr_del};
+    const int T = 128;
+    const int64_t ntiles = (n + T - 1) / T;
+    int rc;
+    if ((rc = reserve(ctx, ctx->gen_len, (size_t)n * 4))) return rc;
+    if ((rc = reserve(ctx, ctx->tile_sums, (size_t)ntiles * 4))) return rc;
+    if ((rc = reserve(ctx, ctx->tile_bases, (size_t)ntiles * 4))) return rc;
+    gen_lengths_kernel<T><<<(unsigned)ntiles, T, 0, ctx->stream>>>(c, first_pair, (long long)n, (uint32_t*)ctx->gen_len.p,
+                                                                    (uint32_t*)ctx->tile_sums.p, d_read_off);
+    CU(cudaGetLastError());
+    scan_tiles_kernel<<<1, 1024, 0, ctx->stream>>>((uint32_t*)ctx->tile_sums.p, (uint32_t*)ctx->tile_bases.p, (int)ntiles, nullptr);
+    CU(cudaGetLastError());
+    gen_write_kernel<T><<<(unsigned)ntiles, T, 0, ctx->stream>>>(c, first_pair, (long long)n, (uint32_t*)ctx->gen_len.p,
+                                                                  (uint32_t*)ctx->tile_bases.p, d_reads, d_refs, d_ref_off);
+    CU(cudaGetLastError());
+    ctx->launches += 3;
+    return GASMA_OK;
+}
+
+}  // extern "C"
+
+// =================================================================================================
+// K4 / K5 entry points (nw.cuh / metrics.cuh)
+// =================================================================================================
+#include "nw_entry.inl"

@@ -1,0 +1,167 @@
+/* gasma_b200.h -- C ABI of libgasma_b200.so: the B200 (sm_100a) implementation of GASMA's
+ * greedy bit-parallel alignment hot path.
+ *
+ * This is the drop-in boundary.  Every entry point is plain C: pointers,
+ * sizes, one opaque context.  Each one names the reference interface it replaces; file:line
+ * citations are relative to the reference tree (GZHoffie/approximate-string-matching).
+ * The header-only C++ adapters in approximate-string-matching_b200/host/ put the reference's own
+ * class names (hurdle_matrix, benchmark) back on top of these calls; INTEGRATION.md shows the
+ * binding a maintainer of the reference would add.
+ *
+ * Conventions
+ *   * Batches are "CSR strings": one concatenated ASCII buffer + (n+1) uint32 offsets; string i is
+ *     bytes [off[i], off[i+1]).  A batch therefore holds < 4 GiB of bases per side.
+ *   * Results are bit-exact to the reference's CPU output in canonical mode (staging tails = 'A',
+ *     no FMA contraction).  Strings longer than max_length are rejected
+ *     (GASMA_E_LENGTH) -- the C++ adapter applies the reference's silent truncation
+ *     (hurdle_matrix.h:626-627) before calling.
+ *   * Every function returns 0 (GASMA_OK) or a negative gasma_status; gasma_last_error() gives text.
+ *   * "_dev" variants take DEVICE pointers (inputs resident in HBM, results left in HBM) and only
+ *     enqueue work on the context's stream; the host variants take HOST pointers, copy in/out and
+ *     synchronise before returning.
+ *   * A context is single-caller (like one hurdle_matrix object) and is bound to one CUDA device.
+ *     There is no CPU fallback: without a usable GPU gasma_create fails with GASMA_E_CUDA.
+ */
+#ifndef GASMA_B200_H
+#define GASMA_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GASMA_MAX_K 50          /* hurdle_matrix.h:8   MAX_K */
+#define GASMA_WORD_BITS 64
+#define GASMA_MAX_WORDS 4       /* thread-per-pair kernels: max_length <= 256 (reference: 128, utils.h:23-25) */
+
+typedef enum {
+    GASMA_OK = 0,
+    GASMA_E_ARG = -1,        /* null pointer, bad size, unaligned device buffer */
+    GASMA_E_LENGTH = -2,     /* a string is longer than max_length */
+    GASMA_E_BAND = -3,       /* k > GASMA_MAX_K, or |ref_len - read_len| > GASMA_MAX_K (out of bounds in the reference) */
+    GASMA_E_CAPACITY = -4,   /* caller's ops buffer too small (op_off[n] tells the size needed) */
+    GASMA_E_CUDA = -5,       /* CUDA runtime / launch failure, or no sm_100 device */
+    GASMA_E_UNSUPPORTED = -6,/* parameter combination outside what the kernels cover */
+    GASMA_E_INTERNAL = -7    /* step limit hit (non-terminating traversal) */
+} gasma_status;
+
+/* alignment_type_t, utils.h:554 */
+typedef enum { GASMA_GLOBAL = 0, GASMA_SEMI_GLOBAL = 1 } gasma_alignment_type;
+
+/* Constructor arguments of hurdle_matrix<T> (hurdle_matrix.h:552-562) + the per-reset band k (:625)
+ * + the bit-vector width.  max_length = 64*W; 128 reproduces hurdle_matrix<int_128bit>. */
+typedef struct {
+    int32_t alignment_type;   /* gasma_alignment_type */
+    int32_t x, o, e;          /* mismatch, gap open, gap extend (hurdle_matrix.h:478-480) */
+    int32_t k;                /* band: lanes -k..k (hurdle_matrix.h:643-644) */
+    int32_t max_length;       /* 128, 192 or 256 */
+    double match_prob, mismatch_prob, indel_prob; /* hurdle_matrix.h:557-559 */
+} gasma_params;
+
+/* fills the reference's defaults: GLOBAL, x=o=e=1, k=3, max_length=128, probs 0.80, 0.20/3, 0.40/3 */
+void gasma_default_params(gasma_params* p);
+
+/* CIGAR op = (length << 3) | code.  Ops are never merged (hurdle_matrix.h:238-251 appends per step). */
+typedef uint16_t gasma_cigar_op;
+enum { GASMA_OP_M = 0, GASMA_OP_I = 1, GASMA_OP_D = 2, GASMA_OP_EQ = 3, GASMA_OP_X = 4 };
+#define GASMA_OP_LEN(op) ((op) >> 3)
+#define GASMA_OP_CODE(op) ((op) & 7)
+
+typedef struct gasma_ctx gasma_ctx;
+
+/* -- lifetime -------------------------------------------------------------------------------- */
+/* Replaces `new hurdle_matrix<int_128bit>(GLOBAL,x,o,e)` (benchmark_utils.h:287). */
+int gasma_create(const gasma_params* params, int device, gasma_ctx** out);
+void gasma_destroy(gasma_ctx* ctx);
+/* Text of the last failure on this context (or of the last failed gasma_create when ctx==NULL). */
+const char* gasma_last_error(const gasma_ctx* ctx);
+/* Change the band between batches: the `error` argument of reset() (hurdle_matrix.h:625). */
+int gasma_set_band(gasma_ctx* ctx, int k);
+/* Use the caller's cudaStream_t (e.g. torch's current stream) for all _dev work. NULL = own stream. */
+int gasma_set_stream(gasma_ctx* ctx, void* cuda_stream);
+/* Blocks until everything enqueued on the context's stream has finished; surfaces async errors
+ * and the device-side status word (length / band / step-limit violations seen by _dev calls). */
+int gasma_synchronize(gasma_ctx* ctx);
+/* Number of kernels this context has launched so far (bench.py's gpu_launches). */
+int64_t gasma_launch_count(const gasma_ctx* ctx);
+
+/* -- K1: 2-bit packing ------------------------------------------------------------------------- */
+/* Replaces sse3_convert2bit1 (bit_convert.cpp:248, bit_convert.h:21) applied to a whole batch:
+ * plane0[i*W + w] bit b = (char 64w+b of string i is C or T), plane1 likewise for G or T, anything
+ * else (and the tail beyond the string) 0.  W = max_length/64. */
+int gasma_pack2bit_batch(gasma_ctx* ctx, const char* seqs, const uint32_t* off, int64_t n,
+                         uint64_t* plane0, uint64_t* plane1);
+int gasma_pack2bit_batch_dev(gasma_ctx* ctx, const char* d_seqs, const uint32_t* d_off, int64_t n,
+                             uint64_t* d_plane0, uint64_t* d_plane1);
+
+/* -- K2+K3: greedy alignment ------------------------------------------------------------------- */
+/* Replaces the loop body of benchmark::_run_greedy (benchmark_utils.h:185-201):
+ * reset(read,m,ref,n,k); run(); get_cost(); get_CIGAR()  (hurdle_matrix.h:625,568,677,613) for n pairs.
+ *   cost[i]            = get_cost()
+ *   ops[op_off[i] .. op_off[i+1])  = get_CIGAR() as encoded ops (render with gasma_render_cigar)
+ * ops may be NULL (costs only; op_off is then not written either).  ops_cap is the capacity of ops in
+ * elements; if it is too small the call fails with GASMA_E_CAPACITY after writing cost[] and op_off[]. */
+int gasma_greedy_batch(gasma_ctx* ctx,
+                       const char* reads, const uint32_t* read_off,
+                       const char* refs, const uint32_t* ref_off, int64_t n_pairs,
+                       int32_t* cost, gasma_cigar_op* ops, int64_t ops_cap, uint32_t* op_off);
+int gasma_greedy_batch_dev(gasma_ctx* ctx,
+                           const char* d_reads, const uint32_t* d_read_off,
+                           const char* d_refs, const uint32_t* d_ref_off, int64_t n_pairs,
+                           int32_t* d_cost, gasma_cigar_op* d_ops, int64_t ops_cap, uint32_t* d_op_off);
+
+/* -- K4: NW verifier ---------------------------------------------------------------------------- */
+/* Replaces benchmark::_run_nw / _run_nw_sse (benchmark_utils.h:104-150; parasail_nw_trace* with
+ * parasail_matrix_create("ACGT",0,-x), :288): optimal global affine-gap penalty (>= 0), gap of length g
+ * costs o+(g-1)e.  d_bound may hold a per-pair upper bound on the optimum (e.g. the greedy cost) used
+ * to size the band (exact); NULL = full matrix.  ops (optional) receive the traceback
+ * as =,X,I,D runs. */
+int gasma_nw_batch(gasma_ctx* ctx,
+                   const char* reads, const uint32_t* read_off,
+                   const char* refs, const uint32_t* ref_off, int64_t n_pairs,
+                   const int32_t* bound, int32_t* penalty,
+                   gasma_cigar_op* ops, int64_t ops_cap, uint32_t* op_off);
+int gasma_nw_batch_dev(gasma_ctx* ctx,
+                       const char* d_reads, const uint32_t* d_read_off,
+                       const char* d_refs, const uint32_t* d_ref_off, int64_t n_pairs,
+                       const int32_t* d_bound, int32_t* d_penalty,
+                       gasma_cigar_op* d_ops, int64_t ops_cap, uint32_t* d_op_off);
+
+/* -- K5: accuracy / coverage counters ----------------------------------------------------------- */
+/* Replaces the counter block of benchmark::_run_benchmark (benchmark_utils.h:238,249-258) and
+ * _check_coverage (:214-225; benchmark_coverage.h:26-91):
+ *   counters[0] += n, [1] += #(nw == correct), [2] += #(greedy == correct), [3] += #(greedy LCM(>=1)
+ *   covers NW LCM(>=3)).  answers may be NULL (correct = nw penalty, benchmark_utils.h:245-248).
+ * Counters ACCUMULATE into d_counters (4 x uint64 in device memory) so that a multi-batch run ends
+ * with one sum per GPU, which the caller all-reduces (NCCL) across GPUs. */
+int gasma_metrics_dev(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_read_off, int64_t n_pairs,
+                      const int32_t* d_greedy_cost, const gasma_cigar_op* d_greedy_ops, const uint32_t* d_greedy_off,
+                      const int32_t* d_nw_penalty, const gasma_cigar_op* d_nw_ops, const uint32_t* d_nw_off,
+                      const int32_t* d_answers, uint64_t* d_counters);
+
+/* -- synthetic inputs ---------------------------------------------------------------------------- */
+/* Restates Dataset (benchmark_dataset.h:100-186) with a counter RNG keyed by (seed, pair index) so
+ * every shard regenerates pair i identically.  mode 0: exactly num_errors edits; 1: uniform in
+ * [0,num_errors); 2: per-base profile (thr_* are cumulative thresholds on a 32-bit draw). */
+typedef struct {
+    uint64_t seed;
+    int32_t length, mode, num_errors, reserved;
+    uint64_t thr_mismatch, thr_sub, thr_ins, thr_del;
+} gasma_gen_config;
+/* bytes of ref buffer that n pairs can need at most */
+int64_t gasma_generate_ref_capacity(const gasma_gen_config* cfg, int64_t n_pairs);
+/* Writes reads (n*length bytes), read_off, refs, ref_off (n+1 each) for pairs first..first+n. */
+int gasma_generate_dev(gasma_ctx* ctx, const gasma_gen_config* cfg, uint64_t first_pair, int64_t n_pairs,
+                       char* d_reads, uint32_t* d_read_off, char* d_refs, uint32_t* d_ref_off);
+
+/* -- host helpers -------------------------------------------------------------------------------- */
+/* get_CIGAR() text from encoded ops: std::to_string(len) + letter per op (hurdle_matrix.h:241-249).
+ * Returns the text length (without NUL); writes at most cap bytes including the NUL. */
+int gasma_render_cigar(const gasma_cigar_op* ops, int n_ops, char* out, int cap);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GASMA_B200_H */

@@ -1,0 +1,145 @@
+// tests/host_sim.cpp -- TEST INFRASTRUCTURE.
+//
+// Compiles the per-pair __host__ __device__ code of the CUDA kernels (csrc/pack.cuh, csrc/greedy.cuh,
+// csrc/nw.cuh ...) with g++ and drives it exactly the way the kernels do (tile -> 16-byte chunks ->
+// shared bit stream -> per-pair window -> traversal), so that the device logic can be checked against
+// the oracle on the CPU-only build container.  It is NOT a fallback: nothing in the product links it,
+// and the shipped library fails loudly without a GPU.  Built by tests/conftest.py into tests/_build/.
+#include <cstdint>
+#include <cstring>
+#include <vector>
+
+#include "../approximate-string-matching_b200/csrc/common.cuh"
+#include "../approximate-string-matching_b200/csrc/pack.cuh"
+#include "../approximate-string-matching_b200/csrc/greedy.cuh"
+
+#include <cmath>
+
+using namespace gasma;
+
+namespace {
+
+template <int W>
+constexpr int chunks(int tile) { return tile * 4 * W + 2; }
+template <int W>
+constexpr int elems(int tile) { return ((chunks<W>(tile) + 2 * (2 * W + 2) + 7) / 8) * 8; }
+
+// host twin of stage_tile (kernels.cuh): same chunking, same partial-tail rule
+bool stage(const uint8_t* buf, uint32_t base16, uint32_t end, uint32_t total, uint16_t* s0, uint16_t* s1, int cap) {
+    int n = (int)((end - base16 + 15u) >> 4);
+    bool ok = n <= cap;
+    if (!ok) n = cap;
+    for (int c = 0; c < n; ++c) {
+        uint32_t a = base16 + 16u * (uint32_t)c, w[4] = {0, 0, 0, 0};
+        for (uint32_t i = 0; i < 16u && a + i < total; ++i) w[i >> 2] |= (uint32_t)buf[a + i] << (8u * (i & 3u));
+        uint32_t p0, p1;
+        pack_chunk(w[0], w[1], w[2], w[3], p0, p1);
+        s0[c] = (uint16_t)p0;
+        s1[c] = (uint16_t)p1;
+    }
+    return ok;
+}
+
+template <int W>
+int sim_greedy(const KParams& P, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, const uint32_t* foff,
+               int64_t n, int T, int32_t* cost, uint16_t* ops_stage, int stride, uint32_t* nops, uint32_t* status_out,
+               int64_t* steps_out) {
+    constexpr int BITS = 64 * W;
+    const int nl = 2 * P.k + 1;
+    std::vector<uint64_t> lanes((size_t)nl * 2 * W), state(nl);
+    std::vector<uint16_t> r0(elems<W>(T)), r1(elems<W>(T)), f0(elems<W>(T)), f1(elems<W>(T));
+    uint32_t status = 0;
+    int64_t steps_total = 0;
+    for (int64_t p0 = 0; p0 < n; p0 += T) {
+        const int np = (int)std::min<int64_t>(T, n - p0);
+        std::fill(r0.begin(), r0.end(), 0); std::fill(r1.begin(), r1.end(), 0);
+        std::fill(f0.begin(), f0.end(), 0); std::fill(f1.begin(), f1.end(), 0);
+        const uint32_t rbase = roff[p0] & ~15u, fbase = foff[p0] & ~15u;
+        bool ok = stage(reads, rbase, roff[p0 + np], roff[n], r0.data(), r1.data(), chunks<W>(T));
+        ok &= stage(refs, fbase, foff[p0 + np], foff[n], f0.data(), f1.data(), chunks<W>(T));
+        for (int t = 0; t < np; ++t) {
+            const int m = (int)(roff[p0 + t + 1] - roff[p0 + t]), nn = (int)(foff[p0 + t + 1] - foff[p0 + t]);
+            uint32_t st = 0;
+            if (!ok) st |= kStatusTile;
+            if (m > BITS || nn > BITS) st |= kStatusLength;
+            else if (iabs(nn - m) > kMaxK) st |= kStatusBand;
+            int c = INT32_MIN, steps = 0;
+            uint32_t my = 0;
+            if (!st) {
+                uint64_t A0[W], A1[W], B0[W], B1[W];
+                const int rbit = (int)(roff[p0 + t] - rbase), fbit = (int)(foff[p0 + t] - fbase);
+                extract_plane<W>(reinterpret_cast<const uint32_t*>(r0.data()), rbit, m, A0);
+                extract_plane<W>(reinterpret_cast<const uint32_t*>(r1.data()), rbit, m, A1);
+                extract_plane<W>(reinterpret_cast<const uint32_t*>(f0.data()), fbit, nn, B0);
+                extract_plane<W>(reinterpret_cast<const uint32_t*>(f1.data()), fbit, nn, B1);
+                LaneStore S{lanes.data(), state.data(), 1};
+                OpSink sink{ops_stage ? ops_stage + (size_t)(p0 + t) * stride : nullptr, stride, 0};
+                st = greedy_pair<W>(P, A0, A1, B0, B1, m, nn, S, sink, c, steps);
+                my = (uint32_t)sink.n;
+            }
+            cost[p0 + t] = c;
+            if (nops) nops[p0 + t] = my;
+            status |= st;
+            steps_total += steps;
+        }
+    }
+    if (status_out) *status_out = status;
+    if (steps_out) *steps_out = steps_total;
+    return 0;
+}
+
+template <int W>
+int sim_pack(const uint8_t* seqs, const uint32_t* off, int64_t n, int T, uint64_t* p0o, uint64_t* p1o, uint32_t* status_out) {
+    constexpr int BITS = 64 * W;
+    std::vector<uint16_t> s0(elems<W>(T)), s1(elems<W>(T));
+    uint32_t status = 0;
+    for (int64_t p0 = 0; p0 < n; p0 += T) {
+        const int np = (int)std::min<int64_t>(T, n - p0);
+        std::fill(s0.begin(), s0.end(), 0); std::fill(s1.begin(), s1.end(), 0);
+        const uint32_t base = off[p0] & ~15u;
+        bool ok = stage(seqs, base, off[p0 + np], off[n], s0.data(), s1.data(), chunks<W>(T));
+        for (int t = 0; t < np; ++t) {
+            const int len = (int)(off[p0 + t + 1] - off[p0 + t]);
+            uint64_t a[W] = {0}, b[W] = {0};
+            if (!ok || len > BITS) status |= kStatusLength;
+            else {
+                const int bit = (int)(off[p0 + t] - base);
+                extract_plane<W>(reinterpret_cast<const uint32_t*>(s0.data()), bit, len, a);
+                extract_plane<W>(reinterpret_cast<const uint32_t*>(s1.data()), bit, len, b);
+            }
+            for (int j = 0; j < W; ++j) { p0o[(p0 + t) * W + j] = a[j]; p1o[(p0 + t) * W + j] = b[j]; }
+        }
+    }
+    if (status_out) *status_out = status;
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int sim_greedy_batch(int W, int T, int k, int x, int o, int e, int global, double pm, double pmm, double pid,
+                     const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, const uint32_t* foff, int64_t n,
+                     int32_t* cost, uint16_t* ops_stage, int stride, uint32_t* nops, uint32_t* status, int64_t* steps) {
+    KParams P{k, x, o, e, global, std::log(pm / 0.25), std::log(pmm / 0.25), std::log(pid / 2 / 0.25)};
+    switch (W) {
+        case 1: return sim_greedy<1>(P, reads, roff, refs, foff, n, T, cost, ops_stage, stride, nops, status, steps);
+        case 2: return sim_greedy<2>(P, reads, roff, refs, foff, n, T, cost, ops_stage, stride, nops, status, steps);
+        case 3: return sim_greedy<3>(P, reads, roff, refs, foff, n, T, cost, ops_stage, stride, nops, status, steps);
+        case 4: return sim_greedy<4>(P, reads, roff, refs, foff, n, T, cost, ops_stage, stride, nops, status, steps);
+    }
+    return -1;
+}
+
+int sim_pack_batch(int W, int T, const uint8_t* seqs, const uint32_t* off, int64_t n, uint64_t* p0, uint64_t* p1,
+                   uint32_t* status) {
+    switch (W) {
+        case 1: return sim_pack<1>(seqs, off, n, T, p0, p1, status);
+        case 2: return sim_pack<2>(seqs, off, n, T, p0, p1, status);
+        case 3: return sim_pack<3>(seqs, off, n, T, p0, p1, status);
+        case 4: return sim_pack<4>(seqs, off, n, T, p0, p1, status);
+    }
+    return -1;
+}
+
+}  // extern "C"

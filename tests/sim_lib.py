@@ -1,0 +1,35 @@
+"""ctypes helpers for tests/host_sim.cpp (the g++ build of the kernels' per-pair code)."""
+import ctypes as C
+
+import numpy as np
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def sim_greedy(S, ol, b, p, T=128):
+    S.sim_greedy_batch.argtypes = [C.c_int] * 7 + [C.c_double] * 3 + [C.c_void_p] * 4 + [
+        C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+    stride = 2 * 64 * p.W + 8
+    cost = np.zeros(b.n, np.int32)
+    stage = np.zeros(b.n * stride, np.uint16)
+    nops = np.zeros(b.n, np.uint32)
+    st = np.zeros(1, np.uint32)
+    steps = np.zeros(1, np.int64)
+    rc = S.sim_greedy_batch(p.W, T, p.k, p.x, p.o, p.e, p.global_, p.match_prob, p.mismatch_prob, p.indel_prob,
+                            _p(b.reads), _p(b.read_off), _p(b.refs), _p(b.ref_off), b.n, _p(cost), _p(stage), stride,
+                            _p(nops), _p(st), _p(steps))
+    assert rc == 0
+    text = [ol.render_ops(stage[i * stride:i * stride + nops[i]]) for i in range(b.n)]
+    return cost, text, int(st[0]), int(steps[0])
+
+
+def sim_pack(S, seqs, off, W, T=128):
+    S.sim_pack_batch.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
+    n = len(off) - 1
+    p0 = np.zeros((n, W), np.uint64)
+    p1 = np.zeros((n, W), np.uint64)
+    st = np.zeros(1, np.uint32)
+    assert S.sim_pack_batch(W, T, _p(seqs), _p(off), n, _p(p0), _p(p1), _p(st)) == 0
+    return p0, p1, int(st[0])

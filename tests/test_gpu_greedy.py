@@ -1,0 +1,171 @@
+"""GPU parity tests (run with -m gpu on a B200): the CUDA path through the C ABI against the golden
+vectors of the unmodified reference and against the oracle on seeded inputs.  Bit-exact or fail."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _batch(ol, pairs):
+    return ol.Batch.from_pairs([(a.encode("latin1"), b.encode("latin1")) for a, b in pairs])
+
+
+def _run(pkg, al, b):
+    out = al.greedy_batch(b.reads, b.read_off, b.refs, b.ref_off)
+    text = [pkg.render_ops(out["ops"][out["op_off"][i]:out["op_off"][i + 1]]) for i in range(b.n)]
+    return out, text
+
+
+def test_gpu_matches_golden(pkg, ol, golden):
+    aligners = {}
+    for s in golden("greedy_ref.json")["sets"]:
+        ps = s["params"]
+        key = (ps["k"], ps["x"], ps["o"], ps["e"], tuple(ps["probs"]))
+        if key not in aligners:
+            aligners[key] = pkg.Aligner(k=ps["k"], x=ps["x"], o=ps["o"], e=ps["e"], match_prob=ps["probs"][0],
+                                        mismatch_prob=ps["probs"][1], indel_prob=ps["probs"][2])
+        b = _batch(ol, s["pairs"])
+        out, text = _run(pkg, aligners[key], b)
+        assert out["cost"].tolist() == s["cost"], s["name"]
+        assert text == s["cigar"], s["name"]
+
+
+@pytest.mark.parametrize("W", [1, 2, 3, 4])
+def test_gpu_matches_oracle_all_widths(pkg, ol, W):
+    rng = np.random.default_rng(300 + W)
+    for (k, x, o, e, g) in [(3, 1, 1, 1, 0), (3, 1, 1, 1, 1), (9, 2, 3, 1, 1), (25, 1, 2, 1, 1)]:
+        b = ol.random_batch(rng, 5000, 1, 64 * W, 0.3, 0.3, 50)
+        al = pkg.Aligner(k=k, x=x, o=o, e=e, max_length=64 * W, alignment_type=1 - g)
+        out, _ = _run(pkg, al, b)
+        r = ol.oracle_greedy(b, ol.make_params(k, x, o, e, W, g), threads=8)
+        assert out["cost"].tolist() == r["cost"].tolist()
+        assert out["op_off"].tolist() == r["op_off"].tolist()
+        assert out["ops"][:out["n_ops"]].tolist() == r["ops"].tolist()
+        al.close()
+
+
+def test_gpu_pack2bit(pkg, ol, golden):
+    vec = golden("convert2bit_ref.json")["vectors"]
+    seqs = np.frombuffer("".join(v["in"] for v in vec).encode("latin1"), np.uint8)
+    off = (np.arange(len(vec) + 1) * 128).astype(np.uint32)
+    al = pkg.Aligner()
+    p0, p1 = al.pack2bit_batch(seqs, off)
+    for i, v in enumerate(vec):
+        assert p0[i].view(np.uint8).tolist() == v["bits0"]
+        assert p1[i].view(np.uint8).tolist() == v["bits1"]
+    rng = np.random.default_rng(6)
+    for W in (1, 2, 3, 4):
+        a = pkg.Aligner(max_length=64 * W)
+        lens = rng.integers(0, 64 * W + 1, 3000)
+        off = np.zeros(len(lens) + 1, np.uint32)
+        off[1:] = np.cumsum(lens)
+        seqs = rng.choice(np.frombuffer(b"ACGTNacgt\0\xff", np.uint8), int(off[-1])).astype(np.uint8)
+        p0, p1 = a.pack2bit_batch(seqs, off)
+        for i in range(0, len(lens), 7):
+            e0, e1 = ol.oracle_pack(seqs[off[i]:off[i + 1]].tobytes(), W)
+            assert p0[i].tolist() == e0.tolist() and p1[i].tolist() == e1.tolist()
+
+
+def test_gpu_edge_cases(pkg, ol):
+    al = pkg.Aligner()
+    # empty batch, empty strings, single pair, costs only
+    out = al.greedy_batch(np.zeros(0, np.uint8), np.zeros(1, np.uint32), np.zeros(0, np.uint8), np.zeros(1, np.uint32))
+    assert out["n_ops"] == 0
+    b = _batch(ol, [("", ""), ("A", ""), ("", "A"), ("ACGT", "ACGT")])
+    out, text = _run(pkg, al, b)
+    assert out["cost"].tolist() == [0, 1, 1, 0] and text == ["", "1I", "1D", "4M"]
+    out = al.greedy_batch(b.reads, b.read_off, b.refs, b.ref_off, want_ops=False)
+    assert out["cost"].tolist() == [0, 1, 1, 0]
+    # errors: too long, |n-m| > MAX_K, ops capacity
+    with pytest.raises(pkg.GasmaError) as ei:
+        bb = _batch(ol, [("A" * 129, "A" * 128)])
+        al.greedy_batch(bb.reads, bb.read_off, bb.refs, bb.ref_off)
+    assert ei.value.code == -2
+    with pytest.raises(pkg.GasmaError) as ei:
+        bb = _batch(ol, [("A" * 10, "A" * 61)])
+        al.greedy_batch(bb.reads, bb.read_off, bb.refs, bb.ref_off)
+    assert ei.value.code == -3
+    with pytest.raises(pkg.GasmaError) as ei:
+        al.greedy_batch(b.reads, b.read_off, b.refs, b.ref_off, ops_cap=1)
+    assert ei.value.code == -4
+    # the context is still usable after an error, and the band can be changed between batches
+    al.set_band(5)
+    out, text = _run(pkg, al, b)
+    assert text == ["", "1I", "1D", "4M"]
+
+
+def test_gpu_generator_and_device_path(pkg, ol):
+    """Device generator == CPU twin; resident (_dev) path == host path; 1M-pair property checks."""
+    import torch
+    al = pkg.Aligner()
+    for mode, e, prof in [(0, 0.10, None), (1, 0.20, None), (2, 0.0, (0.02452, 0.000468, 0.000553))]:
+        cfg = pkg.gen_config(0x47415341, 100, e, mode=mode, profile=prof)
+        ocfg = ol.gen_config(0x47415341, 100, e, mode=mode, profile=prof)
+        n = 3000
+        d_reads = torch.empty(n * 100 + 16, dtype=torch.uint8, device="cuda")
+        d_refs = torch.empty(al.generate_ref_capacity(cfg, n), dtype=torch.uint8, device="cuda")
+        d_roff = torch.empty(n + 1, dtype=torch.int32, device="cuda")
+        d_foff = torch.empty(n + 1, dtype=torch.int32, device="cuda")
+        al.generate_dev(cfg, 12345, n, d_reads, d_roff, d_refs, d_foff)
+        al.synchronize()
+        ref = ol.generate(ocfg, 12345, n)
+        foff = d_foff.cpu().numpy().view(np.uint32)
+        assert foff.tolist() == ref.ref_off.tolist()
+        assert d_roff.cpu().numpy().view(np.uint32).tolist() == ref.read_off.tolist()
+        assert d_reads.cpu().numpy()[:n * 100].tobytes() == ref.reads.tobytes()
+        assert d_refs.cpu().numpy()[:foff[-1]].tobytes() == ref.refs.tobytes()
+        # resident path
+        d_cost = torch.empty(n, dtype=torch.int32, device="cuda")
+        d_ops = torch.empty(n * 64, dtype=torch.int16, device="cuda")
+        d_ooff = torch.empty(n + 1, dtype=torch.int32, device="cuda")
+        al.greedy_batch_dev(d_reads, d_roff, d_refs, d_foff, n, d_cost, d_ops, d_ooff)
+        al.synchronize()
+        r = ol.oracle_greedy(ref, ol.make_params())
+        assert d_cost.cpu().numpy().tolist() == r["cost"].tolist()
+        ooff = d_ooff.cpu().numpy().view(np.uint32)
+        assert ooff.tolist() == r["op_off"].tolist()
+        assert d_ops.cpu().numpy().view(np.uint16)[:ooff[-1]].tolist() == r["ops"].tolist()
+
+
+def test_gpu_full_size_properties(pkg, ol):
+    """BASELINE config sizes (1M pairs): size-independent properties + sampled oracle parity."""
+    import torch
+    al = pkg.Aligner()
+    n = 1_000_000
+    cfg = pkg.gen_config(0x47415342, 100, 0.10)
+    d_reads = torch.empty(n * 100 + 16, dtype=torch.uint8, device="cuda")
+    d_refs = torch.empty(al.generate_ref_capacity(cfg, n), dtype=torch.uint8, device="cuda")
+    d_roff = torch.empty(n + 1, dtype=torch.int32, device="cuda")
+    d_foff = torch.empty(n + 1, dtype=torch.int32, device="cuda")
+    al.generate_dev(cfg, 0, n, d_reads, d_roff, d_refs, d_foff)
+    d_cost = torch.empty(n, dtype=torch.int32, device="cuda")
+    d_ops = torch.empty(n * 32, dtype=torch.int16, device="cuda")
+    d_ooff = torch.empty(n + 1, dtype=torch.int32, device="cuda")
+    al.greedy_batch_dev(d_reads, d_roff, d_refs, d_foff, n, d_cost, d_ops, d_ooff)
+    al.synchronize()
+    cost = d_cost.cpu().numpy()
+    ooff = d_ooff.cpu().numpy().view(np.uint32).astype(np.int64)
+    ops = d_ops.cpu().numpy().view(np.uint16)[:ooff[-1]]
+    assert cost.min() >= 0 and cost.max() <= 60
+    assert (np.diff(ooff) >= 1).all()                       # sorted CSR, every 100 bp pair has >= 1 op
+    # idempotence: a second run gives identical bytes
+    d_cost2 = torch.empty_like(d_cost); d_ops2 = torch.empty_like(d_ops); d_ooff2 = torch.empty_like(d_ooff)
+    al.greedy_batch_dev(d_reads, d_roff, d_refs, d_foff, n, d_cost2, d_ops2, d_ooff2)
+    al.synchronize()
+    assert torch.equal(d_cost, d_cost2) and torch.equal(d_ooff, d_ooff2)
+    assert torch.equal(d_ops[:ooff[-1]], d_ops2[:ooff[-1]])
+    # CIGAR consumes the strings consistently: sum(M)+sum(I) and sum(M)+sum(D) per pair are bounded by lengths,
+    # and the penalty is at least the number of indel ops (x=o=e=1)
+    code = ops & 7
+    ln = (ops >> 3).astype(np.int64)
+    pair_of = np.repeat(np.arange(n), np.diff(ooff))
+    indel = np.bincount(pair_of, weights=(code != 0) * ln, minlength=n)
+    assert (cost >= indel).all()
+    # sampled parity against the oracle: first / middle / last 2000 pairs
+    ocfg = ol.gen_config(0x47415342, 100, 0.10)
+    for lo in (0, n // 2, n - 2000):
+        ref = ol.generate(ocfg, lo, 2000)
+        r = ol.oracle_greedy(ref, ol.make_params(), threads=8)
+        assert cost[lo:lo + 2000].tolist() == r["cost"].tolist()
+        seg = ops[ooff[lo]:ooff[lo + 2000]]
+        assert seg.tolist() == r["ops"].tolist()

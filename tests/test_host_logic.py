@@ -1,0 +1,68 @@
+"""CPU tests of the kernels' per-pair __host__ __device__ code (compiled with g++ by the host_sim fixture)
+against the oracle and the golden vectors.  This is how the device logic is checked in the GPU-less build
+container; the -m gpu tests repeat the comparison through the real C ABI on a B200."""
+import numpy as np
+import pytest
+
+import sim_lib
+
+
+def _batch(ol, pairs):
+    return ol.Batch.from_pairs([(a.encode("latin1"), b.encode("latin1")) for a, b in pairs])
+
+
+def test_kernel_logic_matches_golden(ol, host_sim, golden):
+    for s in golden("greedy_ref.json")["sets"]:
+        ps = s["params"]
+        p = ol.make_params(ps["k"], ps["x"], ps["o"], ps["e"], 2, 1, tuple(ps["probs"]))
+        b = _batch(ol, s["pairs"])
+        cost, text, st, _ = sim_lib.sim_greedy(host_sim, ol, b, p, 128 if ps["k"] < 18 else 32)
+        assert st == 0
+        assert cost.tolist() == s["cost"], s["name"]
+        assert text == s["cigar"], s["name"]
+
+
+@pytest.mark.parametrize("W", [1, 2, 3, 4])
+def test_kernel_logic_matches_oracle_all_widths(ol, host_sim, W):
+    rng = np.random.default_rng(100 + W)
+    for (k, x, o, e, g) in [(3, 1, 1, 1, 1), (7, 2, 3, 1, 1), (3, 1, 1, 1, 0), (0, 1, 1, 1, 1)]:
+        b = ol.random_batch(rng, 1500, 1, 64 * W, 0.3, 0.3, 50)
+        p = ol.make_params(k, x, o, e, W, g)
+        r = ol.oracle_greedy(b, p, threads=4, want_text=True)
+        cost, text, st, steps = sim_lib.sim_greedy(host_sim, ol, b, p)
+        assert st == 0
+        assert cost.tolist() == r["cost"].tolist()
+        assert text == r["text"]
+        assert steps == r["steps"]
+
+
+def test_pack_logic_matches_golden_and_oracle(ol, host_sim, golden):
+    vec = golden("convert2bit_ref.json")["vectors"]
+    seqs = np.frombuffer("".join(v["in"] for v in vec).encode("latin1"), np.uint8)
+    off = (np.arange(len(vec) + 1) * 128).astype(np.uint32)
+    p0, p1, st = sim_lib.sim_pack(host_sim, seqs, off, 2)
+    assert st == 0
+    for i, v in enumerate(vec):
+        assert p0[i].view(np.uint8).tolist() == v["bits0"]
+        assert p1[i].view(np.uint8).tolist() == v["bits1"]
+    # ragged lengths, arbitrary bytes, every alignment of string starts within 16-byte chunks
+    rng = np.random.default_rng(5)
+    for W in (1, 2, 3, 4):
+        lens = rng.integers(0, 64 * W + 1, 700)
+        off = np.zeros(len(lens) + 1, np.uint32)
+        off[1:] = np.cumsum(lens)
+        seqs = rng.choice(np.frombuffer(b"ACGTNacgt\0\xff", np.uint8), int(off[-1])).astype(np.uint8)
+        p0, p1, st = sim_lib.sim_pack(host_sim, seqs, off, W, 128)
+        assert st == 0
+        for i in range(len(lens)):
+            e0, e1 = ol.oracle_pack(seqs[off[i]:off[i + 1]].tobytes(), W)
+            assert p0[i].tolist() == e0.tolist() and p1[i].tolist() == e1.tolist()
+
+
+def test_length_and_band_violations_are_flagged(ol, host_sim):
+    b = _batch(ol, [("A" * 129, "A" * 100), ("ACGT", "ACGT")])
+    cost, _, st, _ = sim_lib.sim_greedy(host_sim, ol, b, ol.make_params())
+    assert st & 1 and cost[0] == -2**31 and cost[1] == 0
+    b = _batch(ol, [("A" * 10, "A" * 61)])
+    _, _, st, _ = sim_lib.sim_greedy(host_sim, ol, b, ol.make_params())
+    assert st & 2

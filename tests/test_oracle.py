@@ -1,0 +1,113 @@
+"""CPU tests: the plain-C oracle against the golden vectors captured from the unmodified reference
+(tests/golden/, made by tests/golden/make_golden.py) and, where oracle/_ref was built, against the
+reference itself on fresh seeded batches."""
+import numpy as np
+import pytest
+
+
+def _batch(ol, pairs):
+    return ol.Batch.from_pairs([(a.encode("latin1"), b.encode("latin1")) for a, b in pairs])
+
+
+def test_oracle_matches_golden_greedy(ol, golden):
+    g = golden("greedy_ref.json")
+    total = 0
+    for s in g["sets"]:
+        ps = s["params"]
+        p = ol.make_params(ps["k"], ps["x"], ps["o"], ps["e"], 2, 1, tuple(ps["probs"]))
+        b = _batch(ol, s["pairs"])
+        r = ol.oracle_greedy(b, p, threads=4, want_text=True)
+        assert r["cost"].tolist() == s["cost"], s["name"]
+        assert r["text"] == s["cigar"], s["name"]
+        assert ol.render_all(r["ops"], r["op_off"]) == s["cigar"]
+        total += b.n
+    assert total > 9000
+
+
+def test_golden_headline_vectors(golden):
+    """G1..G8 of SURVEY.md section 8c, literally."""
+    s = golden("greedy_ref.json")["sets"][0]
+    assert s["params"]["k"] == 3
+    got = list(zip(s["cost"], s["cigar"]))
+    assert got[0] == (6, "22M1D50M1D28M")
+    assert got[1] == (47, "5M1I19M1I12M1I2M2D3M2I1M6M1D3M1D3M1D1M2I4M2D8M1I4M2I1M2D1M2I3M8M1I")
+    assert got[2] == (6, "7M1I44M1D31M1D17M")
+    assert got[3:8] == [(0, "4M"), (1, "1M1I2M"), (4, "4M"), (0, ""), (0, "128M")]
+
+
+def test_oracle_pack_matches_golden(ol, golden):
+    for v in golden("convert2bit_ref.json")["vectors"]:
+        p0, p1 = ol.oracle_pack(v["in"].encode("latin1"), 2)
+        assert p0.view(np.uint8).tolist() == v["bits0"]
+        assert p1.view(np.uint8).tolist() == v["bits1"]
+
+
+def test_significance_constants(golden):
+    import math
+    sig = [float.fromhex(h) for h in golden("convert2bit_ref.json")["significance_default"]]
+    assert sig[0] == math.log(0.80 / 0.25)
+    assert sig[1] == sig[2]  # the tie the FP64 heuristic hinges on (SURVEY.md hazard 2)
+
+
+def test_coverage_matches_golden(ol, golden):
+    import ctypes as C
+    g = golden("coverage_ref.json")
+    codes = {"M": 0, "I": 1, "D": 2, "=": 3, "X": 4}
+    import re
+    for v in g["lcm"]:
+        ops = np.array([(int(n) << 3) | codes[c] for n, c in re.findall(r"(\d+)([MIDX=])", v["cigar"])], np.uint16)
+        s1 = np.frombuffer(v["s1"].encode(), np.uint8)
+        out = np.zeros(600, np.uint8)
+        n = ol.oracle().go_lcm(ol._ptr(s1), len(s1), ol._ptr(ops), len(ops), v["threshold"], ol._ptr(out), 600)
+        assert out[:n].tobytes().decode() == v["lcm"]
+    for v in g["covers"]:
+        a = np.frombuffer(v["a"].encode() + b"\0", np.uint8)
+        b = np.frombuffer(v["b"].encode() + b"\0", np.uint8)
+        assert ol.oracle().go_covers(ol._ptr(a), len(v["a"]), ol._ptr(b), len(v["b"])) == v["covers"]
+
+
+def test_oracle_vs_reference_fresh(ol):
+    """Fresh seeded fuzz against the unmodified reference (only where oracle/_ref could be built)."""
+    if not ol.ref_available():
+        pytest.skip("oracle/_ref not built (needs /root/reference)")
+    rng = np.random.default_rng(4242)
+    for (k, x, o, e) in [(3, 1, 1, 1), (6, 2, 3, 1)]:
+        b = ol.random_batch(rng, 4000, 1, 128, 0.3, 0.3, 50)
+        r = ol.oracle_greedy(b, ol.make_params(k, x, o, e), threads=4, want_text=True)
+        f = ol.ref_greedy(b, k, x, o, e, threads=4)
+        assert r["cost"].tolist() == f["cost"].tolist()
+        assert r["text"] == f["text"]
+
+
+def test_generator_is_deterministic_and_shaped(ol):
+    cfg = ol.gen_config(0x47415341, 100, 0.10)
+    assert cfg.num_errors == 10
+    assert ol.gen_config(1, 100, 0.15).num_errors == 16  # float ceil as benchmark_dataset.h:153 (100*0.15f > 15)
+    a = ol.generate(cfg, 1000, 50)
+    b = ol.generate(cfg, 1010, 10)
+    assert a.slice(10, 20).reads.tobytes() == b.reads.tobytes()
+    assert a.slice(10, 20).refs.tobytes() == b.refs.tobytes()
+    lens = np.diff(a.ref_off.astype(np.int64))
+    assert lens.min() >= 90 and lens.max() <= 110
+    assert set(a.reads.tolist()) <= set(b"ACGT")
+
+
+def test_nw_oracle_basics(ol):
+    b = ol.Batch.from_pairs([(b"ACGT", b"ACGT"), (b"ACGT", b"AGT"), (b"AAAA", b"TTTT"), (b"", b"ACG"), (b"ACGTACGT", b"ACGACGTT")])
+    r = ol.oracle_nw(b, 1, 1, 1)
+    assert r["penalty"].tolist() == [0, 1, 4, 3, 2]
+    assert ol.render_all(r["ops"], r["op_off"])[0] == "4="
+    r2 = ol.oracle_nw(b, 2, 3, 1)
+    assert r2["penalty"].tolist() == [0, 3, 8, 5, 6]
+    # every traceback is consistent: it consumes both strings and re-scores to the penalty
+    for i, text in enumerate(ol.render_all(r2["ops"], r2["op_off"])):
+        import re
+        pen = ri = fi = 0
+        for n, c in re.findall(r"(\d+)([=XID])", text):
+            n = int(n)
+            if c == "=": ri += n; fi += n
+            elif c == "X": ri += n; fi += n; pen += 2 * n
+            elif c == "I": ri += n; pen += 3 + (n - 1)
+            else: fi += n; pen += 3 + (n - 1)
+        a, f = b.pair(i)
+        assert (ri, fi, pen) == (len(a), len(f), int(r2["penalty"][i]))
