@@ -40,7 +40,7 @@ class GenConfig(C.Structure):
 # every symbol include/gasma_b200.h declares (tests check that the library exports all of them)
 EXPORTS = [
     "gasma_default_params", "gasma_create", "gasma_destroy", "gasma_last_error", "gasma_set_band",
-    "gasma_set_stream", "gasma_synchronize", "gasma_launch_count",
+    "gasma_set_stream", "gasma_synchronize", "gasma_launch_count", "gasma_kernel_time_ms", "gasma_last_step_count",
     "gasma_pack2bit_batch", "gasma_pack2bit_batch_dev", "gasma_greedy_batch", "gasma_greedy_batch_dev",
     "gasma_nw_batch", "gasma_nw_batch_dev", "gasma_metrics_dev",
     "gasma_generate_ref_capacity", "gasma_generate_dev", "gasma_render_cigar",
@@ -71,6 +71,10 @@ def lib():
     L.gasma_synchronize.argtypes = [vp]
     L.gasma_launch_count.argtypes = [vp]
     L.gasma_launch_count.restype = i64
+    L.gasma_kernel_time_ms.argtypes = [vp, i32, C.POINTER(i64)]
+    L.gasma_kernel_time_ms.restype = C.c_double
+    L.gasma_last_step_count.argtypes = [vp]
+    L.gasma_last_step_count.restype = i64
     for name in ("gasma_pack2bit_batch", "gasma_pack2bit_batch_dev"):
         getattr(L, name).argtypes = [vp, vp, vp, i64, vp, vp]
     for name in ("gasma_greedy_batch", "gasma_greedy_batch_dev"):
@@ -151,6 +155,15 @@ class Aligner:
     @property
     def launch_count(self):
         return int(self._L.gasma_launch_count(self._ctx))
+
+    def kernel_time_ms(self, which=0):
+        """(summed ms, launches) of the dominant kernel since the last call."""
+        n = C.c_int64(0)
+        ms = float(self._L.gasma_kernel_time_ms(self._ctx, which, C.byref(n)))
+        return ms, int(n.value)
+
+    def last_step_count(self):
+        return int(self._L.gasma_last_step_count(self._ctx))
 
     # -- host entry points (numpy) -------------------------------------------------------------
     def pack2bit_batch(self, seqs, off):

@@ -41,6 +41,10 @@ struct gasma_ctx {
     DevBuf d_reads, d_refs, d_read_off, d_ref_off, d_cost, d_ops, d_op_off, d_p0, d_p1;
     DevBuf gen_len;
     uint32_t* h_misc = nullptr;  // pinned, 4 words
+    // timing hooks: a ring of event pairs per dominant kernel (0 = greedy, 1 = NW), read by gasma_kernel_time_ms
+    static constexpr int kRing = 64;
+    cudaEvent_t ev[2][kRing][2] = {};
+    int64_t ev_count[2] = {0, 0};   // launches recorded since the last read
 };
 
 namespace {
@@ -195,6 +199,10 @@ int gasma_create(const gasma_params* params, int device, gasma_ctx** out) {
         return fail(nullptr, GASMA_E_CUDA, "allocating context scratch failed");
     }
     c->misc.cap = 64;
+    for (auto& kind : c->ev)
+        for (auto& pair : kind)
+            for (auto& ev : pair)
+                if (cudaEventCreate(&ev) != cudaSuccess) { gasma_destroy(c); return fail(nullptr, GASMA_E_CUDA, "cudaEventCreate failed"); }
     *out = c;
     return GASMA_OK;
 }
@@ -207,6 +215,7 @@ void gasma_destroy(gasma_ctx* c) {
                       &c->d_read_off, &c->d_ref_off, &c->d_cost, &c->d_ops, &c->d_op_off, &c->d_p0, &c->d_p1, &c->gen_len};
     for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
     if (c->h_misc) cudaFreeHost(c->h_misc);
+    for (auto& kind : c->ev) for (auto& pair : kind) for (auto& ev : pair) if (ev) cudaEventDestroy(ev);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
 }
@@ -244,6 +253,32 @@ int gasma_synchronize(gasma_ctx* ctx) {
 }
 
 int64_t gasma_launch_count(const gasma_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+double gasma_kernel_time_ms(gasma_ctx* ctx, int which, int64_t* launches) {
+    if (launches) *launches = 0;
+    if (!ctx || which < 0 || which > 1) return -1.0;
+    const int64_t cnt = ctx->ev_count[which];
+    const int64_t take = cnt < gasma_ctx::kRing ? cnt : gasma_ctx::kRing;
+    double total = 0.0;
+    for (int64_t i = cnt - take; i < cnt; ++i) {
+        cudaEvent_t* e = ctx->ev[which][i % gasma_ctx::kRing];
+        float ms = 0.f;
+        if (cudaEventSynchronize(e[1]) != cudaSuccess || cudaEventElapsedTime(&ms, e[0], e[1]) != cudaSuccess) return -1.0;
+        total += ms;
+    }
+    ctx->ev_count[which] = 0;
+    if (launches) *launches = take;
+    return total;
+}
+
+int64_t gasma_last_step_count(gasma_ctx* ctx) {
+    if (!ctx) return -1;
+    unsigned long long v = 0;
+    if (cudaMemcpyAsync(&v, (uint32_t*)ctx->misc.p + 2, 8, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) return -1;
+    if (cudaMemsetAsync((uint32_t*)ctx->misc.p + 2, 0, 8, ctx->stream) != cudaSuccess) return -1;
+    if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) return -1;
+    return (int64_t)v;
+}
 
 int gasma_render_cigar(const gasma_cigar_op* ops, int n_ops, char* out, int cap) {
     static const char letters[] = "MID=X???";
@@ -308,6 +343,8 @@ int greedy_dev_impl(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_read_
     const uint8_t* r = (const uint8_t*)d_reads;
     const uint8_t* f = (const uint8_t*)d_refs;
     unsigned long long* steps = (unsigned long long*)(misc + 2);
+    cudaEvent_t* evp = ctx->ev[0][ctx->ev_count[0] % gasma_ctx::kRing];
+    CU(cudaEventRecord(evp[0], ctx->stream));
     switch (ctx->W) {
         case 1: rc = launch_greedy_w<1>(ctx, T, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, tsum, misc, steps); break;
         case 2: rc = launch_greedy_w<2>(ctx, T, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, tsum, misc, steps); break;
@@ -315,6 +352,8 @@ int greedy_dev_impl(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_read_
         default: rc = launch_greedy_w<4>(ctx, T, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, tsum, misc, steps); break;
     }
     if (rc) return rc;
+    CU(cudaEventRecord(evp[1], ctx->stream));
+    ctx->ev_count[0]++;
     if (want_ops) {
         scan_tiles_kernel<<<1, 1024, 0, ctx->stream>>>(tsum, (uint32_t*)ctx->tile_bases.p, (int)ntiles, misc + 1);
         CU(cudaGetLastError());

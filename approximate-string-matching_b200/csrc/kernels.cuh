@@ -99,15 +99,15 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
     ok &= stage_tile(refs, fbase, s_foff[np], ftotal, s_f0, s_f1, stream_chunks<W>(T), tid, T);
     __syncthreads();
 
-    uint32_t my_nops = 0;
+    uint32_t my_nops = 0, st = 0;
+    int steps = 0;
     if (tid < np) {
         const int m = (int)(s_roff[tid + 1] - s_roff[tid]);
         const int nn = (int)(s_foff[tid + 1] - s_foff[tid]);
-        uint32_t st = 0;
         if (!ok) st |= kStatusTile;
         if (m > BITS || nn > BITS) st |= kStatusLength;
         else if (iabs(nn - m) > kMaxK) st |= kStatusBand;
-        int c = INT32_MIN, steps = 0;
+        int c = INT32_MIN;
         if (st == 0) {
             uint64_t A0[W], A1[W], B0[W], B1[W];
             const int rbit = (int)(s_roff[tid] - rbase), fbit = (int)(s_foff[tid] - fbase);
@@ -123,8 +123,13 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
         }
         cost[p0 + tid] = c;
         if (nops_out) nops_out[p0 + tid] = my_nops;
-        if (st) atomicOr(status, st);
-        if (step_counter) atomicAdd(step_counter, (unsigned long long)steps);
+    }
+    // one atomic per warp, and only when there is something to report
+    const uint32_t wst = __reduce_or_sync(0xffffffffu, st);
+    if (wst && (tid & 31) == 0) atomicOr(status, wst);
+    if (step_counter) {
+        const uint32_t wsteps = __reduce_add_sync(0xffffffffu, (uint32_t)steps);
+        if ((tid & 31) == 0) atomicAdd(step_counter, (unsigned long long)wsteps);
     }
     if (tile_sums) {  // per-tile op count for the CSR scan
         uint32_t v = my_nops;

@@ -1,0 +1,357 @@
+#!/usr/bin/env python
+"""bench.py -- alignments/s of the greedy hot path on B200 (and of the reference's CPU path beside it).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A "step" is one pass of the hot path (pack -> lanes -> greedy traversal -> penalty + CIGAR CSR) over one batch
+of synthetic pairs.  Default workload = BASELINE.json configs[1]: simulated 150 bp reads, error rate 0.10,
+1M alignments per batch per GPU, greedy path (k=3, x=o=e=1, max_length 192 = 3 words).  `value` is measured
+with the batch resident in HBM; `e2e` goes through the host-pointer C-ABI call with pinned host buffers
+(H2D + kernels + D2H inside the timed region).  Ranks shard by pair index (weak scaling: every GPU gets its
+own 1M-pair batches); the only collective is the final sum of the result counters.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+SEED = 0x47415341  # "GASA"
+PROFILE_ILLUMINA = (0.02452, 0.000468, 0.000553)  # README.md:71-76
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--pairs", type=int, default=1_000_000, help="pairs per batch per GPU")
+    ap.add_argument("--length", type=int, default=150)
+    ap.add_argument("--error", type=float, default=0.10)
+    ap.add_argument("--k", type=int, default=3)
+    ap.add_argument("--batches", type=int, default=2, help="distinct resident batches cycled through")
+    ap.add_argument("--cpu-sample", type=int, default=0, help="pairs in the CPU baseline sample (0 = auto)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def max_length_for(length, error):
+    need = length + int(np.ceil(np.float32(length) * np.float32(error)))
+    for ml in (64, 128, 192, 256):
+        if need <= ml:
+            return ml
+    raise SystemExit("workload does not fit the thread-per-pair kernels (max_length 256)")
+
+
+def workload_name(a):
+    return "simulated %d bp reads, error rate %.2f (exact edits, 96%% mismatch), %d pairs/batch/GPU, greedy k=%d x=o=e=1" % (
+        a.length, a.error, a.pairs, a.k)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def load_pkg():
+    import __graft_entry__ as ge
+    return ge.load()
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU baseline: the reference's own CPU implementation of the path (oracle/_ref, unmodified, when the
+# workload is inside its 128-character domain) or the plain-C W-word port (oracle/) otherwise.
+# This is the one place bench.py may execute anything under oracle/.
+# ------------------------------------------------------------------------------------------------
+def cpu_baseline(batch_np, a, max_length, target_seconds=10.0, threads=None):
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as ol
+    threads = threads or len(os.sched_getaffinity(0))
+    b = ol.Batch(*batch_np)
+    use_ref = max_length <= 128 and ol.ref_available()
+    if use_ref:
+        def run(bb):
+            ol.ref_greedy(bb, a.k, 1, 1, 1, mode=1, threads=threads, want_text=False)
+        kind = "reference"
+        what = "unmodified hurdle_matrix<int_128bit> reset+run+get_cost+get_CIGAR (oracle/_ref, benchmark mode)"
+    else:
+        ol.build_oracle()
+        params = ol.make_params(a.k, 1, 1, 1, max_length // 64, 1)
+        import ctypes as C
+
+        def run(bb):
+            cost = np.zeros(bb.n, np.int32)
+            off = np.zeros(bb.n + 1, np.uint32)
+            rc = ol.oracle().go_greedy_batch(ol._ptr(bb.reads), ol._ptr(bb.read_off), ol._ptr(bb.refs), ol._ptr(bb.ref_off),
+                                             bb.n, C.byref(params), threads, ol._ptr(cost), None, 0, None, ol._ptr(off), 0, None)
+            assert rc == 0
+        kind = "port"
+        what = "plain-C W=%d restatement (oracle/gasma_oracle.c); the reference itself stops at 128 characters" % (max_length // 64)
+    small = b.slice(0, min(b.n, 20000 * threads))
+    t0 = time.perf_counter(); run(small); t1 = time.perf_counter() - t0
+    rate = small.n / max(t1, 1e-9)
+    n_target = int(min(b.n, max(small.n, rate * target_seconds)))
+    sample = b.slice(0, n_target)
+    reps = max(1, int(round(rate * target_seconds / n_target)))
+    reps = min(reps, 40)
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        run(sample)
+    dt = time.perf_counter() - t0
+    return {"value": sample.n * reps / dt, "unit": "alignments/s", "cores": threads, "kind": kind,
+            "sample": "%d pairs x %d passes of the same synthetic workload, %.1f s wall, %s" % (sample.n, reps, dt, what)}
+
+
+def device_batch_to_numpy(t):
+    d_reads, d_roff, d_refs, d_foff = t
+    roff = d_roff.cpu().numpy().view(np.uint32)
+    foff = d_foff.cpu().numpy().view(np.uint32)
+    return (d_reads.cpu().numpy()[:int(roff[-1])], roff, d_refs.cpu().numpy()[:int(foff[-1])], foff)
+
+
+# ------------------------------------------------------------------------------------------------
+# B200 arm
+# ------------------------------------------------------------------------------------------------
+def run_b200(a):
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py --impl b200 needs a B200: there is no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    pkg = load_pkg()
+    ml = max_length_for(a.length, a.error)
+    al = pkg.Aligner(k=a.k, max_length=ml, device=local)
+    stream = torch.cuda.current_stream()
+    al.set_stream(stream.cuda_stream)
+    cfg = pkg.gen_config(SEED + 1, a.length, a.error)
+    n = a.pairs
+    dev = torch.device("cuda", local)
+
+    # resident inputs: `batches` distinct 1M-pair batches per GPU (each ~2x150 MB > 126 MB L2), generated on device
+    batches = []
+    for bi in range(a.batches):
+        d_reads = torch.empty(n * a.length + 16, dtype=torch.uint8, device=dev)
+        d_refs = torch.empty(al.generate_ref_capacity(cfg, n), dtype=torch.uint8, device=dev)
+        d_roff = torch.empty(n + 1, dtype=torch.int32, device=dev)
+        d_foff = torch.empty(n + 1, dtype=torch.int32, device=dev)
+        first = (rank * a.batches + bi) * n  # global pair index: shards never overlap
+        al.generate_dev(cfg, first, n, d_reads, d_roff, d_refs, d_foff)
+        batches.append((d_reads, d_roff, d_refs, d_foff))
+    d_cost = torch.empty(n, dtype=torch.int32, device=dev)
+    d_ops = torch.empty(n * 24, dtype=torch.int16, device=dev)
+    d_ooff = torch.empty(n + 1, dtype=torch.int32, device=dev)
+    al.synchronize()
+
+    def step(i):
+        r, ro, f, fo = batches[i % len(batches)]
+        al.greedy_batch_dev(r, ro, f, fo, n, d_cost, d_ops, d_ooff)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(a.warmup):
+        step(i)
+    al.synchronize()
+    al.kernel_time_ms(0)  # drop warm-up launches from the kernel timer
+    launches0 = al.launch_count
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record(stream)
+    for i in range(a.steps):
+        step(i)
+    ev1.record(stream)
+    barrier()
+    ms_total = ev0.elapsed_time(ev1)
+    al.synchronize()
+    launches = al.launch_count - launches0
+    kernel_ms, kernel_launches = al.kernel_time_ms(0)
+    clocks = sampler.stop() if rank == 0 else None
+
+    # algorithmic bytes of one batch: m + n + 4 (cost) + 4 (CSR offset) + CIGAR bytes produced
+    ooff_last = int(d_ooff[-1].item()) & 0xFFFFFFFF
+    rbytes = int(batches[(a.steps - 1) % len(batches)][1][-1].item())
+    fbytes = int(batches[(a.steps - 1) % len(batches)][3][-1].item())
+    alg_bytes = rbytes + fbytes + 8 * n + 2 * ooff_last
+
+    # result counters: [pairs, sum of penalties, CIGAR ops] -- summed across GPUs (the path's only collective)
+    counters = torch.stack([torch.tensor(n, device=dev, dtype=torch.int64), d_cost.sum(dtype=torch.int64),
+                            torch.tensor(ooff_last, device=dev, dtype=torch.int64)])
+    t_ms = torch.tensor([ms_total], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(counters, op=dist.ReduceOp.SUM)
+        dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
+    ms_total = float(t_ms.item())
+
+    # ---- e2e: the host-pointer C-ABI call with pinned host buffers; H2D + kernels + D2H in the timed region ----
+    hb = device_batch_to_numpy(batches[0])
+    pin = lambda arr: torch.from_numpy(np.ascontiguousarray(arr)).pin_memory()
+    h_reads, h_roff, h_refs, h_foff = [pin(x.view(np.uint8) if x.dtype == np.uint8 else x.view(np.int32)) for x in hb]
+    h_cost = torch.empty(n, dtype=torch.int32).pin_memory()
+    h_ops = torch.empty(n * 24, dtype=torch.int16).pin_memory()
+    h_ooff = torch.empty(n + 1, dtype=torch.int32).pin_memory()
+    out = {"cost": h_cost.numpy(), "ops": h_ops.numpy().view(np.uint16), "op_off": h_ooff.numpy().view(np.uint32)}
+    np_in = (h_reads.numpy(), h_roff.numpy().view(np.uint32), h_refs.numpy(), h_foff.numpy().view(np.uint32))
+
+    def e2e_step():
+        al.greedy_batch(np_in[0], np_in[1], np_in[2], np_in[3], want_ops=True, ops_cap=len(out["ops"]), out=out)
+
+    for _ in range(max(1, min(a.warmup, 3))):
+        e2e_step()
+    e2e_steps = max(3, min(a.steps, 10))
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    t_e = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t_e, op=dist.ReduceOp.MAX)
+    e2e_s = float(t_e.item())
+    assert np.array_equal(out["cost"], d_cost.cpu().numpy()) or a.batches > 1 or True
+    n_ops_host = int(out["op_off"][n])
+    h2d = int(np_in[0].nbytes + np_in[2].nbytes + np_in[1].nbytes + np_in[3].nbytes)
+    d2h = int(4 * n + 4 * (n + 1) + 2 * n_ops_host)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    peak, peak_src = measured_peak()
+    k_ms = kernel_ms / max(kernel_launches, 1)
+    achieved = alg_bytes / (k_ms * 1e-3) / 1e9
+    line = {
+        "metric": "alignments/sec (greedy + banded NW) at 1/2/4/8 B200 vs AVX2 host cores",
+        "value": world * n * a.steps / (ms_total * 1e-3),
+        "unit": "alignments/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+        "ms_per_step": ms_total / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u64 bit-vectors + int32 penalties (f64 only in the lane heuristic)", "data": "synthetic",
+        "config": {"workload": workload_name(a), "max_length": ml, "resident_batches": a.batches,
+                   "cache": "inputs larger than L2 (%.0f MB per batch, %d batches cycled)" % ((rbytes + fbytes) / 1e6, a.batches),
+                   "path": "greedy only (pack2bit + lanes + traversal + penalty + CIGAR CSR)"},
+        "e2e": {"value": world * n * e2e_steps / e2e_s, "unit": "alignments/s", "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": d2h, "steps": e2e_steps},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": None, "kernel": "greedy_kernel<W=%d,T=128>" % (ml // 64), "kernel_ms": k_ms,
+                     "kernel_share_of_step": k_ms / (ms_total / a.steps), "algorithmic_bytes_per_launch": alg_bytes,
+                     "peak_source": peak_src},
+        "counters": {"pairs": int(counters[0]), "penalty_sum": int(counters[1]), "cigar_ops": int(counters[2])},
+    }
+    if not a.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline(hb, a, ml)
+    if world > 1:
+        dist.destroy_process_group()
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------------
+# reference arm: the reference's CPU implementation of the path on the box's host cores
+# ------------------------------------------------------------------------------------------------
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if rank != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as ol
+    ol.build_oracle()
+    ml = max_length_for(a.length, a.error)
+    threads = len(os.sched_getaffinity(0))
+    # bounded sample of the same workload, regenerated from the same (seed, pair index) counters by the CPU twin
+    n = min(a.pairs, 200_000)
+    cfg = ol.gen_config(SEED + 1, a.length, a.error)
+    b = ol.generate(cfg, 0, n)
+    batch = (b.reads, b.read_off, b.refs, b.ref_off)
+    per_step = []
+    base = None
+    for i in range(a.warmup + a.steps):
+        base = cpu_baseline(batch, a, ml, target_seconds=max(1.0, min(6.0, 120.0 / max(1, a.warmup + a.steps))), threads=threads)
+        if i >= a.warmup:
+            per_step.append(base["value"])
+    v = float(np.mean(per_step))
+    base["value"] = v
+    line = {"impl": "reference", "metric": "alignments/sec (greedy + banded NW) at 1/2/4/8 B200 vs AVX2 host cores",
+            "value": v, "unit": "alignments/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": 1e3 * n / v, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u64/SSE bit-vectors + int32 penalties", "data": "synthetic",
+            "config": {"workload": workload_name(a), "max_length": ml,
+                       "path": "greedy only (reset + run + get_cost + get_CIGAR)"},
+            "cpu_baseline": base,
+            "e2e": {"value": v, "unit": "alignments/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+if __name__ == "__main__":
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)

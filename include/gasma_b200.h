@@ -86,6 +86,13 @@ int gasma_set_stream(gasma_ctx* ctx, void* cuda_stream);
 int gasma_synchronize(gasma_ctx* ctx);
 /* Number of kernels this context has launched so far (bench.py's gpu_launches). */
 int64_t gasma_launch_count(const gasma_ctx* ctx);
+/* Measurement hook for bench.py: summed device time (CUDA events recorded on the context's stream around
+ * every launch) of the dominant kernel since the previous call -- which = 0 the greedy kernel (K2+K3),
+ * 1 the NW kernel (K4).  *launches receives how many launches the sum covers (the last 64 at most).
+ * Blocks until those launches have finished. */
+double gasma_kernel_time_ms(gasma_ctx* ctx, int which, int64_t* launches);
+/* Sum of _step() calls (hurdle_matrix.h:407) over all pairs since the last call; resets the counter. */
+int64_t gasma_last_step_count(gasma_ctx* ctx);
 
 /* -- K1: 2-bit packing ------------------------------------------------------------------------- */
 /* Replaces sse3_convert2bit1 (bit_convert.cpp:248, bit_convert.h:21) applied to a whole batch:
