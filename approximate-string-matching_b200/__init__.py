@@ -194,6 +194,21 @@ class Aligner:
             out["n_ops"] = int(out["op_off"][n])
         return out
 
+    def nw_batch(self, reads, read_off, refs, ref_off, bound=None, want_ops=True, ops_cap=None):
+        n = len(read_off) - 1
+        out = {"penalty": np.empty(n, np.int32)}
+        ops = op_off = None
+        if want_ops:
+            cap = ops_cap if ops_cap is not None else max(16, int(len(reads)) + int(len(refs)) + 2 * n)
+            ops = out["ops"] = np.empty(cap, np.uint16)
+            op_off = out["op_off"] = np.empty(n + 1, np.uint32)
+        self._check(self._L.gasma_nw_batch(self._ctx, _np_ptr(reads), _np_ptr(read_off), _np_ptr(refs), _np_ptr(ref_off), n,
+                                           _np_ptr(bound), _np_ptr(out["penalty"]), _np_ptr(ops),
+                                           0 if ops is None else len(ops), _np_ptr(op_off)))
+        if want_ops:
+            out["n_ops"] = int(op_off[n])
+        return out
+
     # -- device entry points (torch CUDA tensors) -----------------------------------------------
     def pack2bit_batch_dev(self, d_seqs, d_off, n, d_p0, d_p1):
         self._check(self._L.gasma_pack2bit_batch_dev(self._ctx, _dev_ptr(d_seqs), _dev_ptr(d_off), n, _dev_ptr(d_p0),

@@ -11,6 +11,7 @@
 #include <string>
 
 #include "kernels.cuh"
+#include "nw_kernels.cuh"
 #include "generate.cuh"
 
 using namespace gasma;
@@ -39,7 +40,7 @@ struct gasma_ctx {
     DevBuf ops_stage, nops, tile_sums, tile_bases, misc;  // misc: [0] status u32, [1] total ops u32, [2..3] step counter u64
     // device mirrors for the host-pointer entry points
     DevBuf d_reads, d_refs, d_read_off, d_ref_off, d_cost, d_ops, d_op_off, d_p0, d_p1;
-    DevBuf gen_len;
+    DevBuf gen_len, d_bound, nw_deferred, nw_tb, nw_pool_hi, nw_pool_tb;
     uint32_t* h_misc = nullptr;  // pinned, 4 words
     // timing hooks: a ring of event pairs per dominant kernel (0 = greedy, 1 = NW), read by gasma_kernel_time_ms
     static constexpr int kRing = 64;
@@ -212,7 +213,7 @@ void gasma_destroy(gasma_ctx* c) {
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     DevBuf* bufs[] = {&c->ops_stage, &c->nops, &c->tile_sums, &c->tile_bases, &c->misc, &c->d_reads, &c->d_refs,
-                      &c->d_read_off, &c->d_ref_off, &c->d_cost, &c->d_ops, &c->d_op_off, &c->d_p0, &c->d_p1, &c->gen_len};
+                      &c->d_read_off, &c->d_ref_off, &c->d_cost, &c->d_ops, &c->d_op_off, &c->d_p0, &c->d_p1, &c->gen_len, &c->d_bound, &c->nw_deferred, &c->nw_tb, &c->nw_pool_hi, &c->nw_pool_tb};
     for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
     if (c->h_misc) cudaFreeHost(c->h_misc);
     for (auto& kind : c->ev) for (auto& pair : kind) for (auto& ev : pair) if (ev) cudaEventDestroy(ev);
@@ -239,7 +240,7 @@ int gasma_set_band(gasma_ctx* ctx, int k) {
 int gasma_set_stream(gasma_ctx* ctx, void* cuda_stream) {
     if (!ctx) return GASMA_E_ARG;
     CU(cudaStreamSynchronize(ctx->stream));
-    ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
+    ctx->stream = (cudaStream_t)cuda_stream;  // taken literally: NULL is the legacy default stream
     return GASMA_OK;
 }
 
@@ -360,10 +361,10 @@ int greedy_dev_impl(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_read_
         ctx->launches++;
         if (T == 128)
             compact_ops_kernel<128><<<(unsigned)ntiles, 128, 0, ctx->stream>>>(stage, stride, nops, (uint32_t*)ctx->tile_bases.p,
-                                                                             (long long)n, d_ops, (long long)ops_cap, d_op_off);
+                                                                             (long long)n, d_ops, (long long)ops_cap, d_op_off, 0);
         else
             compact_ops_kernel<32><<<(unsigned)ntiles, 32, 0, ctx->stream>>>(stage, stride, nops, (uint32_t*)ctx->tile_bases.p,
-                                                                           (long long)n, d_ops, (long long)ops_cap, d_op_off);
+                                                                           (long long)n, d_ops, (long long)ops_cap, d_op_off, 0);
         CU(cudaGetLastError());
         ctx->launches++;
     }

@@ -196,7 +196,7 @@ template <int T>
 __global__ void __launch_bounds__(T)
 compact_ops_kernel(const uint16_t* __restrict__ ops_stage, int ops_stride, const uint32_t* __restrict__ nops,
                    const uint32_t* __restrict__ tile_bases, long long n, uint16_t* __restrict__ ops_out,
-                   long long ops_cap, uint32_t* __restrict__ op_off) {
+                   long long ops_cap, uint32_t* __restrict__ op_off, int from_end) {
     __shared__ uint32_t s_warp[T / 32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const long long p = (long long)blockIdx.x * T + tid;
@@ -216,7 +216,8 @@ compact_ops_kernel(const uint16_t* __restrict__ ops_stage, int ops_stride, const
     if (p < n) {
         op_off[p] = off;
         if (p == n - 1) op_off[n] = off + v;
-        const uint16_t* src = ops_stage + (size_t)p * ops_stride;
+        // rows filled back to front (NW traceback) keep their ops at the end of the row
+        const uint16_t* src = ops_stage + (size_t)p * ops_stride + (from_end ? (uint32_t)ops_stride - v : 0u);
         for (uint32_t i = 0; i < v; ++i)
             if ((long long)(off + i) < ops_cap) ops_out[off + i] = src[i];
     }

@@ -79,7 +79,8 @@ void gasma_destroy(gasma_ctx* ctx);
 const char* gasma_last_error(const gasma_ctx* ctx);
 /* Change the band between batches: the `error` argument of reset() (hurdle_matrix.h:625). */
 int gasma_set_band(gasma_ctx* ctx, int k);
-/* Use the caller's cudaStream_t (e.g. torch's current stream) for all _dev work. NULL = own stream. */
+/* Use the caller's cudaStream_t (e.g. torch's current stream) for all work of this context.  The handle is
+ * taken literally: NULL means the legacy default stream.  A fresh context uses a private non-blocking stream. */
 int gasma_set_stream(gasma_ctx* ctx, void* cuda_stream);
 /* Blocks until everything enqueued on the context's stream has finished; surfaces async errors
  * and the device-side status word (length / band / step-limit violations seen by _dev calls). */

@@ -12,6 +12,9 @@
 #include "../approximate-string-matching_b200/csrc/common.cuh"
 #include "../approximate-string-matching_b200/csrc/pack.cuh"
 #include "../approximate-string-matching_b200/csrc/greedy.cuh"
+#include "../approximate-string-matching_b200/csrc/nw.cuh"
+#include "../approximate-string-matching_b200/csrc/metrics.cuh"
+#include "../approximate-string-matching_b200/csrc/generate.cuh"
 
 #include <cmath>
 
@@ -114,9 +117,70 @@ int sim_pack(const uint8_t* seqs, const uint32_t* off, int64_t n, int T, uint64_
     return 0;
 }
 
+// NW: same staging as the kernels, band arrays with stride 1, traceback rows in a heap scratch
+template <int W>
+int sim_nw(int x, int o, int e, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, const uint32_t* foff,
+           int64_t n, int T, const int32_t* bound, int32_t* penalty, uint16_t* ops_stage, int stride, uint32_t* nops,
+           int cap_band, int64_t* n_wide) {
+    constexpr int BITS = 64 * W;
+    std::vector<uint16_t> r0(elems<W>(T)), r1(elems<W>(T)), f0(elems<W>(T)), f1(elems<W>(T));
+    std::vector<int32_t> H(2 * BITS + 2), I(2 * BITS + 2);
+    const int tbw_fast = cap_band / 8, tbw_wide = (2 * BITS + 1 + 7) / 8;
+    std::vector<uint32_t> tb((size_t)BITS * tbw_wide);
+    int64_t wide = 0;
+    for (int64_t p0 = 0; p0 < n; p0 += T) {
+        const int np = (int)std::min<int64_t>(T, n - p0);
+        std::fill(r0.begin(), r0.end(), 0); std::fill(r1.begin(), r1.end(), 0);
+        std::fill(f0.begin(), f0.end(), 0); std::fill(f1.begin(), f1.end(), 0);
+        const uint32_t rbase = roff[p0] & ~15u, fbase = foff[p0] & ~15u;
+        stage(reads, rbase, roff[p0 + np], roff[n], r0.data(), r1.data(), chunks<W>(T));
+        stage(refs, fbase, foff[p0 + np], foff[n], f0.data(), f1.data(), chunks<W>(T));
+        for (int t = 0; t < np; ++t) {
+            const int64_t p = p0 + t;
+            const int m = (int)(roff[p + 1] - roff[p]), nn = (int)(foff[p + 1] - foff[p]);
+            uint64_t A0[W], A1[W], B0[W], B1[W];
+            extract_plane<W>(reinterpret_cast<const uint32_t*>(r0.data()), (int)(roff[p] - rbase), m, A0);
+            extract_plane<W>(reinterpret_cast<const uint32_t*>(r1.data()), (int)(roff[p] - rbase), m, A1);
+            extract_plane<W>(reinterpret_cast<const uint32_t*>(f0.data()), (int)(foff[p] - fbase), nn, B0);
+            extract_plane<W>(reinterpret_cast<const uint32_t*>(f1.data()), (int)(foff[p] - fbase), nn, B1);
+            const NwBand bd = nw_band(m, nn, o, e, bound ? bound[p] : -1);
+            const bool is_wide = bd.hi - bd.lo + 1 > cap_band;
+            wide += is_wide;
+            NwScratch S{H.data(), I.data(), 1, ops_stage ? tb.data() : nullptr, is_wide ? tbw_wide : tbw_fast};
+            penalty[p] = nw_forward<W>(x, o, e, A0, A1, B0, B1, m, nn, bd, S);
+            if (ops_stage) nops[p] = (uint32_t)nw_traceback<W>(A0, A1, B0, B1, m, nn, bd, S, ops_stage + (size_t)p * stride, stride);
+        }
+    }
+    if (n_wide) *n_wide = wide;
+    return 0;
+}
+
 }  // namespace
 
 extern "C" {
+
+int sim_nw_batch(int W, int T, int x, int o, int e, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs,
+                 const uint32_t* foff, int64_t n, const int32_t* bound, int32_t* penalty, uint16_t* ops_stage, int stride,
+                 uint32_t* nops, int cap_band, int64_t* n_wide) {
+    switch (W) {
+        case 1: return sim_nw<1>(x, o, e, reads, roff, refs, foff, n, T, bound, penalty, ops_stage, stride, nops, cap_band, n_wide);
+        case 2: return sim_nw<2>(x, o, e, reads, roff, refs, foff, n, T, bound, penalty, ops_stage, stride, nops, cap_band, n_wide);
+        case 3: return sim_nw<3>(x, o, e, reads, roff, refs, foff, n, T, bound, penalty, ops_stage, stride, nops, cap_band, n_wide);
+        case 4: return sim_nw<4>(x, o, e, reads, roff, refs, foff, n, T, bound, penalty, ops_stage, stride, nops, cap_band, n_wide);
+    }
+    return -1;
+}
+
+int sim_coverage(const uint8_t* s1, int s1_len, const uint16_t* g_ops, int g_n, const uint16_t* n_ops, int n_n) {
+    return coverage_pair(s1, s1_len, g_ops, g_n, n_ops, n_n);
+}
+
+int sim_generate_pair(uint64_t seed, int length, int mode, int num_errors, uint64_t thr_mismatch, uint64_t thr_sub,
+                      uint64_t thr_ins, uint64_t thr_del, uint64_t pair, char* read, char* ref, int* len_only) {
+    GenCfg c{seed, length, mode, num_errors, thr_mismatch, thr_sub, thr_ins, thr_del};
+    *len_only = gen_pair<false>(c, pair, nullptr, nullptr);
+    return gen_pair<true>(c, pair, read, ref);
+}
 
 int sim_greedy_batch(int W, int T, int k, int x, int o, int e, int global, double pm, double pmm, double pid,
                      const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, const uint32_t* foff, int64_t n,

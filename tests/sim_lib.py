@@ -33,3 +33,18 @@ def sim_pack(S, seqs, off, W, T=128):
     st = np.zeros(1, np.uint32)
     assert S.sim_pack_batch(W, T, _p(seqs), _p(off), n, _p(p0), _p(p1), _p(st)) == 0
     return p0, p1, int(st[0])
+
+
+def sim_nw(S, b, W, x, o, e, bound=None, want_ops=True, cap_band=64, T=128):
+    S.sim_nw_batch.argtypes = [C.c_int] * 5 + [C.c_void_p] * 4 + [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
+                                                                     C.c_void_p, C.c_int, C.c_void_p]
+    stride = 2 * 64 * W + 8
+    pen = np.zeros(b.n, np.int32)
+    stage = np.zeros(b.n * stride, np.uint16) if want_ops else None
+    nops = np.zeros(b.n, np.uint32)
+    wide = np.zeros(1, np.int64)
+    rc = S.sim_nw_batch(W, T, x, o, e, _p(b.reads), _p(b.read_off), _p(b.refs), _p(b.ref_off), b.n, _p(bound), _p(pen),
+                        _p(stage), stride, _p(nops), cap_band, _p(wide))
+    assert rc == 0
+    ops = [stage[(i + 1) * stride - nops[i]:(i + 1) * stride] for i in range(b.n)] if want_ops else None
+    return pen, ops, int(wide[0])

@@ -1,0 +1,57 @@
+"""GPU parity tests for K4 (NW verifier) and K5 (accuracy / coverage counters) through the C ABI."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("W", [1, 2, 3, 4])
+def test_gpu_nw_matches_oracle(pkg, ol, W):
+    rng = np.random.default_rng(700 + W)
+    for (x, o, e) in [(1, 1, 1), (2, 3, 1), (4, 6, 2)]:
+        b = ol.random_batch(rng, 3000, 1, 64 * W, 0.3, 0.4, 50)
+        al = pkg.Aligner(k=3, x=x, o=o, e=e, max_length=64 * W)
+        r = ol.oracle_nw(b, x, o, e, threads=8)
+        g = al.greedy_batch(b.reads, b.read_off, b.refs, b.ref_off, want_ops=False)["cost"]
+        for bound in (None, g):           # full matrix (wide kernel) and band from the greedy penalty
+            out = al.nw_batch(b.reads, b.read_off, b.refs, b.ref_off, bound=bound)
+            assert out["penalty"].tolist() == r["penalty"].tolist()
+            assert out["op_off"].tolist() == r["op_off"].tolist()
+            assert out["ops"][:out["n_ops"]].tolist() == r["ops"].tolist()
+        out = al.nw_batch(b.reads, b.read_off, b.refs, b.ref_off, bound=g, want_ops=False)
+        assert out["penalty"].tolist() == r["penalty"].tolist()
+        al.close()
+
+
+def test_gpu_benchmark_counters(pkg, ol):
+    """greedy + NW + counters on the README setup (L=100, e in {0.05, 0.20}) == oracle's counters."""
+    import torch
+    al = pkg.Aligner()
+    for e in (0.05, 0.20):
+        n = 20000
+        cfg = pkg.gen_config(0x47415350, 100, e)
+        d_reads = torch.empty(n * 100 + 16, dtype=torch.uint8, device="cuda")
+        d_refs = torch.empty(al.generate_ref_capacity(cfg, n), dtype=torch.uint8, device="cuda")
+        d_roff = torch.empty(n + 1, dtype=torch.int32, device="cuda")
+        d_foff = torch.empty(n + 1, dtype=torch.int32, device="cuda")
+        al.generate_dev(cfg, 0, n, d_reads, d_roff, d_refs, d_foff)
+        g_cost = torch.empty(n, dtype=torch.int32, device="cuda")
+        g_ops = torch.empty(n * 64, dtype=torch.int16, device="cuda")
+        g_off = torch.empty(n + 1, dtype=torch.int32, device="cuda")
+        al.greedy_batch_dev(d_reads, d_roff, d_refs, d_foff, n, g_cost, g_ops, g_off)
+        nw_pen = torch.empty(n, dtype=torch.int32, device="cuda")
+        nw_ops = torch.empty(n * 128, dtype=torch.int16, device="cuda")
+        nw_off = torch.empty(n + 1, dtype=torch.int32, device="cuda")
+        al.nw_batch_dev(d_reads, d_roff, d_refs, d_foff, n, g_cost, nw_pen, nw_ops, nw_off)
+        counters = torch.zeros(4, dtype=torch.int64, device="cuda")
+        al.metrics_dev(d_reads, d_roff, n, g_cost, g_ops, g_off, nw_pen, nw_ops, nw_off, None, counters)
+        al.metrics_dev(d_reads, d_roff, n, g_cost, g_ops, g_off, nw_pen, nw_ops, nw_off, None, counters)  # accumulates
+        al.synchronize()
+        b = ol.generate(ol.gen_config(0x47415350, 100, e), 0, n)
+        og = ol.oracle_greedy(b, ol.make_params(), threads=8)
+        on = ol.oracle_nw(b, 1, 1, 1, threads=8)
+        exp = ol.oracle_metrics(b, og, on)
+        assert nw_pen.cpu().numpy().tolist() == on["penalty"].tolist()
+        assert counters.cpu().numpy().tolist() == [2 * int(v) for v in exp]
+        acc = exp[2] / exp[0]
+        assert (0.85 < acc < 0.99) if e == 0.05 else (0.30 < acc < 0.70)   # README.md:18,65: 92.975 % / 46.023 %

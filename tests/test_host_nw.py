@@ -1,0 +1,62 @@
+"""CPU tests of the NW / coverage / generator device code (g++ build, tests/host_sim.cpp) against the oracle."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import sim_lib
+
+
+@pytest.mark.parametrize("W", [1, 2, 3])
+def test_nw_logic_matches_oracle(ol, host_sim, W):
+    rng = np.random.default_rng(900 + W)
+    for (x, o, e) in [(1, 1, 1), (2, 3, 1), (4, 6, 2), (1, 0, 1)]:
+        b = ol.random_batch(rng, 400, 1, 64 * W, 0.3, 0.4, 50)
+        r = ol.oracle_nw(b, x, o, e, threads=4)
+        # (a) no bound: full matrix; (b) exact bound = optimum; (c) loose bound = greedy cost
+        g = ol.oracle_greedy(b, ol.make_params(3, x, max(o, 1), e, W))["cost"] if o >= 1 else None
+        for bound in (None, r["penalty"].astype(np.int32), g):
+            if bound is None and o == 0:
+                pass
+            pen, ops, _ = sim_lib.sim_nw(host_sim, b, W, x, o, e, bound)
+            assert pen.tolist() == r["penalty"].tolist(), (W, x, o, e, bound is None)
+            exp = ol.render_all(r["ops"], r["op_off"])
+            assert [ol.render_ops(v) for v in ops] == exp
+    # the narrow/wide split of the kernels gives the same answers
+    b = ol.random_batch(rng, 200, 1, 64 * W, 0.3, 0.4, 50)
+    r = ol.oracle_nw(b, 1, 1, 1)
+    pen, ops, wide = sim_lib.sim_nw(host_sim, b, W, 1, 1, 1, r["penalty"].astype(np.int32) + 9, cap_band=8)
+    assert wide > 0 and pen.tolist() == r["penalty"].tolist()
+    assert [ol.render_ops(v) for v in ops] == ol.render_all(r["ops"], r["op_off"])
+
+
+def test_coverage_logic_matches_oracle(ol, host_sim):
+    host_sim.sim_coverage.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+    rng = np.random.default_rng(31)
+    b = ol.random_batch(rng, 1500, 20, 128, 0.25, 0.3, 50)
+    g = ol.oracle_greedy(b, ol.make_params())
+    nw = ol.oracle_nw(b, 1, 1, 1)
+    exp = ol.oracle_metrics(b, g, nw)
+    cov = 0
+    for i in range(b.n):
+        s1 = b.reads[b.read_off[i]:b.read_off[i + 1]]
+        go = g["ops"][g["op_off"][i]:g["op_off"][i + 1]]
+        no = nw["ops"][nw["op_off"][i]:nw["op_off"][i + 1]]
+        cov += host_sim.sim_coverage(sim_lib._p(s1), len(s1), sim_lib._p(go), len(go), sim_lib._p(no), len(no))
+    assert exp[0] == b.n and exp[1] == b.n
+    assert exp[2] == int((g["cost"] == nw["penalty"]).sum())
+    assert cov == int(exp[3]) and 0 < cov < b.n
+
+
+def test_generator_logic_matches_oracle_twin(ol, host_sim):
+    host_sim.sim_generate_pair.argtypes = [C.c_uint64] + [C.c_int] * 3 + [C.c_uint64] * 5 + [C.c_void_p] * 3
+    for mode, e, prof in [(0, 0.10, None), (1, 0.20, None), (2, 0.0, (0.02452, 0.0468, 0.0553)), (0, 0.15, None)]:
+        cfg = ol.gen_config(77, 100, e, mode=mode, profile=prof)
+        ref = ol.generate(cfg, 500, 300)
+        for i in range(300):
+            rd = np.zeros(128, np.uint8); rf = np.zeros(256, np.uint8); ln = C.c_int(0)
+            n = host_sim.sim_generate_pair(cfg.seed, cfg.length, cfg.mode, cfg.num_errors, cfg.thr_mismatch, cfg.thr_sub,
+                                           cfg.thr_ins, cfg.thr_del, 500 + i, sim_lib._p(rd), sim_lib._p(rf), C.byref(ln))
+            a, f = ref.pair(i)
+            assert n == ln.value == len(f)
+            assert rd[:100].tobytes() == a and rf[:n].tobytes() == f
