@@ -43,7 +43,8 @@ EXPORTS = [
     "gasma_set_stream", "gasma_synchronize", "gasma_launch_count", "gasma_kernel_time_ms", "gasma_last_step_count",
     "gasma_pack2bit_batch", "gasma_pack2bit_batch_dev", "gasma_greedy_batch", "gasma_greedy_batch_dev",
     "gasma_nw_batch", "gasma_nw_batch_dev", "gasma_metrics_dev",
-    "gasma_generate_ref_capacity", "gasma_generate_dev", "gasma_render_cigar",
+    "gasma_generate_ref_capacity", "gasma_generate_dev", "gasma_generate", "gasma_render_cigar",
+    "gasma_benchmark_batch", "gasma_benchmark_batch_dev",
 ]
 
 _lib = None
@@ -86,6 +87,9 @@ def lib():
     L.gasma_generate_ref_capacity.restype = i64
     L.gasma_generate_dev.argtypes = [vp, C.POINTER(GenConfig), C.c_uint64, i64, vp, vp, vp, vp]
     L.gasma_render_cigar.argtypes = [vp, i32, vp, i32]
+    L.gasma_generate.argtypes = [vp, C.POINTER(GenConfig), C.c_uint64, i64, vp, vp, vp, vp]
+    L.gasma_benchmark_batch.argtypes = [vp, vp, vp, vp, vp, i64, vp, vp, vp, vp, vp]
+    L.gasma_benchmark_batch_dev.argtypes = [vp, vp, vp, vp, vp, i64, vp, vp, vp, vp]
     _lib = L
     return L
 
@@ -235,3 +239,33 @@ class Aligner:
 
     def generate_ref_capacity(self, cfg, n):
         return int(self._L.gasma_generate_ref_capacity(C.byref(cfg), n))
+
+    # -- the batched benchmark body (greedy + NW verifier + counters) -------------------------------
+    def benchmark_batch(self, reads, read_off, refs, ref_off, answers=None, counters=None, want_penalties=False):
+        """Host arrays in, the four counters of benchmark::_run_benchmark out (accumulated into `counters`)."""
+        n = len(read_off) - 1
+        if counters is None:
+            counters = np.zeros(4, np.uint64)
+        gc = np.empty(n, np.int32) if want_penalties else None
+        nw = np.empty(n, np.int32) if want_penalties else None
+        ms = (C.c_double * 2)(0.0, 0.0)
+        self._check(self._L.gasma_benchmark_batch(self._ctx, _np_ptr(reads), _np_ptr(read_off), _np_ptr(refs),
+                                                  _np_ptr(ref_off), n, _np_ptr(answers), _np_ptr(counters),
+                                                  _np_ptr(gc), _np_ptr(nw), C.cast(ms, C.c_void_p)))
+        return {"counters": counters, "greedy_cost": gc, "nw_penalty": nw, "device_ms": (ms[0], ms[1])}
+
+    def benchmark_batch_dev(self, d_reads, d_read_off, d_refs, d_ref_off, n, d_counters, d_answers=None,
+                            d_greedy_cost=None, d_nw_penalty=None):
+        self._check(self._L.gasma_benchmark_batch_dev(self._ctx, _dev_ptr(d_reads), _dev_ptr(d_read_off), _dev_ptr(d_refs),
+                                                      _dev_ptr(d_ref_off), n, _dev_ptr(d_answers), _dev_ptr(d_counters),
+                                                      _dev_ptr(d_greedy_cost), _dev_ptr(d_nw_penalty)))
+
+    def generate(self, cfg, first_pair, n):
+        """Synthetic batch generated on the device, returned as host arrays (reads, read_off, refs, ref_off)."""
+        reads = np.empty(n * cfg.length, np.uint8)
+        refs = np.empty(max(1, self.generate_ref_capacity(cfg, n)), np.uint8)
+        roff = np.empty(n + 1, np.uint32)
+        foff = np.empty(n + 1, np.uint32)
+        self._check(self._L.gasma_generate(self._ctx, C.byref(cfg), first_pair, n, _np_ptr(reads), _np_ptr(roff),
+                                           _np_ptr(refs), _np_ptr(foff)))
+        return reads, roff, refs[:int(foff[n])], foff

@@ -149,6 +149,28 @@ int gasma_metrics_dev(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_rea
                       const int32_t* d_nw_penalty, const gasma_cigar_op* d_nw_ops, const uint32_t* d_nw_off,
                       const int32_t* d_answers, uint64_t* d_counters);
 
+/* -- the whole benchmark body, batched ------------------------------------------------------------ */
+/* Replaces benchmark::run's loop over _run_benchmark (benchmark_utils.h:373-385, :231-259) for n pairs:
+ * greedy (reset/run/get_cost/get_CIGAR), NW verifier (banded by the greedy penalty, exact), and the four
+ * counters, entirely on the device; only the counters (and the optional per-pair penalties) come back.
+ *   counters[0..3] += total, nw_correct, greedy_correct, greedy_coverage   (ACCUMULATES, like the class members)
+ *   answers     optional n x int32 (read_answer_file, :358-368); INT32_MIN or NULL = use the NW penalty
+ *   greedy_cost, nw_penalty   optional n x int32 outputs
+ *   device_ms   optional: [0] += greedy kernels, [1] += NW kernels (CUDA-event time, the report's [Time] rows)
+ * The LEAP column of the report (LV_BAG) is a comparator, not part of this path, and is not computed. */
+int gasma_benchmark_batch(gasma_ctx* ctx,
+                          const char* reads, const uint32_t* read_off,
+                          const char* refs, const uint32_t* ref_off, int64_t n_pairs,
+                          const int32_t* answers, uint64_t counters[4],
+                          int32_t* greedy_cost, int32_t* nw_penalty, double device_ms[2]);
+/* Same with the batch resident in HBM; d_counters = 4 x uint64 in device memory (accumulated; all-reduce it
+ * across GPUs at the end of a run).  d_greedy_cost / d_nw_penalty are optional. */
+int gasma_benchmark_batch_dev(gasma_ctx* ctx,
+                              const char* d_reads, const uint32_t* d_read_off,
+                              const char* d_refs, const uint32_t* d_ref_off, int64_t n_pairs,
+                              const int32_t* d_answers, uint64_t* d_counters,
+                              int32_t* d_greedy_cost, int32_t* d_nw_penalty);
+
 /* -- synthetic inputs ---------------------------------------------------------------------------- */
 /* Restates Dataset (benchmark_dataset.h:100-186) with a counter RNG keyed by (seed, pair index) so
  * every shard regenerates pair i identically.  mode 0: exactly num_errors edits; 1: uniform in
@@ -163,6 +185,11 @@ int64_t gasma_generate_ref_capacity(const gasma_gen_config* cfg, int64_t n_pairs
 /* Writes reads (n*length bytes), read_off, refs, ref_off (n+1 each) for pairs first..first+n. */
 int gasma_generate_dev(gasma_ctx* ctx, const gasma_gen_config* cfg, uint64_t first_pair, int64_t n_pairs,
                        char* d_reads, uint32_t* d_read_off, char* d_refs, uint32_t* d_ref_off);
+
+/* Host-pointer variant: generates on the device and copies the batch out (reads: n*length bytes, refs:
+ * gasma_generate_ref_capacity bytes, offsets n+1 each). */
+int gasma_generate(gasma_ctx* ctx, const gasma_gen_config* cfg, uint64_t first_pair, int64_t n_pairs,
+                   char* reads, uint32_t* read_off, char* refs, uint32_t* ref_off);
 
 /* -- host helpers -------------------------------------------------------------------------------- */
 /* get_CIGAR() text from encoded ops: std::to_string(len) + letter per op (hurdle_matrix.h:241-249).

@@ -128,6 +128,11 @@ class Batch:
         return Batch(self.reads[ro[0]:ro[-1]], ro - ro[0], self.refs[fo[0]:fo[-1]], fo - fo[0])
 
 
+def batch_from_strings(reads, refs):
+    """Batch from two lists of str (e.g. a parsed '>read / <ref' file)."""
+    return Batch.from_pairs([(r.encode(), f.encode()) for r, f in zip(reads, refs)])
+
+
 def make_params(k=3, x=1, o=1, e=1, W=2, global_=1, probs=DEFAULT_PROBS):
     return GoParams(k, x, o, e, global_, W, probs[0], probs[1], probs[2])
 

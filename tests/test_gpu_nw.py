@@ -55,3 +55,29 @@ def test_gpu_benchmark_counters(pkg, ol):
         assert counters.cpu().numpy().tolist() == [2 * int(v) for v in exp]
         acc = exp[2] / exp[0]
         assert (0.85 < acc < 0.99) if e == 0.05 else (0.30 < acc < 0.70)   # README.md:18,65: 92.975 % / 46.023 %
+
+
+def test_gpu_benchmark_batch_host_call(pkg, ol):
+    """gasma_benchmark_batch (host pointers): the whole _run_benchmark body in one call == oracle counters,
+    with and without an answers file, accumulating like the class members do."""
+    al = pkg.Aligner()
+    cfg = pkg.gen_config(0x47415351, 100, 0.15)
+    reads, roff, refs, foff = al.generate(cfg, 1000, 30000)
+    b = ol.Batch(reads, roff, refs, foff)
+    tw = ol.generate(ol.gen_config(0x47415351, 100, 0.15), 1000, 30000)
+    assert b.reads.tolist() == tw.reads.tolist() and b.refs.tolist() == tw.refs.tolist()   # host generate == CPU twin
+    og = ol.oracle_greedy(b, ol.make_params(), threads=8)
+    on = ol.oracle_nw(b, 1, 1, 1, threads=8)
+    exp = [int(v) for v in ol.oracle_metrics(b, og, on)]
+    out = al.benchmark_batch(b.reads, b.read_off, b.refs, b.ref_off, want_penalties=True)
+    assert out["counters"].tolist() == exp
+    assert out["greedy_cost"].tolist() == og["cost"].tolist()
+    assert out["nw_penalty"].tolist() == on["penalty"].tolist()
+    assert out["device_ms"][0] > 0 and out["device_ms"][1] > 0
+    # answers: half the pairs get a wrong "optimal" penalty, the rest INT32_MIN (= use NW)
+    ans = np.full(b.n, np.iinfo(np.int32).min, np.int32)
+    ans[::2] = on["penalty"][::2] + 1
+    exp2 = [int(v) for v in ol.oracle_metrics(b, og, on, ans)]
+    out2 = al.benchmark_batch(b.reads, b.read_off, b.refs, b.ref_off, answers=ans, counters=out["counters"])
+    assert out2["counters"].tolist() == [a + c for a, c in zip(exp, exp2)]
+    al.close()
