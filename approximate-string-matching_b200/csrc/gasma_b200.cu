@@ -6,6 +6,7 @@
 #include <math.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <string>
@@ -32,6 +33,8 @@ struct gasma_ctx {
     KParams kp;
     int W = 2;
     int device = 0;
+    int sm_count = 148;
+    int refill_threshold = 8;   // idle threads in a warp that trigger a refill from the pool (greedy kernel)
     cudaStream_t stream = nullptr;      // stream all work goes to
     cudaStream_t own_stream = nullptr;  // created by us
     int64_t launches = 0;
@@ -108,42 +111,50 @@ void derive(gasma_ctx* c) {
 
 constexpr size_t kMaxSmem = 227 * 1024;
 
+// warps per CTA of the greedy kernel: 4 when the lanes of 128 alignments fit shared memory, else 1
 template <int W>
-int tile_threads_for(int k) {
-    if (greedy_smem_bytes<W>(128, k) <= kMaxSmem) return 128;
-    if (greedy_smem_bytes<W>(32, k) <= kMaxSmem) return 32;
+int greedy_warps_for(int k) {
+    if (greedy_smem_bytes<W>(4, k) <= kMaxSmem) return 4;
+    if (greedy_smem_bytes<W>(1, k) <= kMaxSmem) return 1;
     return 0;
 }
 
-template <int W, int T>
+template <int W, int WARPS>
 int launch_greedy_t(gasma_ctx* ctx, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, const uint32_t* foff,
-                    int64_t n, int32_t* cost, uint16_t* stage, int stride, uint32_t* nops, uint32_t* tile_sums,
+                    int64_t n, int32_t* cost, uint16_t* stage, int stride, uint32_t* nops, uint32_t* chunk_counter,
                     uint32_t* status, unsigned long long* steps) {
-    const size_t smem = greedy_smem_bytes<W>(T, ctx->kp.k);
-    auto kern = greedy_kernel<W, T>;
+    const size_t smem = greedy_smem_bytes<W>(WARPS, ctx->kp.k);
+    auto kern = greedy_kernel<W, WARPS>;
     CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const unsigned grid = (unsigned)((n + T - 1) / T);
-    kern<<<grid, T, smem, ctx->stream>>>(ctx->kp, reads, roff, refs, foff, (long long)n, cost, stage, stride, nops,
-                                         tile_sums, status, steps);
+    int per_sm = 0;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 32 * WARPS, smem));
+    if (per_sm < 1) return fail(ctx, GASMA_E_CUDA, "greedy kernel does not fit an SM");
+    // persistent grid: every resident warp pulls 32-pair chunks until the batch is exhausted
+    const int64_t chunks = (n + kPool - 1) / kPool;
+    int64_t grid = (int64_t)ctx->sm_count * per_sm;
+    if (grid * WARPS > chunks) grid = (chunks + WARPS - 1) / WARPS;
+    CU(cudaMemsetAsync(chunk_counter, 0, 4, ctx->stream));
+    kern<<<(unsigned)grid, 32 * WARPS, smem, ctx->stream>>>(ctx->kp, reads, roff, refs, foff, (long long)n, cost, stage, stride,
+                                                          nops, chunk_counter, ctx->refill_threshold, status, steps);
     CU(cudaGetLastError());
     ctx->launches++;
     return GASMA_OK;
 }
 
 template <int W>
-int launch_greedy_w(gasma_ctx* ctx, int T, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs,
+int launch_greedy_w(gasma_ctx* ctx, int warps, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs,
                     const uint32_t* foff, int64_t n, int32_t* cost, uint16_t* stage, int stride, uint32_t* nops,
-                    uint32_t* tile_sums, uint32_t* status, unsigned long long* steps) {
-    if (T == 128) return launch_greedy_t<W, 128>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, tile_sums, status, steps);
-    return launch_greedy_t<W, 32>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, tile_sums, status, steps);
+                    uint32_t* chunk_counter, uint32_t* status, unsigned long long* steps) {
+    if (warps == 4) return launch_greedy_t<W, 4>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, chunk_counter, status, steps);
+    return launch_greedy_t<W, 1>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, chunk_counter, status, steps);
 }
 
-int greedy_tile_threads(const gasma_ctx* c) {
+int greedy_tile_threads(const gasma_ctx* c) {   // 0 = configuration does not fit
     switch (c->W) {
-        case 1: return tile_threads_for<1>(c->kp.k);
-        case 2: return tile_threads_for<2>(c->kp.k);
-        case 3: return tile_threads_for<3>(c->kp.k);
-        default: return tile_threads_for<4>(c->kp.k);
+        case 1: return 32 * greedy_warps_for<1>(c->kp.k);
+        case 2: return 32 * greedy_warps_for<2>(c->kp.k);
+        case 3: return 32 * greedy_warps_for<3>(c->kp.k);
+        default: return 32 * greedy_warps_for<4>(c->kp.k);
     }
 }
 
@@ -189,6 +200,11 @@ int gasma_create(const gasma_params* params, int device, gasma_ctx** out) {
     gasma_ctx* c = new gasma_ctx();
     c->params = *params;
     c->device = device;
+    c->sm_count = prop.multiProcessorCount;
+    if (const char* env = getenv("GASMA_REFILL_THRESHOLD")) {   // tuning knob; results do not depend on it
+        const int v = atoi(env);
+        if (v >= 1 && v <= 32) c->refill_threshold = v;
+    }
     derive(c);
     if (greedy_tile_threads(c) == 0) {
         delete c;
@@ -330,7 +346,8 @@ int greedy_dev_impl(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_read_
         if (d_op_off) CU(cudaMemsetAsync(d_op_off, 0, 4, ctx->stream));
         return GASMA_OK;
     }
-    const int T = greedy_tile_threads(ctx);
+    const int warps = greedy_tile_threads(ctx) / 32;
+    constexpr int T = 128;   // tile of the CSR scan / compaction kernels
     const int64_t ntiles = (n + T - 1) / T;
     const int stride = 2 * ctx->params.max_length + 8;
     uint32_t* misc = (uint32_t*)ctx->misc.p;
@@ -344,33 +361,30 @@ int greedy_dev_impl(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_read_
     }
     uint16_t* stage = want_ops ? (uint16_t*)ctx->ops_stage.p : nullptr;
     uint32_t* nops = want_ops ? (uint32_t*)ctx->nops.p : nullptr;
-    uint32_t* tsum = want_ops ? (uint32_t*)ctx->tile_sums.p : nullptr;
     const uint8_t* r = (const uint8_t*)d_reads;
     const uint8_t* f = (const uint8_t*)d_refs;
     unsigned long long* steps = (unsigned long long*)(misc + 2);
+    uint32_t* chunk_counter = misc + 6;
     cudaEvent_t* evp = ctx->ev[0][ctx->ev_count[0] % gasma_ctx::kRing];
     CU(cudaEventRecord(evp[0], ctx->stream));
     switch (ctx->W) {
-        case 1: rc = launch_greedy_w<1>(ctx, T, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, tsum, misc, steps); break;
-        case 2: rc = launch_greedy_w<2>(ctx, T, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, tsum, misc, steps); break;
-        case 3: rc = launch_greedy_w<3>(ctx, T, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, tsum, misc, steps); break;
-        default: rc = launch_greedy_w<4>(ctx, T, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, tsum, misc, steps); break;
+        case 1: rc = launch_greedy_w<1>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, chunk_counter, misc, steps); break;
+        case 2: rc = launch_greedy_w<2>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, chunk_counter, misc, steps); break;
+        case 3: rc = launch_greedy_w<3>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, chunk_counter, misc, steps); break;
+        default: rc = launch_greedy_w<4>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, chunk_counter, misc, steps); break;
     }
     if (rc) return rc;
     CU(cudaEventRecord(evp[1], ctx->stream));
     ctx->ev_count[0]++;
     if (want_ops) {
-        scan_tiles_kernel<<<1, 1024, 0, ctx->stream>>>(tsum, (uint32_t*)ctx->tile_bases.p, (int)ntiles, misc + 1);
+        tile_sums_kernel<T><<<(unsigned)ntiles, T, 0, ctx->stream>>>(nops, (long long)n, (uint32_t*)ctx->tile_sums.p);
         CU(cudaGetLastError());
-        ctx->launches++;
-        if (T == 128)
-            compact_ops_kernel<128><<<(unsigned)ntiles, 128, 0, ctx->stream>>>(stage, stride, nops, (uint32_t*)ctx->tile_bases.p,
-                                                                             (long long)n, d_ops, (long long)ops_cap, d_op_off, 0);
-        else
-            compact_ops_kernel<32><<<(unsigned)ntiles, 32, 0, ctx->stream>>>(stage, stride, nops, (uint32_t*)ctx->tile_bases.p,
-                                                                           (long long)n, d_ops, (long long)ops_cap, d_op_off, 0);
+        scan_tiles_kernel<<<1, 1024, 0, ctx->stream>>>((uint32_t*)ctx->tile_sums.p, (uint32_t*)ctx->tile_bases.p, (int)ntiles, misc + 1);
         CU(cudaGetLastError());
-        ctx->launches++;
+        compact_ops_kernel<T><<<(unsigned)ntiles, T, 0, ctx->stream>>>(stage, stride, nops, (uint32_t*)ctx->tile_bases.p,
+                                                                     (long long)n, d_ops, (long long)ops_cap, d_op_off, 0);
+        CU(cudaGetLastError());
+        ctx->launches += 3;
     }
     return GASMA_OK;
 }

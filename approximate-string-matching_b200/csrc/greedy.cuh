@@ -23,30 +23,66 @@ GASMA_HD int st_len(uint64_t s) { return (int)((uint32_t)s >> 16); }
 GASMA_HD int st_nsw(uint64_t s) { return (int)((uint32_t)(s >> 32) & 0xFFFFu); }
 GASMA_HD int st_nh(uint64_t s) { return (int)((uint32_t)(s >> 32) >> 16); }
 
-// index of the first bit >= s that is set in (v ^ inv); -1 if none   (first_one/first_zero, utils.h:168-191)
+// ---------------------------------------------------------------------------------------------
+// Lane storage.  A lane is kept as NW = 2W 32-bit words so that a scan or a ranged popcount touches only
+// the one to three words it needs (a dynamic word index is free in shared memory, it is not in registers).
+// Element (lane index li, kind, word w) of this thread lives at lanes[((li*2+kind)*NW + w) * stride]:
+// consecutive threads are consecutive 4-byte words, so a warp never bank-conflicts whatever w each thread
+// picks.  kind 0 = orig, 1 = flip.  `stride` is the number of threads sharing the array (1 in the host harness).
+// ---------------------------------------------------------------------------------------------
+struct LaneStore {
+    uint32_t* lanes;
+    uint64_t* state;  // [li][stride]
+    int stride;
+};
+
+GASMA_HD int ctz32(uint32_t x) {  // x != 0
+#if defined(__CUDA_ARCH__)
+    return __ffs((int)x) - 1;
+#else
+    return __builtin_ctz(x);
+#endif
+}
+GASMA_HD int popc32(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+    return __popc(x);
+#else
+    return __builtin_popcount(x);
+#endif
+}
+
+// index of the first bit >= s that is set in (lane ^ inv); -1 if none   (first_one/first_zero, utils.h:168-191).
+// `base` points at word 0 of the lane for this thread.
 template <int W>
-GASMA_HD int scan_from(const uint64_t v[W], uint64_t inv, int s) {
-    int res = -1;
-#pragma unroll
-    for (int j = W - 1; j >= 0; --j) {
-        uint64_t t = (v[j] ^ inv) & ones_from(s, j);
-        if (t) res = 64 * j + ctz64(t);
+GASMA_HD int scan_from(const uint32_t* base, int stride, uint32_t inv, int s) {
+    constexpr int NW = 2 * W;
+    int w = s >> 5;
+    if (w >= NW) return -1;
+    uint32_t t = (base[w * stride] ^ inv) & (0xFFFFFFFFu << (s & 31));
+    while (t == 0u) {
+        if (++w >= NW) return -1;
+        t = base[w * stride] ^ inv;
     }
-    return res;
+    return 32 * w + ctz32(t);
 }
 
 // pop_count_between(from,to), utils.h:263-270 = shift_left(from).shift_right(from+BITS-to).pop_count():
-// bits [from, to) clipped to the vector, 0 if from >= to, 0 if the second shift would be negative.
+// bits [from, to) clipped to the vector, 0 if from >= to, 0 if the second shift would be negative.  from >= 0.
 template <int W>
-GASMA_HD int pcb(const uint64_t v[W], int from, int to) {
-    if (to > 64 * W + from) return 0;
-    int c = 0;
-#pragma unroll
-    for (int j = 0; j < W; ++j) c += popc64(v[j] & ones_from(from, j) & ~ones_from(to, j));
+GASMA_HD int pcb(const uint32_t* base, int stride, int from, int to) {
+    constexpr int BITS = 64 * W;
+    if (to > BITS + from) return 0;
+    to = imin(to, BITS);
+    if (from >= to) return 0;
+    const int w0 = from >> 5, w1 = (to - 1) >> 5;
+    const uint32_t mlo = 0xFFFFFFFFu << (from & 31), mhi = 0xFFFFFFFFu >> (31 - ((to - 1) & 31));
+    if (w0 == w1) return popc32(base[w0 * stride] & mlo & mhi);
+    int c = popc32(base[w0 * stride] & mlo) + popc32(base[w1 * stride] & mhi);
+    for (int w = w0 + 1; w < w1; ++w) c += popc32(base[w * stride]);
     return c;
 }
 
-// v >> s (towards bit 0), zero fill, for a small constant-ish shift 0 <= s < 64   (shift_left, utils.h:143)
+// v >> s (towards bit 0), zero fill, for a small shift 0 <= s < 64   (shift_left, utils.h:143)
 template <int W>
 GASMA_HD void shift_down_small(const uint64_t v[W], int s, uint64_t out[W]) {
 #pragma unroll
@@ -81,23 +117,17 @@ GASMA_HD void build_lane(const uint64_t A0[W], const uint64_t A1[W], const uint6
     }
 }
 
-// Strided per-thread view of the lane storage: element (lane index li, kind, word w) of this thread.
-// kind 0 = orig, 1 = flip.  `stride` is the number of threads sharing the array (1 in the host harness).
-struct LaneStore {
-    uint64_t* lanes;  // [(li*2+kind)*W + w][stride]
-    uint64_t* state;  // [li][stride]
-    int stride;
-};
+template <int W>
+GASMA_HD const uint32_t* lane_base(const LaneStore& S, int li, int kind) { return S.lanes + (size_t)((li * 2 + kind) * 2 * W) * S.stride; }
 
 template <int W>
-GASMA_HD void lane_load(const LaneStore& S, int li, int kind, uint64_t v[W]) {
-#pragma unroll
-    for (int j = 0; j < W; ++j) v[j] = S.lanes[((li * 2 + kind) * W + j) * S.stride];
-}
-template <int W>
 GASMA_HD void lane_store(const LaneStore& S, int li, int kind, const uint64_t v[W]) {
+    uint32_t* b = S.lanes + (size_t)((li * 2 + kind) * 2 * W) * S.stride;
 #pragma unroll
-    for (int j = 0; j < W; ++j) S.lanes[((li * 2 + kind) * W + j) * S.stride] = v[j];
+    for (int j = 0; j < W; ++j) {
+        b[(2 * j) * S.stride] = (uint32_t)v[j];
+        b[(2 * j + 1) * S.stride] = (uint32_t)(v[j] >> 32);
+    }
 }
 
 struct OpSink {
@@ -116,16 +146,20 @@ struct OpSink {
     }
 };
 
-// The whole alignment of one pair.  Returns status bits (0 = fine).
-template <int W>
-GASMA_HD uint32_t greedy_pair(const KParams& P, const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W],
-                              const uint64_t B1[W], int m, int n, const LaneStore& S, OpSink& sink, int& cost_out,
-                              int& steps_out) {
-    constexpr int BITS = 64 * W;
-    const int k = P.k, x = P.x, o = P.o, e = P.e;
-    const bool GLOBAL = P.global != 0;
+// Running position of one alignment (registers).
+struct PairState {
+    int m, n;        // clamped lengths
+    int cl, cc;      // current lane / column
+    int cost, steps;
+    bool first;      // is_first_step (hurdle_matrix.h:572)
+};
 
-    // reset(): highways::reset (:106-119) + _construct_hurdles (:441-455)
+// reset(): highways::reset (:106-119) + _construct_hurdles (:441-455)
+template <int W>
+GASMA_HD void pair_init(const KParams& P, const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W],
+                        const uint64_t B1[W], int m, int n, const LaneStore& S, PairState& ps) {
+    constexpr int BITS = 64 * W;
+    const int k = P.k;
     for (int l = -k; l <= k; ++l) {
         uint64_t og[W], fl[W];
         build_lane<W>(A0, A1, B0, B1, l, og, fl);
@@ -133,109 +167,123 @@ GASMA_HD uint32_t greedy_pair(const KParams& P, const uint64_t A0[W], const uint
         lane_store<W>(S, l + k, 1, fl);
         S.state[(l + k) * S.stride] = st_pack(-1, 0, BITS, BITS);
     }
+    ps.m = m; ps.n = n; ps.cl = 0; ps.cc = 0; ps.cost = 0; ps.steps = 0; ps.first = true;
+}
+
+// One _step() (hurdle_matrix.h:407-434) including its _update_highway_list and _choose_best_highway.
+// Returns true when the traversal is over (the caller then runs pair_finish).
+template <int W>
+GASMA_HD bool pair_step(const KParams& P, const LaneStore& S, PairState& ps, OpSink& sink, uint32_t& status) {
+    constexpr int BITS = 64 * W;
+    const int k = P.k, x = P.x, o = P.o, e = P.e;
+    const bool GLOBAL = P.global != 0;
+    const int m = ps.m, n = ps.n, cl = ps.cl, cc = ps.cc;
+    const bool leap_cost = GLOBAL || !ps.first;
     const int dl = n - m;
-    int cl = 0, cc = 0, cost = 0, steps = 0;
-    bool first = true;
+    if (++ps.steps > 4 * BITS + 16) { status |= kStatusSteps; return true; }
+
+    // ---- _update_highway_list, loops 1 and 2 fused: both arg-max candidates are tracked, the one that
+    // applies is picked once `reach` is known (hurdle_matrix.h:291-352) ----
+    bool reach = false;
+    double bestH_s = 0.0; int bestLeap_s = 0, bl_s = 0; uint64_t st_s = 0; bool have_s = false;
+    int bestH_r = 0, bestLeap_r = 0, bl_r = 0; uint64_t st_r = 0; bool have_r = false;
+    for (int l = -k; l <= k; ++l) {
+        const int li = l + k;
+        const int sc = cc + sfc(cl, l);
+        const int de = lane_destination(m, n, l);
+        uint64_t st = S.state[li * S.stride];
+        int sp = st_sp(st), len = st_len(st), nsw = st_nsw(st);
+        if (sp < sc) {  // cache miss: look up the closest highway of this lane (:293-310)
+            nsw = iabs(l - cl);
+            const uint32_t* f = lane_base<W>(S, li, 1);
+            const int p0 = scan_from<W>(f, S.stride, ~0u, sc);   // first zero at/after sc
+            const int pos0 = p0 >= 0 ? p0 : imax(sc, BITS);      // zero fill beyond the vector
+            const int p1 = scan_from<W>(f, S.stride, 0u, pos0);  // next hurdle
+            sp = pos0;
+            len = p1 >= 0 ? p1 - pos0 : BITS;                    // first_one of an empty vector = BITS
+            if (sp + len > de) { len = imax(0, de - sp); reach = true; }
+        }
+        const int sw = leap_cost ? slp(cl, l, o, e) : 0;
+        const int nh = pcb<W>(lane_base<W>(S, li, 0), S.stride, sc, sp + len);
+        const int hc = x * nh;
+        st = st_pack(sp, len, nsw, nh);
+        S.state[li * S.stride] = st;
+        // significance heuristic (:328-332): ((ms*len) + (mms*nh)) + (ids*nsw), each op rounded
+        const double h = dadd(dadd(dmul(P.ms, (double)len), dmul(P.mms, (double)nh)), dmul(P.ids, (double)nsw));
+        const int lh = -sw;
+        if (!have_s || h > bestH_s || (h == bestH_s && lh > bestLeap_s)) {
+            have_s = true; bestH_s = h; bestLeap_s = lh; bl_s = l; st_s = st;
+        }
+        // destination heuristic (:334-342), integer valued
+        const int fsw = GLOBAL ? slp(l, dl, o, e) : 0;
+        const int hr = -sw - hc - fsw - x * (de - sp - len);
+        const int lhr = -sw - fsw;
+        if (!have_r || hr > bestH_r || (hr == bestH_r && lhr > bestLeap_r)) {
+            have_r = true; bestH_r = hr; bestLeap_r = lhr; bl_r = l; st_r = st;
+        }
+    }
+    const int bl = reach ? bl_r : bl_s;
+    const uint64_t st_bl = reach ? st_r : st_s;
+    if (st_len(st_bl) <= 0) return true;  // no usable highway (:358-360, :570)
+
+    // ---- _choose_best_highway (:368-401) ----
+    const int spb = st_sp(st_bl);
+    const int swb = leap_cost ? slp(cl, bl, o, e) : 0;
+    int sT = x * st_nh(st_bl) + swb, sI = sT, b = bl;
+    uint64_t st_b = st_bl;
+    const uint32_t* ob = lane_base<W>(S, bl + k, 0);
+    for (int l = -k; l <= k; ++l) {
+        if (l == bl) continue;
+        const uint64_t st = S.state[(l + k) * S.stride];
+        const int sp = st_sp(st), s_l = sfc(l, bl);
+        if (sp + s_l > spb) continue;
+        const int end = sp + st_len(st);
+        const int swl = leap_cost ? slp(cl, l, o, e) : 0;
+        const int ic = swl + st_nh(st);  // == switch_cost + pop_count_between(cc+sfc(cl,l), end), no *x (:388)
+        const int hp = x * pcb<W>(ob, S.stride, s_l + end, spb);
+        const int tc = ic + slp(l, bl, o, e) + imax(0, hp);
+        if (tc <= sT && ic <= sI) { sT = tc; sI = ic; b = l; st_b = st; }
+    }
+    // ---- _step (:412-433) ----
+    const int swc = leap_cost ? slp(cl, b, o, e) : 0;
+    ps.cost += swc + x * st_nh(st_b);
+    const int endb = st_sp(st_b) + st_len(st_b);
+    sink.update(b, cl, endb - (cc + sfc(cl, b)));
+    ps.cl = b;
+    ps.cc = endb;
+    ps.first = false;
+    return endb >= lane_destination(m, n, b);
+}
+
+// run() fix-up (hurdle_matrix.h:575-590).  A destination lane outside the band keeps the state of a fresh
+// object: lane value 1 (utils.h:57-59) and destination -|lane| (hurdle_matrix.h:79-92 with m=n=0).
+template <int W>
+GASMA_HD void pair_finish(const KParams& P, const LaneStore& S, PairState& ps, OpSink& sink) {
+    const int k = P.k, x = P.x;
+    const int dl = ps.n - ps.m, cl = ps.cl, cc = ps.cc;
+    const bool in_band = iabs(dl) <= k;
+    const int dc = in_band ? lane_destination(ps.m, ps.n, dl) : -iabs(dl);
+    if (cl != dl || cc < dc) {
+        int d = 0;
+        if (in_band) d = pcb<W>(lane_base<W>(S, dl + k, 0), S.stride, cc + sfc(cl, dl), dc);
+        // out of band: dc < 0 <= from, so pop_count_between of the default value 1 is 0 as well
+        ps.cost += (P.global ? slp(cl, dl, P.o, P.e) : 0) + imax(0, x * d);
+        sink.update(dl, cl, d);
+    }
+}
+
+// The whole alignment of one pair (host harness, and kernels that do not interleave pairs).  Returns status bits.
+template <int W>
+GASMA_HD uint32_t greedy_pair(const KParams& P, const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W],
+                              const uint64_t B1[W], int m, int n, const LaneStore& S, OpSink& sink, int& cost_out,
+                              int& steps_out) {
+    PairState ps;
     uint32_t status = 0;
-
-    for (;;) {
-        if (++steps > 4 * BITS + 16) { status |= kStatusSteps; break; }
-        // ---- _update_highway_list, loops 1 and 2 fused: both arg-max candidates are tracked, the
-        // one that applies is picked once `reach` is known (hurdle_matrix.h:291-352) ----
-        bool reach = false;
-        double bestH_s = 0.0; int bestLeap_s = 0, bl_s = 0; uint64_t st_s = 0; bool have_s = false;
-        int bestH_r = 0, bestLeap_r = 0, bl_r = 0; uint64_t st_r = 0; bool have_r = false;
-        for (int l = -k; l <= k; ++l) {
-            const int li = l + k;
-            const int sc = cc + sfc(cl, l);
-            const int de = lane_destination(m, n, l);
-            uint64_t st = S.state[li * S.stride];
-            int sp = st_sp(st), len = st_len(st), nsw = st_nsw(st);
-            if (sp < sc) {  // cache miss: look up the closest highway of this lane (:293-310)
-                nsw = iabs(l - cl);
-                uint64_t f[W];
-                lane_load<W>(S, li, 1, f);
-                int p0 = scan_from<W>(f, ~0ull, sc);             // first zero at/after sc
-                int pos0 = p0 >= 0 ? p0 : imax(sc, BITS);        // zero fill beyond the vector
-                int p1 = scan_from<W>(f, 0ull, pos0);            // next hurdle
-                int nx = p1 >= 0 ? p1 - pos0 : BITS;             // first_one of an empty vector = BITS
-                sp = pos0;
-                len = nx;
-                if (sp + len > de) { len = imax(0, de - sp); reach = true; }
-            }
-            const int sw = (GLOBAL || !first) ? slp(cl, l, o, e) : 0;
-            uint64_t og[W];
-            lane_load<W>(S, li, 0, og);
-            const int nh = pcb<W>(og, sc, sp + len);
-            const int hc = x * nh;
-            st = st_pack(sp, len, nsw, nh);
-            S.state[li * S.stride] = st;
-            // significance heuristic (:328-332): ((ms*len) + (mms*nh)) + (ids*nsw), each op rounded
-            const double h = dadd(dadd(dmul(P.ms, (double)len), dmul(P.mms, (double)nh)), dmul(P.ids, (double)nsw));
-            const int lh = -sw;
-            if (!have_s || h > bestH_s || (h == bestH_s && lh > bestLeap_s)) {
-                have_s = true; bestH_s = h; bestLeap_s = lh; bl_s = l; st_s = st;
-            }
-            // destination heuristic (:334-342), integer valued
-            const int fsw = GLOBAL ? slp(l, dl, o, e) : 0;
-            const int hr = -sw - hc - fsw - x * (de - sp - len);
-            const int lhr = -sw - fsw;
-            if (!have_r || hr > bestH_r || (hr == bestH_r && lhr > bestLeap_r)) {
-                have_r = true; bestH_r = hr; bestLeap_r = lhr; bl_r = l; st_r = st;
-            }
-        }
-        const int bl = reach ? bl_r : bl_s;
-        const uint64_t st_bl = reach ? st_r : st_s;
-        if (st_len(st_bl) <= 0) break;  // no usable highway (:358-360)
-
-        // ---- _choose_best_highway (:368-401) ----
-        const int spb = st_sp(st_bl);
-        const int swb = (GLOBAL || !first) ? slp(cl, bl, o, e) : 0;
-        int sT = x * st_nh(st_bl) + swb, sI = sT, b = bl;
-        uint64_t st_b = st_bl;
-        uint64_t ob[W];
-        lane_load<W>(S, bl + k, 0, ob);
-        for (int l = -k; l <= k; ++l) {
-            if (l == bl) continue;
-            const uint64_t st = S.state[(l + k) * S.stride];
-            const int sp = st_sp(st), s_l = sfc(l, bl);
-            if (sp + s_l > spb) continue;
-            const int end = sp + st_len(st);
-            const int swl = (GLOBAL || !first) ? slp(cl, l, o, e) : 0;
-            const int ic = swl + st_nh(st);  // == switch_cost + pop_count_between(cc+sfc(cl,l), end), no *x (:388)
-            const int hp = x * pcb<W>(ob, s_l + end, spb);
-            const int tc = ic + slp(l, bl, o, e) + imax(0, hp);
-            if (tc <= sT && ic <= sI) { sT = tc; sI = ic; b = l; st_b = st; }
-        }
-        // ---- _step (:412-433) ----
-        const int swc = (GLOBAL || !first) ? slp(cl, b, o, e) : 0;
-        cost += swc + x * st_nh(st_b);
-        const int endb = st_sp(st_b) + st_len(st_b);
-        sink.update(b, cl, endb - (cc + sfc(cl, b)));
-        cl = b;
-        cc = endb;
-        first = false;
-        if (cc >= lane_destination(m, n, cl)) break;
-    }
-    // ---- run() fix-up (:575-590).  A destination lane outside the band keeps the state of a fresh
-    // object: lane value 1 (utils.h:57-59) and destination -|lane| (hurdle_matrix.h:79-92 with m=n=0) ----
-    {
-        const bool in_band = iabs(dl) <= k;
-        const int dc = in_band ? lane_destination(m, n, dl) : -iabs(dl);
-        if (cl != dl || cc < dc) {
-            uint64_t od[W];
-            if (in_band) lane_load<W>(S, dl + k, 0, od);
-            else {
-#pragma unroll
-                for (int j = 0; j < W; ++j) od[j] = j ? 0ull : 1ull;
-            }
-            const int d = pcb<W>(od, cc + sfc(cl, dl), dc);
-            cost += (GLOBAL ? slp(cl, dl, o, e) : 0) + imax(0, x * d);
-            sink.update(dl, cl, d);
-        }
-    }
-    cost_out = cost;
-    steps_out = steps;
+    pair_init<W>(P, A0, A1, B0, B1, m, n, S, ps);
+    while (!pair_step<W>(P, S, ps, sink, status)) {}
+    pair_finish<W>(P, S, ps, sink);
+    cost_out = ps.cost;
+    steps_out = ps.steps;
     return status;
 }
 

@@ -51,98 +51,149 @@ __host__ __device__ constexpr int stream_chunks(int tile) { return tile * 4 * W 
 template <int W>
 __host__ __device__ constexpr int stream_elems(int tile) { return ((stream_chunks<W>(tile) + 2 * (2 * W + 2) + 7) / 8) * 8; }
 
+// ---------------------------------------------------------------------------------------------
+// K2+K3: persistent warps, one alignment per thread, finished threads refilled from a per-warp pool.
+//
+// The number of _step() calls differs from pair to pair (1 .. >10), so a warp that runs 32 pairs to
+// completion idles most of its lanes while the slowest pair finishes (r01a profile: 16.7 of 32 threads active).
+// Here every warp owns a POOL of 32 consecutive pairs staged as 2-bit streams in its slice of shared memory;
+// a thread whose pair is done takes the next pair of the pool, and when the pool is empty the whole warp
+// (all 32 lanes, fully converged) claims the next 32-pair chunk from a global counter and stages it with
+// coalesced 16-byte loads.  Results are written by pair index, so they do not depend on the schedule.
+// ---------------------------------------------------------------------------------------------
+constexpr int kPool = 32;   // pairs per chunk = per warp pool
+
 template <int W>
-__host__ __device__ constexpr size_t greedy_smem_bytes(int tile, int k) {
-    return (size_t)(2 * k + 1) * (2 * W + 1) * 8 * tile   // lanes + state
-           + 4 * (size_t)stream_elems<W>(tile) * 2        // read/ref x plane0/plane1 streams
-           + 2 * (size_t)(tile + 1) * 4                   // offsets
+__host__ __device__ constexpr size_t greedy_smem_bytes(int warps, int k) {
+    return (size_t)(2 * k + 1) * (2 * 2 * W * 4 + 8) * 32 * warps   // lanes (orig+flip, 2W words) + state, per thread
+           + (size_t)warps * (4 * (size_t)stream_elems<W>(kPool) * 2 + 2 * (kPool + 1) * 4)   // per-warp streams + offsets
            + 64;
 }
 
-// ---------------------------------------------------------------------------------------------
-// K2+K3: one CTA per tile of T pairs, one thread per pair.
-// ---------------------------------------------------------------------------------------------
-template <int W, int T>
-__global__ void __launch_bounds__(T)
+template <int W, int WARPS>
+__global__ void __launch_bounds__(32 * WARPS)
 greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __restrict__ read_off,
               const uint8_t* __restrict__ refs, const uint32_t* __restrict__ ref_off, long long n,
               int32_t* __restrict__ cost, uint16_t* __restrict__ ops_stage, int ops_stride,
-              uint32_t* __restrict__ nops_out, uint32_t* __restrict__ tile_sums,
+              uint32_t* __restrict__ nops_out, uint32_t* __restrict__ chunk_counter, int refill_threshold,
               uint32_t* __restrict__ status, unsigned long long* __restrict__ step_counter) {
     constexpr int BITS = 64 * W;
+    constexpr int T = 32 * WARPS;
+    constexpr int SE = stream_elems<W>(kPool);
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int nl = 2 * P.k + 1;
-    uint64_t* s_lanes = reinterpret_cast<uint64_t*>(smem_raw);
-    uint64_t* s_state = s_lanes + (size_t)nl * 2 * W * T;
-    uint16_t* s_r0 = reinterpret_cast<uint16_t*>(s_state + (size_t)nl * T);
-    uint16_t* s_r1 = s_r0 + stream_elems<W>(T);
-    uint16_t* s_f0 = s_r1 + stream_elems<W>(T);
-    uint16_t* s_f1 = s_f0 + stream_elems<W>(T);
-    uint32_t* s_roff = reinterpret_cast<uint32_t*>(s_f1 + stream_elems<W>(T));
-    uint32_t* s_foff = s_roff + (T + 1);
-    __shared__ uint32_t s_warp_sums[T / 32];
+    uint64_t* s_state = reinterpret_cast<uint64_t*>(smem_raw);
+    uint32_t* s_lanes = reinterpret_cast<uint32_t*>(s_state + (size_t)nl * T);
+    uint16_t* s_streams = reinterpret_cast<uint16_t*>(s_lanes + (size_t)nl * 4 * W * T);
+    uint32_t* s_offs = reinterpret_cast<uint32_t*>(s_streams + (size_t)WARPS * 4 * SE);
 
-    const int tid = threadIdx.x;
-    const long long p0 = (long long)blockIdx.x * T;
-    const int np = (int)((n - p0) < (long long)T ? (n - p0) : (long long)T);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    uint16_t* s_r0 = s_streams + (size_t)warp * 4 * SE;
+    uint16_t* s_r1 = s_r0 + SE;
+    uint16_t* s_f0 = s_r1 + SE;
+    uint16_t* s_f1 = s_f0 + SE;
+    uint32_t* s_roff = s_offs + warp * 2 * (kPool + 1);
+    uint32_t* s_foff = s_roff + (kPool + 1);
+    // zero the stream padding once so every later read is of initialised memory (stale bits past a string's
+    // length are masked by extract_plane)
+    for (int i = lane; i < SE; i += 32) { s_r0[i] = 0; s_r1[i] = 0; s_f0[i] = 0; s_f1[i] = 0; }
+    __syncwarp();
 
-    for (int i = tid; i <= np; i += T) {
-        s_roff[i] = read_off[p0 + i];
-        s_foff[i] = ref_off[p0 + i];
-    }
-    // zero the stream padding so every later read is of initialised memory
-    for (int i = tid; i < stream_elems<W>(T); i += T) { s_r0[i] = 0; s_r1[i] = 0; s_f0[i] = 0; s_f1[i] = 0; }
-    __syncthreads();
-    const uint32_t rbase = s_roff[0] & ~15u, fbase = s_foff[0] & ~15u;
+    const LaneStore S{s_lanes + tid, s_state + tid, T};
+    const uint32_t nchunks = (uint32_t)((n + kPool - 1) / kPool);
     const uint32_t rtotal = read_off[n], ftotal = ref_off[n];
-    bool ok = stage_tile(reads, rbase, s_roff[np], rtotal, s_r0, s_r1, stream_chunks<W>(T), tid, T);
-    ok &= stage_tile(refs, fbase, s_foff[np], ftotal, s_f0, s_f1, stream_chunks<W>(T), tid, T);
-    __syncthreads();
 
-    uint32_t my_nops = 0, st = 0;
-    int steps = 0;
-    if (tid < np) {
-        const int m = (int)(s_roff[tid + 1] - s_roff[tid]);
-        const int nn = (int)(s_foff[tid + 1] - s_foff[tid]);
-        if (!ok) st |= kStatusTile;
-        if (m > BITS || nn > BITS) st |= kStatusLength;
-        else if (iabs(nn - m) > kMaxK) st |= kStatusBand;
-        int c = INT32_MIN;
-        if (st == 0) {
-            uint64_t A0[W], A1[W], B0[W], B1[W];
-            const int rbit = (int)(s_roff[tid] - rbase), fbit = (int)(s_foff[tid] - fbase);
-            extract_plane<W>(reinterpret_cast<const uint32_t*>(s_r0), rbit, m, A0);
-            extract_plane<W>(reinterpret_cast<const uint32_t*>(s_r1), rbit, m, A1);
-            extract_plane<W>(reinterpret_cast<const uint32_t*>(s_f0), fbit, nn, B0);
-            extract_plane<W>(reinterpret_cast<const uint32_t*>(s_f1), fbit, nn, B1);
-            LaneStore S{s_lanes + tid, s_state + tid, T};
-            OpSink sink{ops_stage ? ops_stage + (size_t)(p0 + tid) * ops_stride : nullptr, ops_stride, 0};
-            st = greedy_pair<W>(P, A0, A1, B0, B1, m, nn, S, sink, c, steps);
-            my_nops = (uint32_t)sink.n;
-            if (sink.n > ops_stride) st |= kStatusSteps;  // cannot happen: stride covers the step limit
+    // warp-uniform pool state
+    long long pool_p0 = 0;
+    int pool_next = 0, pool_count = 0;
+    bool pool_ok = true, exhausted = false;
+    uint32_t rbase = 0, fbase = 0;
+    // per-thread alignment state
+    bool active = false;
+    long long my_p = 0;
+    PairState ps;
+    OpSink sink{nullptr, 0, 0};
+    uint32_t st = 0;
+    uint32_t steps_done = 0;
+
+    for (;;) {
+        const uint32_t idle = __ballot_sync(0xffffffffu, !active);
+        const int n_idle = __popc(idle);
+        if (n_idle >= refill_threshold || n_idle == 32) {
+            if (pool_next == pool_count && !exhausted) {
+                // ---- claim and stage the next chunk (whole warp, converged) ----
+                uint32_t c = 0;
+                if (lane == 0) c = atomicAdd(chunk_counter, 1u);
+                c = __shfl_sync(0xffffffffu, c, 0);
+                if (c >= nchunks) {
+                    exhausted = true;
+                } else {
+                    pool_p0 = (long long)c * kPool;
+                    pool_count = (int)((n - pool_p0) < (long long)kPool ? (n - pool_p0) : (long long)kPool);
+                    pool_next = 0;
+                    __syncwarp();
+                    for (int i = lane; i <= pool_count; i += 32) {
+                        s_roff[i] = read_off[pool_p0 + i];
+                        s_foff[i] = ref_off[pool_p0 + i];
+                    }
+                    __syncwarp();
+                    rbase = s_roff[0] & ~15u;
+                    fbase = s_foff[0] & ~15u;
+                    pool_ok = stage_tile(reads, rbase, s_roff[pool_count], rtotal, s_r0, s_r1, stream_chunks<W>(kPool), lane, 32);
+                    pool_ok &= stage_tile(refs, fbase, s_foff[pool_count], ftotal, s_f0, s_f1, stream_chunks<W>(kPool), lane, 32);
+                    __syncwarp();
+                }
+            }
+            // ---- hand the pool's next pairs to the idle threads ----
+            const int q = pool_next + __popc(idle & ((1u << lane) - 1u));
+            if (!active && q < pool_count) {
+                my_p = pool_p0 + q;
+                const int m = (int)(s_roff[q + 1] - s_roff[q]);
+                const int nn = (int)(s_foff[q + 1] - s_foff[q]);
+                uint32_t bad = 0;
+                if (!pool_ok) bad |= kStatusTile;
+                if (m > BITS || nn > BITS) bad |= kStatusLength;
+                else if (iabs(nn - m) > kMaxK) bad |= kStatusBand;
+                if (bad) {
+                    st |= bad;
+                    cost[my_p] = INT32_MIN;
+                    if (nops_out) nops_out[my_p] = 0u;
+                } else {
+                    uint64_t A0[W], A1[W], B0[W], B1[W];
+                    const int rbit = (int)(s_roff[q] - rbase), fbit = (int)(s_foff[q] - fbase);
+                    extract_plane<W>(reinterpret_cast<const uint32_t*>(s_r0), rbit, m, A0);
+                    extract_plane<W>(reinterpret_cast<const uint32_t*>(s_r1), rbit, m, A1);
+                    extract_plane<W>(reinterpret_cast<const uint32_t*>(s_f0), fbit, nn, B0);
+                    extract_plane<W>(reinterpret_cast<const uint32_t*>(s_f1), fbit, nn, B1);
+                    pair_init<W>(P, A0, A1, B0, B1, m, nn, S, ps);
+                    sink = OpSink{ops_stage ? ops_stage + (size_t)my_p * ops_stride : nullptr, ops_stride, 0};
+                    active = true;
+                }
+            }
+            pool_next = imin(pool_count, pool_next + n_idle);
+            __syncwarp();
         }
-        cost[p0 + tid] = c;
-        if (nops_out) nops_out[p0 + tid] = my_nops;
+        if (__ballot_sync(0xffffffffu, active) == 0u) {
+            if (exhausted && pool_next == pool_count) break;
+            continue;   // nothing staged yet for this warp, or every pair of the pool was rejected
+        }
+        if (active) {
+            if (pair_step<W>(P, S, ps, sink, st)) {
+                pair_finish<W>(P, S, ps, sink);
+                cost[my_p] = ps.cost;
+                if (nops_out) nops_out[my_p] = (uint32_t)sink.n;
+                if (sink.n > ops_stride) st |= kStatusSteps;  // cannot happen: the stride covers the step limit
+                steps_done += (uint32_t)ps.steps;
+                active = false;
+            }
+        }
     }
     // one atomic per warp, and only when there is something to report
     const uint32_t wst = __reduce_or_sync(0xffffffffu, st);
-    if (wst && (tid & 31) == 0) atomicOr(status, wst);
+    if (wst && lane == 0) atomicOr(status, wst);
     if (step_counter) {
-        const uint32_t wsteps = __reduce_add_sync(0xffffffffu, (uint32_t)steps);
-        if ((tid & 31) == 0) atomicAdd(step_counter, (unsigned long long)wsteps);
-    }
-    if (tile_sums) {  // per-tile op count for the CSR scan
-        uint32_t v = my_nops;
-#pragma unroll
-        for (int d = 16; d; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
-        if ((tid & 31) == 0) s_warp_sums[tid >> 5] = v;
-        __syncthreads();
-        if (tid == 0) {
-            uint32_t t = 0;
-#pragma unroll
-            for (int i = 0; i < T / 32; ++i) t += s_warp_sums[i];
-            tile_sums[blockIdx.x] = t;
-        }
+        const uint32_t wsteps = __reduce_add_sync(0xffffffffu, steps_done);
+        if (lane == 0) atomicAdd(step_counter, (unsigned long long)wsteps);
     }
 }
 
