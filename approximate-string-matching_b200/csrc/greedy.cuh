@@ -6,9 +6,11 @@
 // (W=2 is the reference's int_128bit).  Semantics follow SURVEY.md section 8a rows a4-a12 literally,
 // including the stale per-lane cache and the popcount-as-length final op.
 //
-// One alignment per thread.  The 2k+1 lanes (orig + short-hurdle-flipped) and the per-lane cached
+// One alignment per thread.  The 2k+1 lanes (original hurdle masks as 32-bit words) and the per-lane cached
 // highway live in shared memory, laid out [lane][word][thread] so that a warp's accesses are
 // conflict-free; the running position, penalty and the two arg-max candidates live in registers.
+// The traversal is split into pair_init / pair_step / pair_finish so that a kernel can interleave pairs:
+// a thread that finishes takes a new pair while its warp neighbours keep stepping (kernels.cuh).
 #pragma once
 #include "common.cuh"
 
@@ -26,9 +28,11 @@ GASMA_HD int st_nh(uint64_t s) { return (int)((uint32_t)(s >> 32) >> 16); }
 // ---------------------------------------------------------------------------------------------
 // Lane storage.  A lane is kept as NW = 2W 32-bit words so that a scan or a ranged popcount touches only
 // the one to three words it needs (a dynamic word index is free in shared memory, it is not in registers).
-// Element (lane index li, kind, word w) of this thread lives at lanes[((li*2+kind)*NW + w) * stride]:
-// consecutive threads are consecutive 4-byte words, so a warp never bank-conflicts whatever w each thread
-// picks.  kind 0 = orig, 1 = flip.  `stride` is the number of threads sharing the array (1 in the host harness).
+// Word w of lane index li of this thread lives at lanes[(li*NW + w) * stride]: consecutive threads are
+// consecutive 4-byte words, so a warp never bank-conflicts whatever w each thread picks.  Only the ORIGINAL
+// hurdle masks are stored; the short-hurdle-flipped view (flip_short_hurdles(1), utils.h:200-216) is derived
+// word by word inside the scans (3 ALU ops per word), which halves the shared memory per alignment.
+// `stride` is the number of threads sharing the array (1 in the host harness).
 // ---------------------------------------------------------------------------------------------
 struct LaneStore {
     uint32_t* lanes;
@@ -51,19 +55,100 @@ GASMA_HD int popc32(uint32_t x) {
 #endif
 }
 
-// index of the first bit >= s that is set in (lane ^ inv); -1 if none   (first_one/first_zero, utils.h:168-191).
-// `base` points at word 0 of the lane for this thread.
+GASMA_HD uint32_t funnel_l1(uint32_t lo, uint32_t hi) {  // bits of (hi:lo) << 1, upper word
+#if defined(__CUDA_ARCH__)
+    return __funnelshift_l(lo, hi, 1);
+#else
+    return (hi << 1) | (lo >> 31);
+#endif
+}
+GASMA_HD uint32_t funnel_r1(uint32_t lo, uint32_t hi) {  // bits of (hi:lo) >> 1, lower word
+#if defined(__CUDA_ARCH__)
+    return __funnelshift_r(lo, hi, 1);
+#else
+    return (lo >> 1) | (hi << 31);
+#endif
+}
+// word of flip_short_hurdles(1): a hurdle survives iff a neighbouring bit is a hurdle too (edges see 0)
+GASMA_HD uint32_t flip_word(uint32_t prev, uint32_t cur, uint32_t next) {
+    return cur & (funnel_l1(prev, cur) | funnel_r1(cur, next));
+}
+
+// The closest highway of a lane at/after column sc (hurdle_matrix.h:296-303 on the flipped lane):
+//   sp  = sc + first_zero(flip >> sc)          first non-hurdle at/after sc; max(sc, BITS) if there is none
+//   len = first_one(flip >> sp)                run of non-hurdles from sp; BITS if no hurdle follows (utils.h:168-182)
+// One loop serves both searches (it flips from "looking for a 0" to "looking for a 1" in place and carries on in
+// the same word), touching only the words between sc and the end of the highway.
+// `base` points at word 0 of the lane's original mask for this thread.
 template <int W>
-GASMA_HD int scan_from(const uint32_t* base, int stride, uint32_t inv, int s) {
-    constexpr int NW = 2 * W;
-    int w = s >> 5;
-    if (w >= NW) return -1;
-    uint32_t t = (base[w * stride] ^ inv) & (0xFFFFFFFFu << (s & 31));
-    while (t == 0u) {
-        if (++w >= NW) return -1;
-        t = base[w * stride] ^ inv;
+GASMA_HD void scan_highway_loop(const uint32_t* base, int stride, int sc, int& sp, int& len) {
+    constexpr int NW = 2 * W, BITS = 64 * W;
+    sp = imax(sc, BITS);
+    len = BITS;
+    int w = sc >> 5;
+    if (w >= NW) return;
+    uint32_t prev = w > 0 ? base[(w - 1) * stride] : 0u;
+    uint32_t cur = base[w * stride];
+    uint32_t next = w + 1 < NW ? base[(w + 1) * stride] : 0u;
+    uint32_t inv = 0xFFFFFFFFu, mask = 0xFFFFFFFFu << (sc & 31);
+    for (;;) {
+        const uint32_t t = (flip_word(prev, cur, next) ^ inv) & mask;
+        if (t) {
+            const int pos = 32 * w + ctz32(t);
+            if (inv == 0u) { len = pos - sp; return; }
+            sp = pos;                                  // bit `pos` is 0, so it cannot match the search for a 1
+            inv = 0u;
+            mask = 0xFFFFFFFFu << (pos & 31);
+        } else {
+            if (++w >= NW) return;
+            prev = cur;
+            cur = next;
+            next = w + 1 < NW ? base[(w + 1) * stride] : 0u;
+            mask = 0xFFFFFFFFu;
+        }
     }
-    return 32 * w + ctz32(t);
+}
+
+GASMA_HD uint32_t funnel_r(uint32_t lo, uint32_t hi, int s) {  // low word of (hi:lo) >> s, 0 <= s < 32
+#if defined(__CUDA_ARCH__)
+    return __funnelshift_r(lo, hi, s);
+#else
+    return (uint32_t)((((uint64_t)hi << 32) | lo) >> s);
+#endif
+}
+
+// Same result as scan_highway_loop.  Fast path: the 64 bits of the flipped lane that start at sc are gathered
+// into one window and both searches are resolved without a branch; highways are geometrically distributed
+// (~1/error-rate bases), so the loop is only needed when a run does not end inside the window.
+template <int W>
+GASMA_HD void scan_highway(const uint32_t* base, int stride, int sc, int& sp, int& len) {
+    constexpr int NW = 2 * W, BITS = 64 * W;
+    const int w = sc >> 5, b = sc & 31;
+    if (w >= NW) { sp = imax(sc, BITS); len = BITS; return; }
+    const uint32_t om = w > 0 ? base[(w - 1) * stride] : 0u;
+    const uint32_t o0 = base[w * stride];
+    const uint32_t o1 = w + 1 < NW ? base[(w + 1) * stride] : 0u;
+    const uint32_t o2 = w + 2 < NW ? base[(w + 2) * stride] : 0u;
+    const uint32_t o3 = w + 3 < NW ? base[(w + 3) * stride] : 0u;
+    const uint32_t f0 = flip_word(om, o0, o1), f1 = flip_word(o0, o1, o2), f2 = flip_word(o1, o2, o3);
+    const uint32_t lo = funnel_r(f0, f1, b), hi = funnel_r(f1, f2, b);   // flipped lane bits [sc, sc+64), zero fill
+    const uint32_t zlo = ~lo, zhi = ~hi;
+    bool resolved = false;
+    if ((zlo | zhi) != 0u) {
+        const int fz = zlo ? ctz32(zlo) : 32 + ctz32(zhi);
+        const uint32_t tlo = fz < 32 ? (lo & (0xFFFFFFFFu << fz)) : 0u;
+        const uint32_t thi = fz < 32 ? hi : (hi & (0xFFFFFFFFu << (fz - 32)));
+        if ((tlo | thi) != 0u) {
+            sp = sc + fz;
+            len = (tlo ? ctz32(tlo) : 32 + ctz32(thi)) - fz;
+            resolved = true;
+        } else if (sc + 64 >= BITS) {   // the window reaches the end of the vector: no hurdle follows
+            sp = sc + fz;
+            len = BITS;
+            resolved = true;
+        }
+    }
+    if (!resolved) scan_highway_loop<W>(base, stride, sc, sp, len);
 }
 
 // pop_count_between(from,to), utils.h:263-270 = shift_left(from).shift_right(from+BITS-to).pop_count():
@@ -76,8 +161,8 @@ GASMA_HD int pcb(const uint32_t* base, int stride, int from, int to) {
     if (from >= to) return 0;
     const int w0 = from >> 5, w1 = (to - 1) >> 5;
     const uint32_t mlo = 0xFFFFFFFFu << (from & 31), mhi = 0xFFFFFFFFu >> (31 - ((to - 1) & 31));
-    if (w0 == w1) return popc32(base[w0 * stride] & mlo & mhi);
-    int c = popc32(base[w0 * stride] & mlo) + popc32(base[w1 * stride] & mhi);
+    const uint32_t a = base[w0 * stride] & mlo, z = base[w1 * stride] & mhi;   // w0 == w1: both masks on one word
+    int c = w0 == w1 ? popc32(a & mhi) : popc32(a) + popc32(z);
     for (int w = w0 + 1; w < w1; ++w) c += popc32(base[w * stride]);
     return c;
 }
@@ -92,10 +177,10 @@ GASMA_HD void shift_down_small(const uint64_t v[W], int s, uint64_t out[W]) {
     }
 }
 
-// One lane of _construct_hurdles (hurdle_matrix.h:441-455) + flip_short_hurdles(1) (utils.h:200-216)
+// One lane of _construct_hurdles (hurdle_matrix.h:441-455): the original (unflipped) hurdle mask
 template <int W>
 GASMA_HD void build_lane(const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W], const uint64_t B1[W],
-                         int lane, uint64_t orig[W], uint64_t flip[W]) {
+                         int lane, uint64_t orig[W]) {
     uint64_t s0[W], s1[W];
     const int a = iabs(lane);
     if (lane < 0) {
@@ -109,20 +194,14 @@ GASMA_HD void build_lane(const uint64_t A0[W], const uint64_t A1[W], const uint6
 #pragma unroll
         for (int j = 0; j < W; ++j) orig[j] = (s0[j] ^ A0[j]) | (s1[j] ^ A1[j]);
     }
-#pragma unroll
-    for (int j = 0; j < W; ++j) {
-        uint64_t up = (orig[j] << 1) | (j ? orig[j - 1] >> 63 : 0ull);
-        uint64_t dn = (orig[j] >> 1) | (j + 1 < W ? orig[j + 1] << 63 : 0ull);
-        flip[j] = orig[j] & (up | dn);
-    }
 }
 
 template <int W>
-GASMA_HD const uint32_t* lane_base(const LaneStore& S, int li, int kind) { return S.lanes + (size_t)((li * 2 + kind) * 2 * W) * S.stride; }
+GASMA_HD const uint32_t* lane_base(const LaneStore& S, int li) { return S.lanes + (size_t)(li * 2 * W) * S.stride; }
 
 template <int W>
-GASMA_HD void lane_store(const LaneStore& S, int li, int kind, const uint64_t v[W]) {
-    uint32_t* b = S.lanes + (size_t)((li * 2 + kind) * 2 * W) * S.stride;
+GASMA_HD void lane_store(const LaneStore& S, int li, const uint64_t v[W]) {
+    uint32_t* b = S.lanes + (size_t)(li * 2 * W) * S.stride;
 #pragma unroll
     for (int j = 0; j < W; ++j) {
         b[(2 * j) * S.stride] = (uint32_t)v[j];
@@ -161,10 +240,9 @@ GASMA_HD void pair_init(const KParams& P, const uint64_t A0[W], const uint64_t A
     constexpr int BITS = 64 * W;
     const int k = P.k;
     for (int l = -k; l <= k; ++l) {
-        uint64_t og[W], fl[W];
-        build_lane<W>(A0, A1, B0, B1, l, og, fl);
-        lane_store<W>(S, l + k, 0, og);
-        lane_store<W>(S, l + k, 1, fl);
+        uint64_t og[W];
+        build_lane<W>(A0, A1, B0, B1, l, og);
+        lane_store<W>(S, l + k, og);
         S.state[(l + k) * S.stride] = st_pack(-1, 0, BITS, BITS);
     }
     ps.m = m; ps.n = n; ps.cl = 0; ps.cc = 0; ps.cost = 0; ps.steps = 0; ps.first = true;
@@ -195,16 +273,11 @@ GASMA_HD bool pair_step(const KParams& P, const LaneStore& S, PairState& ps, OpS
         int sp = st_sp(st), len = st_len(st), nsw = st_nsw(st);
         if (sp < sc) {  // cache miss: look up the closest highway of this lane (:293-310)
             nsw = iabs(l - cl);
-            const uint32_t* f = lane_base<W>(S, li, 1);
-            const int p0 = scan_from<W>(f, S.stride, ~0u, sc);   // first zero at/after sc
-            const int pos0 = p0 >= 0 ? p0 : imax(sc, BITS);      // zero fill beyond the vector
-            const int p1 = scan_from<W>(f, S.stride, 0u, pos0);  // next hurdle
-            sp = pos0;
-            len = p1 >= 0 ? p1 - pos0 : BITS;                    // first_one of an empty vector = BITS
+            scan_highway<W>(lane_base<W>(S, li), S.stride, sc, sp, len);
             if (sp + len > de) { len = imax(0, de - sp); reach = true; }
         }
         const int sw = leap_cost ? slp(cl, l, o, e) : 0;
-        const int nh = pcb<W>(lane_base<W>(S, li, 0), S.stride, sc, sp + len);
+        const int nh = pcb<W>(lane_base<W>(S, li), S.stride, sc, sp + len);
         const int hc = x * nh;
         st = st_pack(sp, len, nsw, nh);
         S.state[li * S.stride] = st;
@@ -231,7 +304,7 @@ GASMA_HD bool pair_step(const KParams& P, const LaneStore& S, PairState& ps, OpS
     const int swb = leap_cost ? slp(cl, bl, o, e) : 0;
     int sT = x * st_nh(st_bl) + swb, sI = sT, b = bl;
     uint64_t st_b = st_bl;
-    const uint32_t* ob = lane_base<W>(S, bl + k, 0);
+    const uint32_t* ob = lane_base<W>(S, bl + k);
     for (int l = -k; l <= k; ++l) {
         if (l == bl) continue;
         const uint64_t st = S.state[(l + k) * S.stride];
@@ -265,7 +338,7 @@ GASMA_HD void pair_finish(const KParams& P, const LaneStore& S, PairState& ps, O
     const int dc = in_band ? lane_destination(ps.m, ps.n, dl) : -iabs(dl);
     if (cl != dl || cc < dc) {
         int d = 0;
-        if (in_band) d = pcb<W>(lane_base<W>(S, dl + k, 0), S.stride, cc + sfc(cl, dl), dc);
+        if (in_band) d = pcb<W>(lane_base<W>(S, dl + k), S.stride, cc + sfc(cl, dl), dc);
         // out of band: dc < 0 <= from, so pop_count_between of the default value 1 is 0 as well
         ps.cost += (P.global ? slp(cl, dl, P.o, P.e) : 0) + imax(0, x * d);
         sink.update(dl, cl, d);

@@ -20,27 +20,39 @@ __device__ __forceinline__ uint4 ldg_stream16(const void* p) {
     return r;
 }
 
+__device__ __forceinline__ uint4 load_chunk(const uint8_t* __restrict__ buf, uint32_t a, uint32_t total) {
+    if (a + 16u <= total) return ldg_stream16(buf + a);
+    // last partial chunk of the whole buffer: never read past the logical end (rare: kept small, not unrolled)
+    uint32_t w[4] = {0u, 0u, 0u, 0u};
+#pragma unroll 1
+    for (uint32_t i = 0; a + i < total; ++i) {
+        const uint32_t b = (uint32_t)buf[a + i] << (8u * (i & 3u));
+        if (i < 4u) w[0] |= b; else if (i < 8u) w[1] |= b; else if (i < 12u) w[2] |= b; else w[3] |= b;
+    }
+    return make_uint4(w[0], w[1], w[2], w[3]);
+}
+
 // Packs bytes [base16, end) of `buf` (base16 is 16-byte aligned, total = logical size of buf) into
 // stream0/stream1 (one uint16 per chunk).  Returns false if the range does not fit `cap_chunks`.
+// Software-pipelined by one chunk (the next 16-byte load is in flight while the current one is packed) and
+// deliberately NOT unrolled: the pack body is ~100 instructions and the kernels that inline this are
+// instruction-cache sensitive (r01e profile: 90 KB of SASS, "no instruction" the top stall).
 __device__ __forceinline__ bool stage_tile(const uint8_t* __restrict__ buf, uint32_t base16, uint32_t end, uint32_t total,
                                            uint16_t* stream0, uint16_t* stream1, int cap_chunks, int tid, int nthreads) {
     int nchunks = (int)((end - base16 + 15u) >> 4);
     bool ok = nchunks <= cap_chunks;
     if (!ok) nchunks = cap_chunks;
+    uint4 cur = make_uint4(0u, 0u, 0u, 0u);
+    if (tid < nchunks) cur = load_chunk(buf, base16 + 16u * (uint32_t)tid, total);
+#pragma unroll 1
     for (int c = tid; c < nchunks; c += nthreads) {
-        const uint32_t a = base16 + 16u * (uint32_t)c;
-        uint4 v;
-        if (a + 16u <= total) {
-            v = ldg_stream16(buf + a);
-        } else {  // last partial chunk of the whole buffer: never read past the logical end
-            uint32_t w[4] = {0u, 0u, 0u, 0u};
-            for (uint32_t i = 0; a + i < total && i < 16u; ++i) w[i >> 2] |= (uint32_t)buf[a + i] << (8u * (i & 3u));
-            v = make_uint4(w[0], w[1], w[2], w[3]);
-        }
+        uint4 nxt = make_uint4(0u, 0u, 0u, 0u);
+        if (c + nthreads < nchunks) nxt = load_chunk(buf, base16 + 16u * (uint32_t)(c + nthreads), total);
         uint32_t p0, p1;
-        pack_chunk(v.x, v.y, v.z, v.w, p0, p1);
+        pack_chunk(cur.x, cur.y, cur.z, cur.w, p0, p1);
         stream0[c] = (uint16_t)p0;
         stream1[c] = (uint16_t)p1;
+        cur = nxt;
     }
     return ok;
 }
@@ -65,13 +77,13 @@ constexpr int kPool = 32;   // pairs per chunk = per warp pool
 
 template <int W>
 __host__ __device__ constexpr size_t greedy_smem_bytes(int warps, int k) {
-    return (size_t)(2 * k + 1) * (2 * 2 * W * 4 + 8) * 32 * warps   // lanes (orig+flip, 2W words) + state, per thread
+    return (size_t)(2 * k + 1) * (2 * W * 4 + 8) * 32 * warps   // lanes (2W 32-bit words) + state, per thread
            + (size_t)warps * (4 * (size_t)stream_elems<W>(kPool) * 2 + 2 * (kPool + 1) * 4)   // per-warp streams + offsets
            + 64;
 }
 
 template <int W, int WARPS>
-__global__ void __launch_bounds__(32 * WARPS)
+__global__ void __launch_bounds__(32 * WARPS, WARPS == 4 ? 5 : 1)
 greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __restrict__ read_off,
               const uint8_t* __restrict__ refs, const uint32_t* __restrict__ ref_off, long long n,
               int32_t* __restrict__ cost, uint16_t* __restrict__ ops_stage, int ops_stride,
@@ -84,7 +96,7 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
     const int nl = 2 * P.k + 1;
     uint64_t* s_state = reinterpret_cast<uint64_t*>(smem_raw);
     uint32_t* s_lanes = reinterpret_cast<uint32_t*>(s_state + (size_t)nl * T);
-    uint16_t* s_streams = reinterpret_cast<uint16_t*>(s_lanes + (size_t)nl * 4 * W * T);
+    uint16_t* s_streams = reinterpret_cast<uint16_t*>(s_lanes + (size_t)nl * 2 * W * T);
     uint32_t* s_offs = reinterpret_cast<uint32_t*>(s_streams + (size_t)WARPS * 4 * SE);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -106,8 +118,43 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
     // warp-uniform pool state
     long long pool_p0 = 0;
     int pool_next = 0, pool_count = 0;
-    bool pool_ok = true, exhausted = false;
+    bool pool_ok = true;
     uint32_t rbase = 0, fbase = 0;
+    // The NEXT chunk is claimed and brought towards the SM while the current pool is being worked on, one
+    // stage per loop iteration so that no stage waits for the previous one's memory round trip:
+    //   kClaimed   lane 0 has issued the atomicAdd, its result is not consumed yet
+    //   kOffsets   the chunk index is known, the offset loads (lane i: off[p0+i], all lanes: off[p0+cnt]) are issued
+    //   kReady     the byte ranges are known, L2 prefetches for both sides are issued
+    //   kNone      nothing in flight (start), kDone: the counter ran past the last chunk
+    enum { kNone, kClaimed, kOffsets, kReady, kDone };
+    int pf = kNone;
+    uint32_t nx_chunk = 0;                   // valid in lane 0 from kClaimed, in all lanes from kOffsets
+    int nx_count = 0;
+    uint32_t nx_ro = 0, nx_fo = 0, nx_re = 0, nx_fe = 0;
+    auto advance = [&]() {                   // one pipeline stage; warp-uniform
+        if (pf == kNone) {
+            if (lane == 0) nx_chunk = atomicAdd(chunk_counter, 1u);
+            pf = kClaimed;
+        } else if (pf == kClaimed) {
+            nx_chunk = __shfl_sync(0xffffffffu, nx_chunk, 0);
+            if (nx_chunk >= nchunks) { pf = kDone; return; }
+            const long long p0n = (long long)nx_chunk * kPool;
+            nx_count = (int)((n - p0n) < (long long)kPool ? (n - p0n) : (long long)kPool);
+            const int i = lane < nx_count ? lane : nx_count;
+            nx_ro = read_off[p0n + i];
+            nx_fo = ref_off[p0n + i];
+            nx_re = read_off[p0n + nx_count];
+            nx_fe = ref_off[p0n + nx_count];
+            pf = kOffsets;
+        } else if (pf == kOffsets) {
+            const uint32_t r0 = __shfl_sync(0xffffffffu, nx_ro, 0) & ~127u, f0 = __shfl_sync(0xffffffffu, nx_fo, 0) & ~127u;
+            for (uint32_t a = r0 + 128u * lane; a < nx_re; a += 128u * 32u)
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(reads + a));
+            for (uint32_t a = f0 + 128u * lane; a < nx_fe; a += 128u * 32u)
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(refs + a));
+            pf = kReady;
+        }
+    };
     // per-thread alignment state
     bool active = false;
     long long my_p = 0;
@@ -117,31 +164,32 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
     uint32_t steps_done = 0;
 
     for (;;) {
+        if (pf != kReady && pf != kDone) advance();
         const uint32_t idle = __ballot_sync(0xffffffffu, !active);
         const int n_idle = __popc(idle);
         if (n_idle >= refill_threshold || n_idle == 32) {
-            if (pool_next == pool_count && !exhausted) {
-                // ---- claim and stage the next chunk (whole warp, converged) ----
-                uint32_t c = 0;
-                if (lane == 0) c = atomicAdd(chunk_counter, 1u);
-                c = __shfl_sync(0xffffffffu, c, 0);
-                if (c >= nchunks) {
-                    exhausted = true;
-                } else {
-                    pool_p0 = (long long)c * kPool;
-                    pool_count = (int)((n - pool_p0) < (long long)kPool ? (n - pool_p0) : (long long)kPool);
+            if (pool_next == pool_count && pf != kDone) {
+                // ---- stage the claimed chunk (whole warp, converged) ----
+                while (pf != kReady && pf != kDone) advance();   // start of the kernel / a very short pool
+                if (pf == kReady) {
+                    pool_p0 = (long long)nx_chunk * kPool;
+                    pool_count = nx_count;
                     pool_next = 0;
                     __syncwarp();
-                    for (int i = lane; i <= pool_count; i += 32) {
-                        s_roff[i] = read_off[pool_p0 + i];
-                        s_foff[i] = ref_off[pool_p0 + i];
-                    }
+                    if (lane < pool_count) { s_roff[lane] = nx_ro; s_foff[lane] = nx_fo; }
+                    if (lane == 0) { s_roff[pool_count] = nx_re; s_foff[pool_count] = nx_fe; }
                     __syncwarp();
                     rbase = s_roff[0] & ~15u;
                     fbase = s_foff[0] & ~15u;
-                    pool_ok = stage_tile(reads, rbase, s_roff[pool_count], rtotal, s_r0, s_r1, stream_chunks<W>(kPool), lane, 32);
-                    pool_ok &= stage_tile(refs, fbase, s_foff[pool_count], ftotal, s_f0, s_f1, stream_chunks<W>(kPool), lane, 32);
+                    pool_ok = true;
+#pragma unroll 1
+                    for (int side = 0; side < 2; ++side)   // one instance of the pack code for both sides
+                        pool_ok &= stage_tile(side ? refs : reads, side ? fbase : rbase, side ? nx_fe : nx_re,
+                                              side ? ftotal : rtotal, side ? s_f0 : s_r0, side ? s_f1 : s_r1,
+                                              stream_chunks<W>(kPool), lane, 32);
                     __syncwarp();
+                    pf = kNone;
+                    advance();   // claim the chunk after this one right away
                 }
             }
             // ---- hand the pool's next pairs to the idle threads ----
@@ -174,8 +222,8 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
             __syncwarp();
         }
         if (__ballot_sync(0xffffffffu, active) == 0u) {
-            if (exhausted && pool_next == pool_count) break;
-            continue;   // nothing staged yet for this warp, or every pair of the pool was rejected
+            if (pf == kDone && pool_next == pool_count) break;
+            continue;   // every pair handed out so far was rejected, or the pool just ran empty
         }
         if (active) {
             if (pair_step<W>(P, S, ps, sink, st)) {

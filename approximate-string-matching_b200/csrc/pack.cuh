@@ -34,13 +34,33 @@ GASMA_HD void pack_word(uint32_t x, uint32_t& n0, uint32_t& n1) {
     n1 = gather4(g | t);
 }
 
+// 4 characters -> plane nibbles, assuming they are all in {A,C,G,T}; `bad` collects the proof that they are.
+// ASCII A=0x41 C=0x43 G=0x47 T=0x54: bit 2 is the G/T plane and bit1^bit2 the C/T plane.  The character is then
+// rebuilt from its two bits (0x41 + 2*ct + 6*gt + 11*(ct&gt) gives 0x41/0x43/0x47/0x54; bytes never carry) and
+// compared with the input, so any other byte leaves a non-zero mark in `bad`.
+GASMA_HD void pack_word_acgt(uint32_t x, uint32_t& n0, uint32_t& n1, uint32_t& bad) {
+    const uint32_t gt = (x >> 2) & 0x01010101u;
+    const uint32_t ct = ((x >> 1) ^ (x >> 2)) & 0x01010101u;
+    const uint32_t rebuilt = 0x41414141u + 2u * ct + 6u * gt + 11u * (ct & gt);
+    bad |= rebuilt ^ x;
+    // bit 8j -> bit 28+j: 0x10204080 = 2^28+2^21+2^14+2^7; the cross terms fall below bit 28 on distinct bits or overflow
+    n0 = (ct * 0x10204080u) >> 28;
+    n1 = (gt * 0x10204080u) >> 28;
+}
+
 // 16 characters -> 16 + 16 plane bits
 GASMA_HD void pack_chunk(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, uint32_t& p0, uint32_t& p1) {
-    uint32_t a0, a1, b0, b1, c0, c1, d0, d1;
-    pack_word(w0, a0, a1);
-    pack_word(w1, b0, b1);
-    pack_word(w2, c0, c1);
-    pack_word(w3, d0, d1);
+    uint32_t a0, a1, b0, b1, c0, c1, d0, d1, bad = 0u;
+    pack_word_acgt(w0, a0, a1, bad);
+    pack_word_acgt(w1, b0, b1, bad);
+    pack_word_acgt(w2, c0, c1, bad);
+    pack_word_acgt(w3, d0, d1, bad);
+    if (bad) {   // some byte is not A/C/G/T (N, lower case, NUL ...): exact compares, such bytes pack as 00
+        pack_word(w0, a0, a1);
+        pack_word(w1, b0, b1);
+        pack_word(w2, c0, c1);
+        pack_word(w3, d0, d1);
+    }
     p0 = a0 | (b0 << 4) | (c0 << 8) | (d0 << 12);
     p1 = a1 | (b1 << 4) | (c1 << 8) | (d1 << 12);
 }

@@ -49,7 +49,7 @@ int sim_greedy(const KParams& P, const uint8_t* reads, const uint32_t* roff, con
                int64_t* steps_out) {
     constexpr int BITS = 64 * W;
     const int nl = 2 * P.k + 1;
-    std::vector<uint32_t> lanes((size_t)nl * 2 * 2 * W);
+    std::vector<uint32_t> lanes((size_t)nl * 2 * W);
     std::vector<uint64_t> state(nl);
     std::vector<uint16_t> r0(elems<W>(T)), r1(elems<W>(T)), f0(elems<W>(T)), f1(elems<W>(T));
     uint32_t status = 0;
