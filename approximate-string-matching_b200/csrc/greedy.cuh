@@ -120,8 +120,10 @@ GASMA_HD uint32_t funnel_r(uint32_t lo, uint32_t hi, int s) {  // low word of (h
 // Same result as scan_highway_loop.  Fast path: the 64 bits of the flipped lane that start at sc are gathered
 // into one window and both searches are resolved without a branch; highways are geometrically distributed
 // (~1/error-rate bases), so the loop is only needed when a run does not end inside the window.
+// `de` is the lane's destination column: the caller clamps any highway with sp+len > de to the destination, so a
+// run that leaves the window beyond de needs no exact end (len = BITS stands for "past the destination").
 template <int W>
-GASMA_HD void scan_highway(const uint32_t* base, int stride, int sc, int& sp, int& len) {
+GASMA_HD void scan_highway(const uint32_t* base, int stride, int sc, int de, int& sp, int& len) {
     constexpr int NW = 2 * W, BITS = 64 * W;
     const int w = sc >> 5, b = sc & 31;
     if (w >= NW) { sp = imax(sc, BITS); len = BITS; return; }
@@ -142,7 +144,7 @@ GASMA_HD void scan_highway(const uint32_t* base, int stride, int sc, int& sp, in
             sp = sc + fz;
             len = (tlo ? ctz32(tlo) : 32 + ctz32(thi)) - fz;
             resolved = true;
-        } else if (sc + 64 >= BITS) {   // the window reaches the end of the vector: no hurdle follows
+        } else if (sc + 64 >= BITS || sc + 64 > de) {   // no hurdle up to the end of the vector / past the destination
             sp = sc + fz;
             len = BITS;
             resolved = true;
@@ -163,7 +165,8 @@ GASMA_HD int pcb(const uint32_t* base, int stride, int from, int to) {
     const uint32_t mlo = 0xFFFFFFFFu << (from & 31), mhi = 0xFFFFFFFFu >> (31 - ((to - 1) & 31));
     const uint32_t a = base[w0 * stride] & mlo, z = base[w1 * stride] & mhi;   // w0 == w1: both masks on one word
     int c = w0 == w1 ? popc32(a & mhi) : popc32(a) + popc32(z);
-    for (int w = w0 + 1; w < w1; ++w) c += popc32(base[w * stride]);
+    if (w1 - w0 >= 2) c += popc32(base[(w0 + 1) * stride]);   // up to three words without a loop
+    for (int w = w0 + 2; w < w1; ++w) c += popc32(base[w * stride]);
     return c;
 }
 
@@ -273,7 +276,7 @@ GASMA_HD bool pair_step(const KParams& P, const LaneStore& S, PairState& ps, OpS
         int sp = st_sp(st), len = st_len(st), nsw = st_nsw(st);
         if (sp < sc) {  // cache miss: look up the closest highway of this lane (:293-310)
             nsw = iabs(l - cl);
-            scan_highway<W>(lane_base<W>(S, li), S.stride, sc, sp, len);
+            scan_highway<W>(lane_base<W>(S, li), S.stride, sc, de, sp, len);
             if (sp + len > de) { len = imax(0, de - sp); reach = true; }
         }
         const int sw = leap_cost ? slp(cl, l, o, e) : 0;
