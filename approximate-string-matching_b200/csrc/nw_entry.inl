@@ -17,6 +17,28 @@ int launch_nw_w(gasma_ctx* ctx, const uint8_t* reads, const uint32_t* roff, cons
     const int nslots = W <= 2 ? 8192 : 4096;
     if ((rc = reserve(ctx, ctx->nw_pool_hi, (size_t)nslots * 2 * (2 * BITS + 2) * 4))) return rc;
     if (want_ops && (rc = reserve(ctx, ctx->nw_pool_tb, (size_t)nslots * BITS * nw_tb_words_wide<W>() * 4))) return rc;
+    if (ctx->kp.x == 1 && ctx->kp.o == 1 && ctx->kp.e == 1) {
+        // unit penalties (the benchmark's configuration): bit-vector columns, exact without a band
+        const int64_t per_pair = (int64_t)myers_tb_words<W>() * 4;
+        const int64_t mchunk = want_ops ? ((int64_t)1 << 30) / per_pair : n;
+        if (want_ops && (rc = reserve(ctx, ctx->nw_tb, (size_t)(n < mchunk ? n : mchunk) * per_pair))) return rc;
+        auto mk = nw_myers_kernel<W, T>;
+        const size_t msmem = myers_smem_bytes<W>(T);
+        CU(cudaFuncSetAttribute(mk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msmem));
+        cudaEvent_t* mev = ctx->ev[1][ctx->ev_count[1] % gasma_ctx::kRing];
+        CU(cudaEventRecord(mev[0], ctx->stream));
+        for (int64_t first = 0; first < n; first += mchunk) {
+            const int64_t count = n - first < mchunk ? n - first : mchunk;
+            mk<<<(unsigned)((count + T - 1) / T), T, msmem, ctx->stream>>>(reads, roff, refs, foff, (long long)n, (long long)first,
+                                                                          (long long)count, bound, penalty, (uint32_t*)ctx->nw_tb.p,
+                                                                          stage, stride, nops, misc);
+            CU(cudaGetLastError());
+            ctx->launches++;
+        }
+        CU(cudaEventRecord(mev[1], ctx->stream));
+        ctx->ev_count[1]++;
+        return GASMA_OK;
+    }
     CU(cudaMemsetAsync(dcount, 0, 4, ctx->stream));
     auto kern = nw_kernel<W, T>;
     const size_t smem = nw_smem_bytes<W>(T);

@@ -1,0 +1,204 @@
+// nw_myers.cuh -- K4 fast path: the NW verifier for unit penalties (x = o = e = 1), bit-parallel.
+//
+// The reference's benchmark always verifies with benchmark(1,1,1,...) (GASMA/benchmark/benchmark.cpp:22,27),
+// i.e. parasail_nw_trace with match 0 / mismatch -1 / gap -(1+(g-1)) (benchmark_utils.h:113-116,139-142,288):
+// plain Levenshtein distance.  For that scoring the DP matrix is computed one COLUMN per step with Myers' /
+// Hyyro's bit-vector recurrence on the vertical and horizontal deltas (all rows of the read at once, 32 rows per
+// machine word) instead of one cell at a time, in its global (NW) form: every column enters row 0 with a
+// horizontal delta of +1 (H[0][j] = j) and column 0 has vertical deltas +1 (H[i][0] = i).
+//
+// Traceback is the same deterministic rule as the general Gotoh kernel / oracle (oracle/gasma_oracle.c:go_nw;
+// with o == e a gap is never "extended" in preference to being re-opened, so the three-state walk collapses):
+//   at (i,j): diagonal if H[i][j] == H[i-1][j-1] + (read[i] != ref[j]), else I (up) if H[i][j] == H[i-1][j] + 1,
+//   else D (left).
+// Both tests are bits of two vectors that fall out of the column step, so two bit-vectors per column are all the
+// traceback needs:  UP = Pv (vertical delta +1)  and
+//   DG = Eq | ~zero(dv + dh'),   dv = vertical delta of column j at row i, dh' = horizontal delta at row i-1
+// because H[i][j] - H[i-1][j-1] = dv_j(i) + dh_j(i-1) is 0 or 1, is 0 on a match, and a mismatching diagonal is
+// optimal exactly when that difference is 1.
+//
+// Traceback storage.  An optimal path stays on the diagonals d = j - i of nw_band() (nw.cuh) whenever an upper bound
+// on the optimum is known (the greedy penalty), so of each column only the rows i in [j-hi, j-lo] can ever be
+// visited.  If that band has at most 64 diagonals, a 64-bit WINDOW of DG and UP starting at row j-hi is kept per
+// column (16 bytes instead of 16W): the kernel is bound by this scratch traffic, not by arithmetic.  Wider bands
+// (or no bound) keep the full vectors.
+#pragma once
+#include "common.cuh"
+#include "nw.cuh"
+
+namespace gasma {
+
+// One column.  NW32 = number of 32-bit words covering the read.  eq[] = rows whose character equals ref[j].
+// Updates pv/mv in place, returns the horizontal delta at row `m` (bit m-1), writes DG into dg[].
+template <int NW32>
+GASMA_HD int myers_column(const uint32_t eq[NW32], uint32_t pv[NW32], uint32_t mv[NW32], uint32_t dg[NW32], int m) {
+    uint32_t ph[NW32], mh[NW32], xv[NW32];
+    uint32_t carry = 0u;
+#pragma unroll
+    for (int w = 0; w < NW32; ++w) {
+        xv[w] = eq[w] | mv[w];
+        // sum = (eq & pv) + pv over the whole multi-word vector
+        const uint32_t a = eq[w] & pv[w];
+        const uint64_t s = (uint64_t)a + pv[w] + carry;
+        carry = (uint32_t)(s >> 32);
+        const uint32_t xh = ((uint32_t)s ^ pv[w]) | eq[w];
+        ph[w] = mv[w] | ~(xh | pv[w]);
+        mh[w] = pv[w] & xh;
+    }
+    int dh = 0;
+    if (m > 0) {
+        const int w = (m - 1) >> 5, b = (m - 1) & 31;
+        uint32_t p = 0u, q = 0u;
+#pragma unroll
+        for (int j = 0; j < NW32; ++j)
+            if (j == w) { p = ph[j]; q = mh[j]; }
+        dh = (int)((p >> b) & 1u) - (int)((q >> b) & 1u);
+    }
+    // shift the horizontal deltas down one row; row 0 enters with +1 (global alignment)
+    uint32_t cp = 1u, cm = 0u;
+#pragma unroll
+    for (int w = 0; w < NW32; ++w) {
+        const uint32_t php = (ph[w] << 1) | cp, mhp = (mh[w] << 1) | cm;
+        cp = ph[w] >> 31;
+        cm = mh[w] >> 31;
+        const uint32_t npv = mhp | ~(xv[w] | php);
+        const uint32_t nmv = php & xv[w];
+        const uint32_t zero = (~(npv | nmv) & ~(php | mhp)) | (npv & mhp) | (nmv & php);   // dv + dh' == 0
+        dg[w] = eq[w] | ~zero;
+        pv[w] = npv;
+        mv[w] = nmv;
+    }
+    return dh;
+}
+
+GASMA_HD uint32_t funnel32(uint32_t lo, uint32_t hi, int s) {  // low word of (hi:lo) >> s, 0 <= s < 32
+#if defined(__CUDA_ARCH__)
+    return __funnelshift_r(lo, hi, s);
+#else
+    return (uint32_t)((((uint64_t)hi << 32) | lo) >> s);
+#endif
+}
+
+// bits [s, s+64) of an NW32-word vector (zeros beyond it), s >= 0
+template <int NW32>
+GASMA_HD void window64_of(const uint32_t v[NW32], int s, uint32_t& lo, uint32_t& hi) {
+    const int idx = s >> 5, sh = s & 31;
+    uint32_t x0 = 0u, x1 = 0u, x2 = 0u;
+#pragma unroll
+    for (int w = 0; w < NW32; ++w) {
+        if (w == idx) x0 = v[w];
+        if (w == idx + 1) x1 = v[w];
+        if (w == idx + 2) x2 = v[w];
+    }
+    lo = funnel32(x0, x1, sh);
+    hi = funnel32(x1, x2, sh);
+}
+
+// first row (0-based bit index) of the window kept for column j0 (0-based) when the band's top diagonal is hi
+GASMA_HD int myers_window_start(int j0, int hi) { return imax(0, j0 - hi); }
+
+// Forward pass.  Returns the optimal penalty.  tb (optional, 16-byte aligned) receives per column j0 = 0..n-1
+//   windowed:  4 words  {DG window lo, hi, UP window lo, hi}                       at tb[j0 * 4]
+//   full:      NW32 words of DG then NW32 words of UP (= Pv)                       at tb[j0 * 2 * NW32]
+template <int W>
+GASMA_HD int myers_forward(const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W], const uint64_t B1[W], int m, int n,
+                           uint32_t* tb, bool windowed, int band_hi) {
+    constexpr int NW32 = 2 * W;
+    if (m == 0) return n;
+    uint32_t a0[NW32], a1[NW32], pv[NW32], mv[NW32];
+#pragma unroll
+    for (int j = 0; j < W; ++j) {
+        a0[2 * j] = (uint32_t)A0[j]; a0[2 * j + 1] = (uint32_t)(A0[j] >> 32);
+        a1[2 * j] = (uint32_t)A1[j]; a1[2 * j + 1] = (uint32_t)(A1[j] >> 32);
+    }
+#pragma unroll
+    for (int w = 0; w < NW32; ++w) { pv[w] = 0xFFFFFFFFu; mv[w] = 0u; }
+    int score = m;
+    uint64_t b0 = 0, b1 = 0;
+    for (int j = 0; j < n; ++j) {
+        if ((j & 63) == 0) {   // next 64 reference characters
+#pragma unroll
+            for (int q = 0; q < W; ++q)
+                if (q == (j >> 6)) { b0 = B0[q]; b1 = B1[q]; }
+        }
+        const uint32_t k0 = (uint32_t)0 - (uint32_t)(b0 & 1ull), k1 = (uint32_t)0 - (uint32_t)(b1 & 1ull);
+        b0 >>= 1;
+        b1 >>= 1;
+        uint32_t eq[NW32], dg[NW32];
+#pragma unroll
+        for (int w = 0; w < NW32; ++w) eq[w] = ~(a0[w] ^ k0) & ~(a1[w] ^ k1);
+        score += myers_column<NW32>(eq, pv, mv, dg, m);
+        if (tb && windowed) {
+            const int s0 = myers_window_start(j, band_hi);
+            uint32_t t0, t1, t2, t3;
+            window64_of<NW32>(dg, s0, t0, t1);
+            window64_of<NW32>(pv, s0, t2, t3);
+            uint32_t* col = tb + (size_t)j * 4;
+#if defined(__CUDA_ARCH__)
+            *reinterpret_cast<uint4*>(col) = make_uint4(t0, t1, t2, t3);
+#else
+            col[0] = t0; col[1] = t1; col[2] = t2; col[3] = t3;
+#endif
+        } else if (tb) {
+            uint32_t* col = tb + (size_t)j * 2 * NW32;
+#if defined(__CUDA_ARCH__)
+            uint32_t t[4 * W];   // one column = 16W bytes = W 16-byte stores
+#pragma unroll
+            for (int w = 0; w < NW32; ++w) { t[w] = dg[w]; t[NW32 + w] = pv[w]; }
+#pragma unroll
+            for (int q = 0; q < W; ++q)
+                reinterpret_cast<uint4*>(col)[q] = make_uint4(t[4 * q], t[4 * q + 1], t[4 * q + 2], t[4 * q + 3]);
+#else
+            for (int w = 0; w < NW32; ++w) { col[w] = dg[w]; col[NW32 + w] = pv[w]; }
+#endif
+        }
+    }
+    return score;
+}
+
+// Traceback from (m,n); same output convention as nw_traceback (nw.cuh): run-length ops (3 '=', 4 'X', 1 'I',
+// 2 'D') written back to front into row[cap-cnt .. cap); returns cnt.
+template <int W>
+GASMA_HD int myers_traceback(const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W], const uint64_t B1[W], int m,
+                             int n, const uint32_t* tb, bool windowed, int band_hi, uint16_t* row, int cap) {
+    constexpr int NW32 = 2 * W;
+    int i = m, j = n, cnt = 0, cur = -1, run = 0;
+    auto push = [&](int code, int len) {
+        if (code == cur) { run += len; return; }
+        if (cur >= 0) { ++cnt; if (cnt <= cap) row[cap - cnt] = (uint16_t)((run << 3) | cur); }
+        cur = code; run = len;
+    };
+    while (i > 0 && j > 0) {
+        uint32_t dgw, upw;
+        int b;
+        if (windowed) {
+            const uint32_t* col = tb + (size_t)(j - 1) * 4;
+            const int r = (i - 1) - myers_window_start(j - 1, band_hi);   // 0..63 on any optimal path
+            b = r & 31;
+            dgw = col[r >> 5];
+            upw = col[2 + (r >> 5)];
+        } else {
+            const uint32_t* col = tb + (size_t)(j - 1) * 2 * NW32;
+            b = (i - 1) & 31;
+            dgw = col[(i - 1) >> 5];
+            upw = col[NW32 + ((i - 1) >> 5)];
+        }
+        if ((dgw >> b) & 1u) {
+            const int mis = (bit_of<W>(A0, i - 1) ^ bit_of<W>(B0, j - 1)) | (bit_of<W>(A1, i - 1) ^ bit_of<W>(B1, j - 1));
+            push(mis ? 4 : 3, 1);
+            --i; --j;
+        } else if ((upw >> b) & 1u) {
+            push(1, 1);
+            --i;
+        } else {
+            push(2, 1);
+            --j;
+        }
+    }
+    if (i > 0) push(1, i);
+    if (j > 0) push(2, j);
+    push(-2, 0);  // flush
+    return cnt;
+}
+
+}  // namespace gasma

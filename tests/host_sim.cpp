@@ -13,6 +13,7 @@
 #include "../approximate-string-matching_b200/csrc/pack.cuh"
 #include "../approximate-string-matching_b200/csrc/greedy.cuh"
 #include "../approximate-string-matching_b200/csrc/nw.cuh"
+#include "../approximate-string-matching_b200/csrc/nw_myers.cuh"
 #include "../approximate-string-matching_b200/csrc/metrics.cuh"
 #include "../approximate-string-matching_b200/csrc/generate.cuh"
 
@@ -156,9 +157,56 @@ int sim_nw(int x, int o, int e, const uint8_t* reads, const uint32_t* roff, cons
     return 0;
 }
 
+// unit-penalty NW (Myers bit-vector columns), same staging, traceback vectors in a heap scratch
+template <int W>
+int sim_myers(const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, const uint32_t* foff, int64_t n, int T,
+              const int32_t* bound, int32_t* penalty, uint16_t* ops_stage, int stride, uint32_t* nops, int64_t* n_windowed) {
+    int64_t nwin = 0;
+    constexpr int BITS = 64 * W;
+    std::vector<uint16_t> r0(elems<W>(T)), r1(elems<W>(T)), f0(elems<W>(T)), f1(elems<W>(T));
+    std::vector<uint32_t> tb((size_t)BITS * 4 * W);
+    for (int64_t p0 = 0; p0 < n; p0 += T) {
+        const int np = (int)std::min<int64_t>(T, n - p0);
+        std::fill(r0.begin(), r0.end(), 0); std::fill(r1.begin(), r1.end(), 0);
+        std::fill(f0.begin(), f0.end(), 0); std::fill(f1.begin(), f1.end(), 0);
+        const uint32_t rbase = roff[p0] & ~15u, fbase = foff[p0] & ~15u;
+        stage(reads, rbase, roff[p0 + np], roff[n], r0.data(), r1.data(), chunks<W>(T));
+        stage(refs, fbase, foff[p0 + np], foff[n], f0.data(), f1.data(), chunks<W>(T));
+        for (int t = 0; t < np; ++t) {
+            const int64_t p = p0 + t;
+            const int m = (int)(roff[p + 1] - roff[p]), nn = (int)(foff[p + 1] - foff[p]);
+            uint64_t A0[W], A1[W], B0[W], B1[W];
+            extract_plane<W>(reinterpret_cast<const uint32_t*>(r0.data()), (int)(roff[p] - rbase), m, A0);
+            extract_plane<W>(reinterpret_cast<const uint32_t*>(r1.data()), (int)(roff[p] - rbase), m, A1);
+            extract_plane<W>(reinterpret_cast<const uint32_t*>(f0.data()), (int)(foff[p] - fbase), nn, B0);
+            extract_plane<W>(reinterpret_cast<const uint32_t*>(f1.data()), (int)(foff[p] - fbase), nn, B1);
+            const NwBand bd = nw_band(m, nn, 1, 1, bound ? bound[p] : -1);
+            const bool windowed = bd.hi - bd.lo + 1 <= 64;
+            nwin += windowed;
+            penalty[p] = myers_forward<W>(A0, A1, B0, B1, m, nn, ops_stage ? tb.data() : nullptr, windowed, bd.hi);
+            if (ops_stage)
+                nops[p] = (uint32_t)myers_traceback<W>(A0, A1, B0, B1, m, nn, tb.data(), windowed, bd.hi, ops_stage + (size_t)p * stride, stride);
+        }
+    }
+    if (n_windowed) *n_windowed = nwin;
+    return 0;
+}
+
 }  // namespace
 
 extern "C" {
+
+int sim_myers_batch(int W, int T, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, const uint32_t* foff,
+                    int64_t n, const int32_t* bound, int32_t* penalty, uint16_t* ops_stage, int stride, uint32_t* nops,
+                    int64_t* n_windowed) {
+    switch (W) {
+        case 1: return sim_myers<1>(reads, roff, refs, foff, n, T, bound, penalty, ops_stage, stride, nops, n_windowed);
+        case 2: return sim_myers<2>(reads, roff, refs, foff, n, T, bound, penalty, ops_stage, stride, nops, n_windowed);
+        case 3: return sim_myers<3>(reads, roff, refs, foff, n, T, bound, penalty, ops_stage, stride, nops, n_windowed);
+        case 4: return sim_myers<4>(reads, roff, refs, foff, n, T, bound, penalty, ops_stage, stride, nops, n_windowed);
+    }
+    return -1;
+}
 
 int sim_nw_batch(int W, int T, int x, int o, int e, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs,
                  const uint32_t* foff, int64_t n, const int32_t* bound, int32_t* penalty, uint16_t* ops_stage, int stride,

@@ -30,6 +30,36 @@ def test_nw_logic_matches_oracle(ol, host_sim, W):
     assert [ol.render_ops(v) for v in ops] == ol.render_all(r["ops"], r["op_off"])
 
 
+@pytest.mark.parametrize("W", [1, 2, 3, 4])
+def test_unit_penalty_bitvector_nw_matches_oracle(ol, host_sim, W):
+    """The Myers-column verifier (x=o=e=1) gives the Gotoh oracle's penalty AND its traceback, op for op."""
+    rng = np.random.default_rng(950 + W)
+    for max_err, indel in ((0.05, 0.1), (0.3, 0.4), (0.9, 0.5)):
+        b = ol.random_batch(rng, 600, 0, 64 * W, max_err, indel, 64 * W)
+        r = ol.oracle_nw(b, 1, 1, 1, threads=4)
+        pen, ops = sim_lib.sim_myers(host_sim, b, W)
+        assert pen.tolist() == r["penalty"].tolist()
+        assert [ol.render_ops(v) for v in ops] == ol.render_all(r["ops"], r["op_off"])
+        pen2, _ = sim_lib.sim_myers(host_sim, b, W, want_ops=False)
+        assert pen2.tolist() == pen.tolist()
+        # with an upper bound (greedy penalty / the optimum itself / optimum + slack) the traceback vectors are kept
+        # as 64-bit windows around the band whenever it has <= 64 diagonals: same answers, op for op
+        g = ol.oracle_greedy(b, ol.make_params(3, 1, 1, 1, W))["cost"]
+        keep = np.abs(b.ref_off[1:].astype(np.int64) - b.ref_off[:-1] - (b.read_off[1:].astype(np.int64) - b.read_off[:-1])) <= 50
+        for bound in (np.where(keep, g, 10**6).astype(np.int32), r["penalty"].astype(np.int32), (r["penalty"] + 7).astype(np.int32)):
+            pen3, ops3 = sim_lib.sim_myers(host_sim, b, W, bound=bound)
+            assert pen3.tolist() == r["penalty"].tolist()
+            assert [ol.render_ops(v) for v in ops3] == ol.render_all(r["ops"], r["op_off"])
+        assert sim_lib.sim_myers.last_windowed > 0
+    # unrelated strings of very different lengths (whole-matrix paths), and empty sides
+    pairs = [(b"", b""), (b"ACGT", b""), (b"", b"ACGT"), (b"A" * (64 * W), b"T" * (64 * W)), (b"ACGT" * (16 * W), b"TGCA" * 5)]
+    b = ol.Batch.from_pairs(pairs)
+    r = ol.oracle_nw(b, 1, 1, 1)
+    pen, ops = sim_lib.sim_myers(host_sim, b, W)
+    assert pen.tolist() == r["penalty"].tolist()
+    assert [ol.render_ops(v) for v in ops] == ol.render_all(r["ops"], r["op_off"])
+
+
 def test_coverage_logic_matches_oracle(ol, host_sim):
     host_sim.sim_coverage.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int]
     rng = np.random.default_rng(31)
