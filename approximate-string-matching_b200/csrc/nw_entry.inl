@@ -11,34 +11,42 @@ int launch_nw_w(gasma_ctx* ctx, const uint8_t* reads, const uint32_t* roff, cons
     const bool want_ops = stage != nullptr;
     int rc;
     if ((rc = reserve(ctx, ctx->nw_deferred, (size_t)n * 4))) return rc;
-    // traceback scratch of the fast kernel: bounded to ~1 GiB by processing the batch in chunks
-    const int64_t chunk = want_ops ? ((int64_t)1 << 30) / ((int64_t)BITS * nw_tb_words_fast<W>() * 4) : n;
-    if (want_ops && (rc = reserve(ctx, ctx->nw_tb, (size_t)(n < chunk ? n : chunk) * BITS * nw_tb_words_fast<W>() * 4))) return rc;
     const int nslots = W <= 2 ? 8192 : 4096;
     if ((rc = reserve(ctx, ctx->nw_pool_hi, (size_t)nslots * 2 * (2 * BITS + 2) * 4))) return rc;
     if (want_ops && (rc = reserve(ctx, ctx->nw_pool_tb, (size_t)nslots * BITS * nw_tb_words_wide<W>() * 4))) return rc;
     if (ctx->kp.x == 1 && ctx->kp.o == 1 && ctx->kp.e == 1) {
-        // unit penalties (the benchmark's configuration): bit-vector columns, exact without a band
-        const int64_t per_pair = (int64_t)myers_tb_words<W>() * 4;
-        const int64_t mchunk = want_ops ? ((int64_t)1 << 30) / per_pair : n;
-        if (want_ops && (rc = reserve(ctx, ctx->nw_tb, (size_t)(n < mchunk ? n : mchunk) * per_pair))) return rc;
+        // unit penalties (the benchmark's configuration): bit-vector columns, exact without a bound.
+        // pass 1: penalties; pass 2 (only when the CIGAR is wanted): traceback with shared-memory windows
         auto mk = nw_myers_kernel<W, T>;
         const size_t msmem = myers_smem_bytes<W>(T);
         CU(cudaFuncSetAttribute(mk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msmem));
         cudaEvent_t* mev = ctx->ev[1][ctx->ev_count[1] % gasma_ctx::kRing];
         CU(cudaEventRecord(mev[0], ctx->stream));
-        for (int64_t first = 0; first < n; first += mchunk) {
-            const int64_t count = n - first < mchunk ? n - first : mchunk;
-            mk<<<(unsigned)((count + T - 1) / T), T, msmem, ctx->stream>>>(reads, roff, refs, foff, (long long)n, (long long)first,
-                                                                          (long long)count, bound, penalty, (uint32_t*)ctx->nw_tb.p,
-                                                                          stage, stride, nops, misc);
+        mk<<<(unsigned)((n + T - 1) / T), T, msmem, ctx->stream>>>(reads, roff, refs, foff, (long long)n, penalty, misc);
+        CU(cudaGetLastError());
+        ctx->launches++;
+        if (want_ops) {
+            constexpr int TT = 64;
+            auto tk = nw_myers_trace_kernel<W, TT>;
+            const size_t tsmem = myers_trace_smem_bytes<W>(TT);
+            CU(cudaFuncSetAttribute(tk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsmem));
+            CU(cudaMemsetAsync(dcount, 0, 4, ctx->stream));
+            tk<<<(unsigned)((n + TT - 1) / TT), TT, tsmem, ctx->stream>>>(reads, roff, refs, foff, (long long)n, penalty, stage, stride,
+                                                                        nops, (uint32_t*)ctx->nw_deferred.p, dcount);
             CU(cudaGetLastError());
-            ctx->launches++;
+            nw_wide_kernel<W><<<nslots / 128, 128, 0, ctx->stream>>>(
+                1, 1, 1, reads, roff, refs, foff, penalty, penalty, (int32_t*)ctx->nw_pool_hi.p, (uint32_t*)ctx->nw_pool_tb.p, nslots,
+                stage, stride, nops, (const uint32_t*)ctx->nw_deferred.p, dcount);
+            CU(cudaGetLastError());
+            ctx->launches += 2;
         }
         CU(cudaEventRecord(mev[1], ctx->stream));
         ctx->ev_count[1]++;
         return GASMA_OK;
     }
+    // traceback scratch of the banded Gotoh kernel: bounded to ~1 GiB by processing the batch in chunks
+    const int64_t chunk = want_ops ? ((int64_t)1 << 30) / ((int64_t)BITS * nw_tb_words_fast<W>() * 4) : n;
+    if (want_ops && (rc = reserve(ctx, ctx->nw_tb, (size_t)(n < chunk ? n : chunk) * BITS * nw_tb_words_fast<W>() * 4))) return rc;
     CU(cudaMemsetAsync(dcount, 0, 4, ctx->stream));
     auto kern = nw_kernel<W, T>;
     const size_t smem = nw_smem_bytes<W>(T);

@@ -93,7 +93,7 @@ template <int W>
 __global__ void __launch_bounds__(128)
 nw_wide_kernel(int x, int o, int e, const uint8_t* __restrict__ reads, const uint32_t* __restrict__ read_off,
                const uint8_t* __restrict__ refs, const uint32_t* __restrict__ ref_off,
-               const int32_t* __restrict__ bound, int32_t* __restrict__ penalty,
+               const int32_t* bound, int32_t* penalty,   // may alias (pass 2 of the unit-penalty verifier)
                int32_t* __restrict__ pool_hi, uint32_t* __restrict__ pool_tb, int nslots,
                uint16_t* __restrict__ ops_stage, int ops_stride, uint32_t* __restrict__ nops_out,
                const uint32_t* __restrict__ deferred, const uint32_t* __restrict__ deferred_count) {
@@ -133,22 +133,21 @@ nw_wide_kernel(int x, int o, int e, const uint8_t* __restrict__ reads, const uin
     }
 }
 
-// Unit-penalty verifier (x = o = e = 1): Myers bit-vector columns, one pair per thread, no band needed.
-// tb: per-pair traceback vectors, pair p of this launch uses tb + (p - first) * myers_tb_words<W>() words.
-template <int W>
-__host__ __device__ constexpr int myers_tb_words() { return 64 * W * 4 * W; }   // 64W columns x (DG + UP) x 2W words
-
+// Unit-penalty verifier (x = o = e = 1), pass 1: Myers bit-vector columns, penalty only, one pair per thread.
 template <int W>
 __host__ __device__ constexpr size_t myers_smem_bytes(int tile) {
     return 4 * (size_t)stream_elems<W>(tile) * 2 + 2 * (size_t)(tile + 1) * 4 + 64;
+}
+// pass 2 adds the per-alignment traceback windows: 64W columns x (DG, UP) x 4 bytes
+template <int W>
+__host__ __device__ constexpr size_t myers_trace_smem_bytes(int tile) {
+    return myers_smem_bytes<W>(tile) + (size_t)64 * W * 2 * 4 * tile;
 }
 
 template <int W, int T>
 __global__ void __launch_bounds__(T)
 nw_myers_kernel(const uint8_t* __restrict__ reads, const uint32_t* __restrict__ read_off, const uint8_t* __restrict__ refs,
-                const uint32_t* __restrict__ ref_off, long long n, long long first, long long count,
-                const int32_t* __restrict__ bound, int32_t* __restrict__ penalty, uint32_t* __restrict__ tb, uint16_t* __restrict__ ops_stage, int ops_stride,
-                uint32_t* __restrict__ nops_out, uint32_t* __restrict__ status) {
+                const uint32_t* __restrict__ ref_off, long long n, int32_t* __restrict__ penalty, uint32_t* __restrict__ status) {
     constexpr int BITS = 64 * W;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint16_t* s_r0 = reinterpret_cast<uint16_t*>(smem_raw);
@@ -159,9 +158,8 @@ nw_myers_kernel(const uint8_t* __restrict__ reads, const uint32_t* __restrict__ 
     uint32_t* s_foff = s_roff + (T + 1);
 
     const int tid = threadIdx.x;
-    const long long p0 = first + (long long)blockIdx.x * T;
-    const long long pend = first + count;
-    const int np = (int)((pend - p0) < (long long)T ? (pend - p0) : (long long)T);
+    const long long p0 = (long long)blockIdx.x * T;
+    const int np = (int)((n - p0) < (long long)T ? (n - p0) : (long long)T);
     for (int i = tid; i <= np; i += T) { s_roff[i] = read_off[p0 + i]; s_foff[i] = ref_off[p0 + i]; }
     for (int i = tid; i < stream_elems<W>(T); i += T) { s_r0[i] = 0; s_r1[i] = 0; s_f0[i] = 0; s_f1[i] = 0; }
     __syncthreads();
@@ -178,7 +176,6 @@ nw_myers_kernel(const uint8_t* __restrict__ reads, const uint32_t* __restrict__ 
         if (!ok) st |= kStatusTile;
         if (m > BITS || nn > BITS) st |= kStatusLength;
         int pen = INT32_MIN;
-        uint32_t cnt = 0;
         if (st == 0) {
             uint64_t A0[W], A1[W], B0[W], B1[W];
             const int rbit = (int)(s_roff[tid] - rbase), fbit = (int)(s_foff[tid] - fbase);
@@ -186,19 +183,67 @@ nw_myers_kernel(const uint8_t* __restrict__ reads, const uint32_t* __restrict__ 
             extract_plane<W>(reinterpret_cast<const uint32_t*>(s_r1), rbit, m, A1);
             extract_plane<W>(reinterpret_cast<const uint32_t*>(s_f0), fbit, nn, B0);
             extract_plane<W>(reinterpret_cast<const uint32_t*>(s_f1), fbit, nn, B1);
-            uint32_t* my_tb = ops_stage ? tb + (size_t)(p - first) * myers_tb_words<W>() : nullptr;
-            const NwBand bd = nw_band(m, nn, 1, 1, bound ? bound[p] : -1);
-            const bool windowed = bd.hi - bd.lo + 1 <= 64;
-            pen = myers_forward<W>(A0, A1, B0, B1, m, nn, my_tb, windowed, bd.hi);
-            if (ops_stage)
-                cnt = (uint32_t)myers_traceback<W>(A0, A1, B0, B1, m, nn, my_tb, windowed, bd.hi,
-                                                   ops_stage + (size_t)p * ops_stride, ops_stride);
+            pen = myers_forward<W>(A0, A1, B0, B1, m, nn);
         }
         penalty[p] = pen;
-        if (nops_out) nops_out[p] = cnt;
     }
     const uint32_t wst = __reduce_or_sync(0xffffffffu, st);
     if (wst && (tid & 31) == 0) atomicOr(status, wst);
+}
+
+// Pass 2: traceback ops.  `penalty` holds the exact optimum of every pair (pass 1).  Pairs whose band has more than
+// 32 diagonals are appended to `deferred` for nw_wide_kernel (general Gotoh, same traceback rule).
+template <int W, int T>
+__global__ void __launch_bounds__(T)
+nw_myers_trace_kernel(const uint8_t* __restrict__ reads, const uint32_t* __restrict__ read_off, const uint8_t* __restrict__ refs,
+                      const uint32_t* __restrict__ ref_off, long long n, const int32_t* __restrict__ penalty,
+                      uint16_t* __restrict__ ops_stage, int ops_stride, uint32_t* __restrict__ nops_out,
+                      uint32_t* __restrict__ deferred, uint32_t* __restrict__ deferred_count) {
+    constexpr int BITS = 64 * W;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint32_t* s_tb = reinterpret_cast<uint32_t*>(smem_raw);                       // [(col*2 + kind)][T]
+    uint16_t* s_r0 = reinterpret_cast<uint16_t*>(s_tb + (size_t)BITS * 2 * T);
+    uint16_t* s_r1 = s_r0 + stream_elems<W>(T);
+    uint16_t* s_f0 = s_r1 + stream_elems<W>(T);
+    uint16_t* s_f1 = s_f0 + stream_elems<W>(T);
+    uint32_t* s_roff = reinterpret_cast<uint32_t*>(s_f1 + stream_elems<W>(T));
+    uint32_t* s_foff = s_roff + (T + 1);
+
+    const int tid = threadIdx.x;
+    const long long p0 = (long long)blockIdx.x * T;
+    const int np = (int)((n - p0) < (long long)T ? (n - p0) : (long long)T);
+    for (int i = tid; i <= np; i += T) { s_roff[i] = read_off[p0 + i]; s_foff[i] = ref_off[p0 + i]; }
+    for (int i = tid; i < stream_elems<W>(T); i += T) { s_r0[i] = 0; s_r1[i] = 0; s_f0[i] = 0; s_f1[i] = 0; }
+    __syncthreads();
+    const uint32_t rbase = s_roff[0] & ~15u, fbase = s_foff[0] & ~15u;
+    stage_tile(reads, rbase, s_roff[np], read_off[n], s_r0, s_r1, stream_chunks<W>(T), tid, T);
+    stage_tile(refs, fbase, s_foff[np], ref_off[n], s_f0, s_f1, stream_chunks<W>(T), tid, T);
+    __syncthreads();
+
+    if (tid < np) {
+        const long long p = p0 + tid;
+        const int m = (int)(s_roff[tid + 1] - s_roff[tid]);
+        const int nn = (int)(s_foff[tid + 1] - s_foff[tid]);
+        const int pen = penalty[p];
+        uint32_t cnt = 0;
+        if (pen != INT32_MIN) {   // INT32_MIN: rejected by pass 1 (status already raised there)
+            const NwBand bd = nw_band(m, nn, 1, 1, pen);
+            if (bd.hi - bd.lo + 1 > 32) {
+                deferred[atomicAdd(deferred_count, 1u)] = (uint32_t)p;
+            } else {
+                uint64_t A0[W], A1[W], B0[W], B1[W];
+                const int rbit = (int)(s_roff[tid] - rbase), fbit = (int)(s_foff[tid] - fbase);
+                extract_plane<W>(reinterpret_cast<const uint32_t*>(s_r0), rbit, m, A0);
+                extract_plane<W>(reinterpret_cast<const uint32_t*>(s_r1), rbit, m, A1);
+                extract_plane<W>(reinterpret_cast<const uint32_t*>(s_f0), fbit, nn, B0);
+                extract_plane<W>(reinterpret_cast<const uint32_t*>(s_f1), fbit, nn, B1);
+                myers_forward_w32<W>(A0, A1, B0, B1, m, nn, s_tb + tid, T, bd.hi);
+                cnt = (uint32_t)myers_traceback_w32<W>(A0, A1, B0, B1, m, nn, s_tb + tid, T, bd.hi,
+                                                       ops_stage + (size_t)p * ops_stride, ops_stride);
+            }
+        }
+        nops_out[p] = cnt;
+    }
 }
 
 // per-tile sums of an op-count array (input of scan_tiles_kernel)

@@ -17,11 +17,12 @@
 // because H[i][j] - H[i-1][j-1] = dv_j(i) + dh_j(i-1) is 0 or 1, is 0 on a match, and a mismatching diagonal is
 // optimal exactly when that difference is 1.
 //
-// Traceback storage.  An optimal path stays on the diagonals d = j - i of nw_band() (nw.cuh) whenever an upper bound
-// on the optimum is known (the greedy penalty), so of each column only the rows i in [j-hi, j-lo] can ever be
-// visited.  If that band has at most 64 diagonals, a 64-bit WINDOW of DG and UP starting at row j-hi is kept per
-// column (16 bytes instead of 16W): the kernel is bound by this scratch traffic, not by arithmetic.  Wider bands
-// (or no bound) keep the full vectors.
+// Traceback storage.  The verifier runs in two passes: a penalty-only pass (no memory traffic at all), then, when
+// the CIGAR is wanted, a second pass that knows the exact optimum.  An optimal path stays on the diagonals
+// d = j - i of nw_band(optimum) (nw.cuh), at most optimum+1 of them, so of each column only the rows
+// i in [j-hi, j-lo] can be visited; when the band has <= 32 diagonals one 32-bit WINDOW of DG and of UP per column
+// (8 bytes) is all the walk back needs, and a whole alignment's traceback fits in shared memory.  Wider bands go
+// to the general Gotoh kernel (same traceback rule).
 #pragma once
 #include "common.cuh"
 #include "nw.cuh"
@@ -79,30 +80,12 @@ GASMA_HD uint32_t funnel32(uint32_t lo, uint32_t hi, int s) {  // low word of (h
 #endif
 }
 
-// bits [s, s+64) of an NW32-word vector (zeros beyond it), s >= 0
-template <int NW32>
-GASMA_HD void window64_of(const uint32_t v[NW32], int s, uint32_t& lo, uint32_t& hi) {
-    const int idx = s >> 5, sh = s & 31;
-    uint32_t x0 = 0u, x1 = 0u, x2 = 0u;
-#pragma unroll
-    for (int w = 0; w < NW32; ++w) {
-        if (w == idx) x0 = v[w];
-        if (w == idx + 1) x1 = v[w];
-        if (w == idx + 2) x2 = v[w];
-    }
-    lo = funnel32(x0, x1, sh);
-    hi = funnel32(x1, x2, sh);
-}
-
 // first row (0-based bit index) of the window kept for column j0 (0-based) when the band's top diagonal is hi
 GASMA_HD int myers_window_start(int j0, int hi) { return imax(0, j0 - hi); }
 
-// Forward pass.  Returns the optimal penalty.  tb (optional, 16-byte aligned) receives per column j0 = 0..n-1
-//   windowed:  4 words  {DG window lo, hi, UP window lo, hi}                       at tb[j0 * 4]
-//   full:      NW32 words of DG then NW32 words of UP (= Pv)                       at tb[j0 * 2 * NW32]
+// Penalty-only forward pass: H[m][n].
 template <int W>
-GASMA_HD int myers_forward(const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W], const uint64_t B1[W], int m, int n,
-                           uint32_t* tb, bool windowed, int band_hi) {
+GASMA_HD int myers_forward(const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W], const uint64_t B1[W], int m, int n) {
     constexpr int NW32 = 2 * W;
     if (m == 0) return n;
     uint32_t a0[NW32], a1[NW32], pv[NW32], mv[NW32];
@@ -127,41 +110,66 @@ GASMA_HD int myers_forward(const uint64_t A0[W], const uint64_t A1[W], const uin
         uint32_t eq[NW32], dg[NW32];
 #pragma unroll
         for (int w = 0; w < NW32; ++w) eq[w] = ~(a0[w] ^ k0) & ~(a1[w] ^ k1);
-        score += myers_column<NW32>(eq, pv, mv, dg, m);
-        if (tb && windowed) {
-            const int s0 = myers_window_start(j, band_hi);
-            uint32_t t0, t1, t2, t3;
-            window64_of<NW32>(dg, s0, t0, t1);
-            window64_of<NW32>(pv, s0, t2, t3);
-            uint32_t* col = tb + (size_t)j * 4;
-#if defined(__CUDA_ARCH__)
-            *reinterpret_cast<uint4*>(col) = make_uint4(t0, t1, t2, t3);
-#else
-            col[0] = t0; col[1] = t1; col[2] = t2; col[3] = t3;
-#endif
-        } else if (tb) {
-            uint32_t* col = tb + (size_t)j * 2 * NW32;
-#if defined(__CUDA_ARCH__)
-            uint32_t t[4 * W];   // one column = 16W bytes = W 16-byte stores
-#pragma unroll
-            for (int w = 0; w < NW32; ++w) { t[w] = dg[w]; t[NW32 + w] = pv[w]; }
-#pragma unroll
-            for (int q = 0; q < W; ++q)
-                reinterpret_cast<uint4*>(col)[q] = make_uint4(t[4 * q], t[4 * q + 1], t[4 * q + 2], t[4 * q + 3]);
-#else
-            for (int w = 0; w < NW32; ++w) { col[w] = dg[w]; col[NW32 + w] = pv[w]; }
-#endif
-        }
+        score += myers_column<NW32>(eq, pv, mv, dg, m);   // dg is dead here and compiled away
     }
     return score;
 }
 
-// Traceback from (m,n); same output convention as nw_traceback (nw.cuh): run-length ops (3 '=', 4 'X', 1 'I',
-// 2 'D') written back to front into row[cap-cnt .. cap); returns cnt.
+// ---- narrow-band variant: 32-bit windows kept in shared memory -----------------------------------------
+// With the exact optimum known (a penalty-only pass), nw_band() has at most penalty+1 diagonals; when that is
+// <= 32 the traceback needs one 32-bit window of DG and of UP per column: 8 bytes, small enough to keep a whole
+// alignment's traceback in shared memory (tb[(j0*2 + kind) * stride], one column of threads per alignment), so the
+// walk back reads shared memory instead of chasing one DRAM sector per step.
+template <int NW32>
+GASMA_HD uint32_t window32_of(const uint32_t v[NW32], int s) {
+    const int idx = s >> 5, sh = s & 31;
+    uint32_t x0 = 0u, x1 = 0u;
+#pragma unroll
+    for (int w = 0; w < NW32; ++w) {
+        if (w == idx) x0 = v[w];
+        if (w == idx + 1) x1 = v[w];
+    }
+    return funnel32(x0, x1, sh);
+}
+
 template <int W>
-GASMA_HD int myers_traceback(const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W], const uint64_t B1[W], int m,
-                             int n, const uint32_t* tb, bool windowed, int band_hi, uint16_t* row, int cap) {
+GASMA_HD int myers_forward_w32(const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W], const uint64_t B1[W], int m,
+                               int n, uint32_t* tb, int stride, int band_hi) {
     constexpr int NW32 = 2 * W;
+    if (m == 0) return n;
+    uint32_t a0[NW32], a1[NW32], pv[NW32], mv[NW32];
+#pragma unroll
+    for (int j = 0; j < W; ++j) {
+        a0[2 * j] = (uint32_t)A0[j]; a0[2 * j + 1] = (uint32_t)(A0[j] >> 32);
+        a1[2 * j] = (uint32_t)A1[j]; a1[2 * j + 1] = (uint32_t)(A1[j] >> 32);
+    }
+#pragma unroll
+    for (int w = 0; w < NW32; ++w) { pv[w] = 0xFFFFFFFFu; mv[w] = 0u; }
+    int score = m;
+    uint64_t b0 = 0, b1 = 0;
+    for (int j = 0; j < n; ++j) {
+        if ((j & 63) == 0) {
+#pragma unroll
+            for (int q = 0; q < W; ++q)
+                if (q == (j >> 6)) { b0 = B0[q]; b1 = B1[q]; }
+        }
+        const uint32_t k0 = (uint32_t)0 - (uint32_t)(b0 & 1ull), k1 = (uint32_t)0 - (uint32_t)(b1 & 1ull);
+        b0 >>= 1;
+        b1 >>= 1;
+        uint32_t eq[NW32], dg[NW32];
+#pragma unroll
+        for (int w = 0; w < NW32; ++w) eq[w] = ~(a0[w] ^ k0) & ~(a1[w] ^ k1);
+        score += myers_column<NW32>(eq, pv, mv, dg, m);
+        const int s0 = myers_window_start(j, band_hi);
+        tb[(size_t)(2 * j) * stride] = window32_of<NW32>(dg, s0);
+        tb[(size_t)(2 * j + 1) * stride] = window32_of<NW32>(pv, s0);
+    }
+    return score;
+}
+
+template <int W>
+GASMA_HD int myers_traceback_w32(const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W], const uint64_t B1[W], int m,
+                                 int n, const uint32_t* tb, int stride, int band_hi, uint16_t* row, int cap) {
     int i = m, j = n, cnt = 0, cur = -1, run = 0;
     auto push = [&](int code, int len) {
         if (code == cur) { run += len; return; }
@@ -169,25 +177,13 @@ GASMA_HD int myers_traceback(const uint64_t A0[W], const uint64_t A1[W], const u
         cur = code; run = len;
     };
     while (i > 0 && j > 0) {
-        uint32_t dgw, upw;
-        int b;
-        if (windowed) {
-            const uint32_t* col = tb + (size_t)(j - 1) * 4;
-            const int r = (i - 1) - myers_window_start(j - 1, band_hi);   // 0..63 on any optimal path
-            b = r & 31;
-            dgw = col[r >> 5];
-            upw = col[2 + (r >> 5)];
-        } else {
-            const uint32_t* col = tb + (size_t)(j - 1) * 2 * NW32;
-            b = (i - 1) & 31;
-            dgw = col[(i - 1) >> 5];
-            upw = col[NW32 + ((i - 1) >> 5)];
-        }
+        const int b = (i - 1) - myers_window_start(j - 1, band_hi);   // 0..31 on any optimal path
+        const uint32_t dgw = tb[(size_t)(2 * (j - 1)) * stride];
         if ((dgw >> b) & 1u) {
             const int mis = (bit_of<W>(A0, i - 1) ^ bit_of<W>(B0, j - 1)) | (bit_of<W>(A1, i - 1) ^ bit_of<W>(B1, j - 1));
             push(mis ? 4 : 3, 1);
             --i; --j;
-        } else if ((upw >> b) & 1u) {
+        } else if ((tb[(size_t)(2 * (j - 1) + 1) * stride] >> b) & 1u) {
             push(1, 1);
             --i;
         } else {

@@ -38,19 +38,16 @@ def test_unit_penalty_bitvector_nw_matches_oracle(ol, host_sim, W):
         b = ol.random_batch(rng, 600, 0, 64 * W, max_err, indel, 64 * W)
         r = ol.oracle_nw(b, 1, 1, 1, threads=4)
         pen, ops = sim_lib.sim_myers(host_sim, b, W)
+        windowed = sim_lib.sim_myers.last_windowed
         assert pen.tolist() == r["penalty"].tolist()
         assert [ol.render_ops(v) for v in ops] == ol.render_all(r["ops"], r["op_off"])
         pen2, _ = sim_lib.sim_myers(host_sim, b, W, want_ops=False)
         assert pen2.tolist() == pen.tolist()
-        # with an upper bound (greedy penalty / the optimum itself / optimum + slack) the traceback vectors are kept
-        # as 64-bit windows around the band whenever it has <= 64 diagonals: same answers, op for op
-        g = ol.oracle_greedy(b, ol.make_params(3, 1, 1, 1, W))["cost"]
-        keep = np.abs(b.ref_off[1:].astype(np.int64) - b.ref_off[:-1] - (b.read_off[1:].astype(np.int64) - b.read_off[:-1])) <= 50
-        for bound in (np.where(keep, g, 10**6).astype(np.int32), r["penalty"].astype(np.int32), (r["penalty"] + 7).astype(np.int32)):
-            pen3, ops3 = sim_lib.sim_myers(host_sim, b, W, bound=bound)
-            assert pen3.tolist() == r["penalty"].tolist()
-            assert [ol.render_ops(v) for v in ops3] == ol.render_all(r["ops"], r["op_off"])
-        assert sim_lib.sim_myers.last_windowed > 0
+        # both traceback routes were exercised: 32-bit band windows and the wide (Gotoh) route
+        if max_err <= 0.3:
+            assert 0 < windowed
+        if max_err >= 0.9 and W >= 2:
+            assert windowed < b.n
     # unrelated strings of very different lengths (whole-matrix paths), and empty sides
     pairs = [(b"", b""), (b"ACGT", b""), (b"", b"ACGT"), (b"A" * (64 * W), b"T" * (64 * W)), (b"ACGT" * (16 * W), b"TGCA" * 5)]
     b = ol.Batch.from_pairs(pairs)
