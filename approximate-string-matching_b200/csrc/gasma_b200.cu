@@ -37,6 +37,11 @@ struct gasma_ctx {
     int refill_threshold = 8;   // idle threads in a warp that trigger a refill from the pool (greedy kernel)
     cudaStream_t stream = nullptr;      // stream all work goes to
     cudaStream_t own_stream = nullptr;  // created by us
+    // host-pointer calls on large batches are pipelined in slices: H2D of slice i+1 and D2H of slice i-1 overlap
+    // the kernels of slice i
+    static constexpr int kSlices = 4;
+    cudaStream_t copy_in = nullptr, copy_out = nullptr;
+    cudaEvent_t ev_in[kSlices] = {}, ev_comp[kSlices] = {}, ev_off[kSlices] = {}, ev_fence = nullptr;
     int64_t launches = 0;
     std::string err;
     // device scratch
@@ -213,6 +218,14 @@ int gasma_create(const gasma_params* params, int device, gasma_ctx** out) {
     cudaError_t e2 = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
     if (e2 != cudaSuccess) { delete c; return fail(nullptr, GASMA_E_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(e2)); }
     c->stream = c->own_stream;
+    bool aux_ok = cudaStreamCreateWithFlags(&c->copy_in, cudaStreamNonBlocking) == cudaSuccess &&
+                  cudaStreamCreateWithFlags(&c->copy_out, cudaStreamNonBlocking) == cudaSuccess &&
+                  cudaEventCreateWithFlags(&c->ev_fence, cudaEventDisableTiming) == cudaSuccess;
+    for (int i = 0; i < gasma_ctx::kSlices && aux_ok; ++i)
+        aux_ok = cudaEventCreateWithFlags(&c->ev_in[i], cudaEventDisableTiming) == cudaSuccess &&
+                 cudaEventCreateWithFlags(&c->ev_comp[i], cudaEventDisableTiming) == cudaSuccess &&
+                 cudaEventCreateWithFlags(&c->ev_off[i], cudaEventDisableTiming) == cudaSuccess;
+    if (!aux_ok) { gasma_destroy(c); return fail(nullptr, GASMA_E_CUDA, "creating copy streams / events failed"); }
     if (cudaMalloc(&c->misc.p, 64) != cudaSuccess || cudaMemset(c->misc.p, 0, 64) != cudaSuccess ||
         cudaMallocHost((void**)&c->h_misc, 128) != cudaSuccess) {
         gasma_destroy(c);
@@ -237,6 +250,14 @@ void gasma_destroy(gasma_ctx* c) {
     for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
     if (c->h_misc) cudaFreeHost(c->h_misc);
     for (auto& kind : c->ev) for (auto& pair : kind) for (auto& ev : pair) if (ev) cudaEventDestroy(ev);
+    for (int i = 0; i < gasma_ctx::kSlices; ++i) {
+        if (c->ev_in[i]) cudaEventDestroy(c->ev_in[i]);
+        if (c->ev_comp[i]) cudaEventDestroy(c->ev_comp[i]);
+        if (c->ev_off[i]) cudaEventDestroy(c->ev_off[i]);
+    }
+    if (c->ev_fence) cudaEventDestroy(c->ev_fence);
+    if (c->copy_in) cudaStreamDestroy(c->copy_in);
+    if (c->copy_out) cudaStreamDestroy(c->copy_out);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
 }
@@ -333,9 +354,11 @@ int launch_pack_w(gasma_ctx* ctx, const uint8_t* seqs, const uint32_t* off, int6
     return GASMA_OK;
 }
 
+// carry_ops: op_off continues from the running total left by the previous call (slices of one batch share one
+// CSR array); otherwise it starts at 0.
 int greedy_dev_impl(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_read_off, const char* d_refs,
                     const uint32_t* d_ref_off, int64_t n, int32_t* d_cost, gasma_cigar_op* d_ops, int64_t ops_cap,
-                    uint32_t* d_op_off) {
+                    uint32_t* d_op_off, bool carry_ops = false) {
     if (!ctx) return GASMA_E_ARG;
     if (n < 0 || n > (int64_t)1 << 31) return fail(ctx, GASMA_E_ARG, "n_pairs out of range");
     if (!d_read_off || !d_ref_off || !d_cost) return fail(ctx, GASMA_E_ARG, "null offsets/cost pointer");
@@ -379,13 +402,75 @@ int greedy_dev_impl(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_read_
     if (want_ops) {
         tile_sums_kernel<T><<<(unsigned)ntiles, T, 0, ctx->stream>>>(nops, (long long)n, (uint32_t*)ctx->tile_sums.p);
         CU(cudaGetLastError());
-        scan_tiles_kernel<<<1, 1024, 0, ctx->stream>>>((uint32_t*)ctx->tile_sums.p, (uint32_t*)ctx->tile_bases.p, (int)ntiles, misc + 1);
+        scan_tiles_kernel<<<1, 1024, 0, ctx->stream>>>((uint32_t*)ctx->tile_sums.p, (uint32_t*)ctx->tile_bases.p, (int)ntiles, misc + 1, carry_ops ? misc + 1 : nullptr);
         CU(cudaGetLastError());
         compact_ops_kernel<T><<<(unsigned)ntiles, T, 0, ctx->stream>>>(stage, stride, nops, (uint32_t*)ctx->tile_bases.p,
                                                                      (long long)n, d_ops, (long long)ops_cap, d_op_off, 0);
         CU(cudaGetLastError());
         ctx->launches += 3;
     }
+    return GASMA_OK;
+}
+
+// Host-pointer greedy call on a large batch, pipelined over kSlices slices of pairs (slice edges on multiples of
+// 128 pairs).  Device mirrors are already reserved by the caller.  Streams: copy_in (H2D), ctx->stream (kernels),
+// copy_out (D2H); the CSR op array is shared by all slices, op_off continues across them on the device.
+int greedy_batch_pipelined(gasma_ctx* ctx, const char* reads, const uint32_t* read_off, const char* refs,
+                           const uint32_t* ref_off, int64_t n, int32_t* cost, gasma_cigar_op* ops, int64_t ops_cap,
+                           uint32_t* op_off) {
+    constexpr int S = gasma_ctx::kSlices;
+    const size_t ob = (size_t)(n + 1) * 4;
+    int64_t edge[S + 1];
+    for (int i = 0; i <= S; ++i) edge[i] = i == S ? n : ((n * i / S) / 128) * 128;
+    char* d_reads = (char*)ctx->d_reads.p;
+    char* d_refs = (char*)ctx->d_refs.p;
+    uint32_t* d_roff = (uint32_t*)ctx->d_read_off.p;
+    uint32_t* d_foff = (uint32_t*)ctx->d_ref_off.p;
+    int32_t* d_cost = (int32_t*)ctx->d_cost.p;
+    gasma_cigar_op* d_ops = ops ? (gasma_cigar_op*)ctx->d_ops.p : nullptr;
+    uint32_t* d_ooff = ops ? (uint32_t*)ctx->d_op_off.p : nullptr;
+    uint32_t* misc = (uint32_t*)ctx->misc.p;
+    // the mirrors may still be in use by earlier work on the compute stream
+    CU(cudaEventRecord(ctx->ev_fence, ctx->stream));
+    CU(cudaStreamWaitEvent(ctx->copy_in, ctx->ev_fence, 0));
+    CU(cudaStreamWaitEvent(ctx->copy_out, ctx->ev_fence, 0));
+    CU(cudaMemcpyAsync(d_roff, read_off, ob, cudaMemcpyHostToDevice, ctx->copy_in));
+    CU(cudaMemcpyAsync(d_foff, ref_off, ob, cudaMemcpyHostToDevice, ctx->copy_in));
+    for (int i = 0; i < S; ++i) {
+        const size_t r0 = read_off[edge[i]], r1 = read_off[edge[i + 1]], f0 = ref_off[edge[i]], f1 = ref_off[edge[i + 1]];
+        if (r1 > r0) CU(cudaMemcpyAsync(d_reads + r0, reads + r0, r1 - r0, cudaMemcpyHostToDevice, ctx->copy_in));
+        if (f1 > f0) CU(cudaMemcpyAsync(d_refs + f0, refs + f0, f1 - f0, cudaMemcpyHostToDevice, ctx->copy_in));
+        CU(cudaEventRecord(ctx->ev_in[i], ctx->copy_in));
+    }
+    CU(cudaMemsetAsync(misc + 1, 0, 4, ctx->stream));   // running op total
+    for (int i = 0; i < S; ++i) {
+        const int64_t lo = edge[i], cnt = edge[i + 1] - edge[i];
+        if (cnt == 0) { CU(cudaEventRecord(ctx->ev_off[i], ctx->copy_out)); continue; }
+        CU(cudaStreamWaitEvent(ctx->stream, ctx->ev_in[i], 0));
+        int rc = greedy_dev_impl(ctx, d_reads, d_roff + lo, d_refs, d_foff + lo, cnt, d_cost + lo, d_ops, ops_cap,
+                                 d_ooff ? d_ooff + lo : nullptr, /*carry_ops=*/true);
+        if (rc) return rc;
+        CU(cudaEventRecord(ctx->ev_comp[i], ctx->stream));
+        CU(cudaStreamWaitEvent(ctx->copy_out, ctx->ev_comp[i], 0));
+        CU(cudaMemcpyAsync(cost + lo, d_cost + lo, (size_t)cnt * 4, cudaMemcpyDeviceToHost, ctx->copy_out));
+        if (ops) CU(cudaMemcpyAsync(op_off + lo, d_ooff + lo, (size_t)(cnt + 1) * 4, cudaMemcpyDeviceToHost, ctx->copy_out));
+        CU(cudaEventRecord(ctx->ev_off[i], ctx->copy_out));
+    }
+    bool overflow = false;
+    if (ops) {
+        for (int i = 0; i < S; ++i) {   // as soon as a slice's offsets are on the host its ops can follow
+            if (edge[i + 1] == edge[i]) continue;
+            CU(cudaEventSynchronize(ctx->ev_off[i]));
+            const int64_t lo = op_off[edge[i]], hi = op_off[edge[i + 1]];
+            if (hi > ops_cap) { overflow = true; continue; }
+            if (hi > lo) CU(cudaMemcpyAsync(ops + lo, d_ops + lo, (size_t)(hi - lo) * 2, cudaMemcpyDeviceToHost, ctx->copy_out));
+        }
+    }
+    CU(cudaStreamSynchronize(ctx->copy_out));
+    int rc = gasma_synchronize(ctx);
+    if (rc) return rc;
+    if (overflow)
+        return fail(ctx, GASMA_E_CAPACITY, "ops buffer holds %lld ops, %lld needed", (long long)ops_cap, (long long)op_off[n]);
     return GASMA_OK;
 }
 
@@ -466,6 +551,7 @@ int gasma_greedy_batch(gasma_ctx* ctx, const char* reads, const uint32_t* read_o
         if ((rc = reserve(ctx, ctx->d_op_off, ob))) return rc;
         if ((rc = reserve(ctx, ctx->d_ops, (size_t)(ops_cap > 0 ? ops_cap : 1) * 2))) return rc;
     }
+    if (n >= 65536) return greedy_batch_pipelined(ctx, reads, read_off, refs, ref_off, n, cost, ops, ops_cap, op_off);
     if (rb) CU(cudaMemcpyAsync(ctx->d_reads.p, reads, rb, cudaMemcpyHostToDevice, ctx->stream));
     if (fb) CU(cudaMemcpyAsync(ctx->d_refs.p, refs, fb, cudaMemcpyHostToDevice, ctx->stream));
     CU(cudaMemcpyAsync(ctx->d_read_off.p, read_off, ob, cudaMemcpyHostToDevice, ctx->stream));
@@ -519,7 +605,7 @@ int gasma_generate_dev(gasma_ctx* ctx, const gasma_gen_config* cfg, uint64_t fir
     gen_lengths_kernel<T><<<(unsigned)ntiles, T, 0, ctx->stream>>>(c, first_pair, (long long)n, (uint32_t*)ctx->gen_len.p,
                                                                     (uint32_t*)ctx->tile_sums.p, d_read_off);
     CU(cudaGetLastError());
-    scan_tiles_kernel<<<1, 1024, 0, ctx->stream>>>((uint32_t*)ctx->tile_sums.p, (uint32_t*)ctx->tile_bases.p, (int)ntiles, nullptr);
+    scan_tiles_kernel<<<1, 1024, 0, ctx->stream>>>((uint32_t*)ctx->tile_sums.p, (uint32_t*)ctx->tile_bases.p, (int)ntiles, nullptr, nullptr);
     CU(cudaGetLastError());
     gen_write_kernel<T><<<(unsigned)ntiles, T, 0, ctx->stream>>>(c, first_pair, (long long)n, (uint32_t*)ctx->gen_len.p,
                                                                   (uint32_t*)ctx->tile_bases.p, d_reads, d_refs, d_ref_off);

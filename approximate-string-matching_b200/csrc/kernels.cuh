@@ -250,11 +250,11 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
 // base_in (optional, device) is added to every output so several launches can share one CSR array.
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(1024) scan_tiles_kernel(const uint32_t* __restrict__ sums, uint32_t* __restrict__ bases,
-                                                          int ntiles, uint32_t* __restrict__ total_out) {
+                                                          int ntiles, uint32_t* total_out, const uint32_t* base_in) {
     __shared__ uint32_t s_warp[32];
     __shared__ uint32_t s_carry;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) s_carry = 0;
+    if (tid == 0) s_carry = base_in ? *base_in : 0u;   // base_in may be total_out: read here, written at the end
     __syncthreads();
     for (int start = 0; start < ntiles; start += 1024) {
         const int i = start + tid;

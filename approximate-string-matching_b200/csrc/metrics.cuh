@@ -54,26 +54,45 @@ GASMA_HD int coverage_pair(const uint8_t* s1, int s1_len, const uint16_t* g_ops,
 }
 
 #if defined(__CUDACC__)
+// One pair per thread.  The tile's reads are one contiguous byte range of the CSR buffer: it is copied to shared
+// memory with coalesced 16-byte loads first, because the coverage test walks each read character by character
+// (twice) and would otherwise chase one global byte per step.  `reads_total` = logical size of the reads buffer;
+// smem_cap = bytes of dynamic shared memory (a tile that does not fit falls back to global reads).
 template <int T>
 __global__ void __launch_bounds__(T)
 metrics_kernel(const uint8_t* __restrict__ reads, const uint32_t* __restrict__ read_off, long long n,
                const int32_t* __restrict__ g_cost, const uint16_t* __restrict__ g_ops, const uint32_t* __restrict__ g_off,
                const int32_t* __restrict__ nw_pen, const uint16_t* __restrict__ n_ops, const uint32_t* __restrict__ n_off,
-               const int32_t* __restrict__ answers, unsigned long long* __restrict__ counters) {
+               const int32_t* __restrict__ answers, unsigned long long* __restrict__ counters, int smem_cap) {
+    extern __shared__ __align__(16) unsigned char s_reads[];
     __shared__ uint32_t s_acc[3];
     const int tid = threadIdx.x;
     if (tid < 3) s_acc[tid] = 0;
+    const long long p0 = (long long)blockIdx.x * T;
+    const int np = (int)((n - p0) < (long long)T ? (n - p0) : (long long)T);
+    const bool cov_wanted = g_ops && n_ops;
+    uint32_t base = 0;
+    bool staged = false;
+    if (cov_wanted) {
+        const uint32_t lo = read_off[p0], hi = read_off[p0 + np], total = read_off[n];
+        base = lo & ~15u;
+        staged = hi - base + 16u <= (uint32_t)smem_cap;   // whole 16-byte chunks are written
+        if (staged)
+            for (uint32_t a = base + 16u * tid; a < hi; a += 16u * T)
+                *reinterpret_cast<uint4*>(s_reads + (a - base)) = load_chunk(reads, a, total);
+    }
     __syncthreads();
-    const long long p = (long long)blockIdx.x * T + tid;
+    const long long p = p0 + tid;
     uint32_t nwc = 0, gc = 0, cov = 0;
     if (p < n) {
         const int nwp = nw_pen[p];
         const int correct = (answers && answers[p] != INT32_MIN) ? answers[p] : nwp;   // benchmark_utils.h:245-248
         nwc = nwp == correct;
         gc = g_cost[p] == correct;
-        if (g_ops && n_ops) {
+        if (cov_wanted) {
             const uint32_t r0 = read_off[p];
-            cov = (uint32_t)coverage_pair(reads + r0, (int)(read_off[p + 1] - r0), g_ops + g_off[p],
+            const uint8_t* s1 = staged ? s_reads + (r0 - base) : reads + r0;
+            cov = (uint32_t)coverage_pair(s1, (int)(read_off[p + 1] - r0), g_ops + g_off[p],
                                           (int)(g_off[p + 1] - g_off[p]), n_ops + n_off[p], (int)(n_off[p + 1] - n_off[p]));
         }
     }

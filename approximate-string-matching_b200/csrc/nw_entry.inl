@@ -110,7 +110,7 @@ int nw_dev_impl(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_read_off,
         uint32_t* misc = (uint32_t*)ctx->misc.p;
         tile_sums_kernel<128><<<(unsigned)ntiles, 128, 0, ctx->stream>>>(nops, (long long)n, (uint32_t*)ctx->tile_sums.p);
         CU(cudaGetLastError());
-        scan_tiles_kernel<<<1, 1024, 0, ctx->stream>>>((uint32_t*)ctx->tile_sums.p, (uint32_t*)ctx->tile_bases.p, (int)ntiles, misc + 1);
+        scan_tiles_kernel<<<1, 1024, 0, ctx->stream>>>((uint32_t*)ctx->tile_sums.p, (uint32_t*)ctx->tile_bases.p, (int)ntiles, misc + 1, nullptr);
         CU(cudaGetLastError());
         compact_ops_kernel<128><<<(unsigned)ntiles, 128, 0, ctx->stream>>>(stage, stride, nops, (uint32_t*)ctx->tile_bases.p,
                                                                          (long long)n, d_ops, (long long)ops_cap, d_op_off, 1);
@@ -181,11 +181,14 @@ int gasma_metrics_dev(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_rea
     if (n < 0 || !d_greedy_cost || !d_nw_penalty || !d_counters) return fail(ctx, GASMA_E_ARG, "bad argument");
     const bool cov = d_greedy_ops && d_nw_ops;
     if (cov && (!d_reads || !d_read_off || !d_greedy_off || !d_nw_off)) return fail(ctx, GASMA_E_ARG, "coverage needs reads and both CSR arrays");
+    if (cov && !aligned16(d_reads)) return fail(ctx, GASMA_E_ARG, "sequence buffers must be 16-byte aligned");
     CU(cudaSetDevice(ctx->device));
     if (n == 0) return GASMA_OK;
-    metrics_kernel<128><<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>(
+    const int smem_cap = 128 * ctx->params.max_length + 32;   // a tile's reads (+ alignment slack)
+    CU(cudaFuncSetAttribute(metrics_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap));
+    metrics_kernel<128><<<(unsigned)((n + 127) / 128), 128, smem_cap, ctx->stream>>>(
         (const uint8_t*)d_reads, d_read_off, (long long)n, d_greedy_cost, cov ? d_greedy_ops : nullptr, d_greedy_off,
-        d_nw_penalty, cov ? d_nw_ops : nullptr, d_nw_off, d_answers, (unsigned long long*)d_counters);
+        d_nw_penalty, cov ? d_nw_ops : nullptr, d_nw_off, d_answers, (unsigned long long*)d_counters, smem_cap);
     CU(cudaGetLastError());
     ctx->launches++;
     return GASMA_OK;

@@ -169,3 +169,42 @@ def test_gpu_full_size_properties(pkg, ol):
         assert cost[lo:lo + 2000].tolist() == r["cost"].tolist()
         seg = ops[ooff[lo]:ooff[lo + 2000]]
         assert seg.tolist() == r["ops"].tolist()
+
+
+def test_gpu_host_call_pipelined_slices(pkg, ol):
+    """Host-pointer call on a batch large enough to be pipelined in slices (H2D / kernels / D2H overlapped): one CSR
+    array across the slices, bit-equal to the oracle and to the resident (_dev) path; capacity errors still reported."""
+    import torch
+    al = pkg.Aligner()
+    rng = np.random.default_rng(4242)
+    b = ol.random_batch(rng, 70_001, 0, 128, 0.25, 0.3, 50)     # ragged lengths, empty strings, odd pair count
+    out = al.greedy_batch(b.reads, b.read_off, b.refs, b.ref_off)
+    r = ol.oracle_greedy(b, ol.make_params(), threads=8)
+    assert out["cost"].tolist() == r["cost"].tolist()
+    assert out["op_off"].tolist() == r["op_off"].tolist()
+    assert out["ops"][:out["n_ops"]].tolist() == r["ops"].tolist()
+    # costs only
+    c2 = al.greedy_batch(b.reads, b.read_off, b.refs, b.ref_off, want_ops=False)["cost"]
+    assert c2.tolist() == r["cost"].tolist()
+    # too small an ops buffer: GASMA_E_CAPACITY with op_off[n] = size needed
+    small = {"cost": np.empty(b.n, np.int32), "ops": np.empty(1000, np.uint16), "op_off": np.empty(b.n + 1, np.uint32)}
+    with pytest.raises(pkg.GasmaError) as ei:
+        al.greedy_batch(b.reads, b.read_off, b.refs, b.ref_off, ops_cap=1000, out=small)
+    assert ei.value.code == -4 and int(small["op_off"][b.n]) == len(r["ops"])
+    assert small["cost"].tolist() == r["cost"].tolist()
+    # 1M-pair synthetic batch through the host call == the resident path
+    cfg = pkg.gen_config(0x47415360, 100, 0.10)
+    reads, roff, refs, foff = al.generate(cfg, 0, 1_000_000)
+    h = al.greedy_batch(reads, roff, refs, foff)
+    d = [torch.from_numpy(x.view(np.uint8) if x.dtype == np.uint8 else x.view(np.int32)).cuda() for x in (reads, roff, refs, foff)]
+    d_reads = torch.zeros(len(reads) + 16, dtype=torch.uint8, device="cuda"); d_reads[:len(reads)] = d[0]
+    d_refs = torch.zeros(len(refs) + 16, dtype=torch.uint8, device="cuda"); d_refs[:len(refs)] = d[2]
+    d_cost = torch.empty(1_000_000, dtype=torch.int32, device="cuda")
+    d_ops = torch.empty(h["n_ops"] + 8, dtype=torch.int16, device="cuda")
+    d_ooff = torch.empty(1_000_001, dtype=torch.int32, device="cuda")
+    al.greedy_batch_dev(d_reads, d[1], d_refs, d[3], 1_000_000, d_cost, d_ops, d_ooff)
+    al.synchronize()
+    assert np.array_equal(h["cost"], d_cost.cpu().numpy())
+    assert np.array_equal(h["op_off"], d_ooff.cpu().numpy().view(np.uint32))
+    assert np.array_equal(h["ops"][:h["n_ops"]], d_ops.cpu().numpy().view(np.uint16)[:h["n_ops"]])
+    al.close()
