@@ -12,6 +12,7 @@
 #include <string>
 
 #include "kernels.cuh"
+#include "greedy_warp.cuh"
 #include "nw_kernels.cuh"
 #include "generate.cuh"
 
@@ -89,8 +90,9 @@ int reserve(gasma_ctx* ctx, DevBuf& b, size_t bytes) {
 
 int validate_params(const gasma_params* p, std::string& why) {
     if (!p) { why = "params is null"; return GASMA_E_ARG; }
-    if (p->max_length != 64 && p->max_length != 128 && p->max_length != 192 && p->max_length != 256) {
-        why = "max_length must be 64, 128, 192 or 256 (thread-per-pair kernels)";
+    if (p->max_length != 64 && p->max_length != 128 && p->max_length != 192 && p->max_length != 256 &&
+        p->max_length != 512 && p->max_length != 1024) {
+        why = "max_length must be 64, 128, 192, 256 (one alignment per thread) or 512, 1024 (one alignment per warp)";
         return GASMA_E_UNSUPPORTED;
     }
     if (p->k < 0 || p->k > GASMA_MAX_K) { why = "k outside [0, MAX_K=50]"; return GASMA_E_BAND; }
@@ -159,8 +161,32 @@ int greedy_tile_threads(const gasma_ctx* c) {   // 0 = configuration does not fi
         case 1: return 32 * greedy_warps_for<1>(c->kp.k);
         case 2: return 32 * greedy_warps_for<2>(c->kp.k);
         case 3: return 32 * greedy_warps_for<3>(c->kp.k);
-        default: return 32 * greedy_warps_for<4>(c->kp.k);
+        case 4: return 32 * greedy_warps_for<4>(c->kp.k);
+        case 8: return 4 * WarpLayout<8>::bytes_per_warp(c->kp.k) + 64 <= kMaxSmem ? 128 : 0;
+        default: return 4 * WarpLayout<16>::bytes_per_warp(c->kp.k) + 64 <= kMaxSmem ? 128 : 0;
     }
+}
+
+// one alignment per warp (max_length 512 / 1024)
+template <int W>
+int launch_greedy_warp(gasma_ctx* ctx, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, const uint32_t* foff,
+                       int64_t n, int32_t* cost, uint16_t* stage, int stride, uint32_t* nops, uint32_t* pair_counter,
+                       uint32_t* status, unsigned long long* steps) {
+    constexpr int WARPS = 4;
+    const size_t smem = WARPS * ((WarpLayout<W>::bytes_per_warp(ctx->kp.k) + 15) / 16 * 16);
+    auto kern = greedy_warp_kernel<W, WARPS>;
+    CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 0;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 32 * WARPS, smem));
+    if (per_sm < 1) return fail(ctx, GASMA_E_CUDA, "warp-per-alignment kernel does not fit an SM");
+    int64_t grid = (int64_t)ctx->sm_count * per_sm;
+    if (grid * WARPS > n) grid = (n + WARPS - 1) / WARPS;
+    CU(cudaMemsetAsync(pair_counter, 0, 4, ctx->stream));
+    kern<<<(unsigned)grid, 32 * WARPS, smem, ctx->stream>>>(ctx->kp, reads, roff, refs, foff, (long long)n, cost, stage, stride, nops,
+                                                          pair_counter, status, steps);
+    CU(cudaGetLastError());
+    ctx->launches++;
+    return GASMA_OK;
 }
 
 int check_status(gasma_ctx* ctx, uint32_t st) {
@@ -213,7 +239,7 @@ int gasma_create(const gasma_params* params, int device, gasma_ctx** out) {
     derive(c);
     if (greedy_tile_threads(c) == 0) {
         delete c;
-        return fail(nullptr, GASMA_E_UNSUPPORTED, "k=%d with max_length=%d does not fit the thread-per-pair kernel", params->k, params->max_length);
+        return fail(nullptr, GASMA_E_UNSUPPORTED, "k=%d with max_length=%d does not fit shared memory", params->k, params->max_length);
     }
     cudaError_t e2 = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
     if (e2 != cudaSuccess) { delete c; return fail(nullptr, GASMA_E_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(e2)); }
@@ -273,7 +299,7 @@ int gasma_set_band(gasma_ctx* ctx, int k) {
     if (greedy_tile_threads(ctx) == 0) {
         ctx->params.k = old;
         derive(ctx);
-        return fail(ctx, GASMA_E_UNSUPPORTED, "k=%d with max_length=%d does not fit the thread-per-pair kernel", k, ctx->params.max_length);
+        return fail(ctx, GASMA_E_UNSUPPORTED, "k=%d with max_length=%d does not fit shared memory", k, ctx->params.max_length);
     }
     return GASMA_OK;
 }
@@ -394,7 +420,9 @@ int greedy_dev_impl(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_read_
         case 1: rc = launch_greedy_w<1>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, chunk_counter, misc, steps); break;
         case 2: rc = launch_greedy_w<2>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, chunk_counter, misc, steps); break;
         case 3: rc = launch_greedy_w<3>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, chunk_counter, misc, steps); break;
-        default: rc = launch_greedy_w<4>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, chunk_counter, misc, steps); break;
+        case 4: rc = launch_greedy_w<4>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, chunk_counter, misc, steps); break;
+        case 8: rc = launch_greedy_warp<8>(ctx, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, chunk_counter, misc, steps); break;
+        default: rc = launch_greedy_warp<16>(ctx, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, chunk_counter, misc, steps); break;
     }
     if (rc) return rc;
     CU(cudaEventRecord(evp[1], ctx->stream));
@@ -497,7 +525,9 @@ int gasma_pack2bit_batch_dev(gasma_ctx* ctx, const char* d_seqs, const uint32_t*
         case 1: return launch_pack_w<1>(ctx, s, d_off, n, d_plane0, d_plane1);
         case 2: return launch_pack_w<2>(ctx, s, d_off, n, d_plane0, d_plane1);
         case 3: return launch_pack_w<3>(ctx, s, d_off, n, d_plane0, d_plane1);
-        default: return launch_pack_w<4>(ctx, s, d_off, n, d_plane0, d_plane1);
+        case 4: return launch_pack_w<4>(ctx, s, d_off, n, d_plane0, d_plane1);
+        case 8: return launch_pack_w<8>(ctx, s, d_off, n, d_plane0, d_plane1);
+        default: return launch_pack_w<16>(ctx, s, d_off, n, d_plane0, d_plane1);
     }
 }
 

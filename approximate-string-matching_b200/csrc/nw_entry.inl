@@ -84,6 +84,8 @@ int nw_dev_impl(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_read_off,
         if (d_op_off) CU(cudaMemsetAsync(d_op_off, 0, 4, ctx->stream));
         return GASMA_OK;
     }
+    if (ctx->W > 4)
+        return fail(ctx, GASMA_E_UNSUPPORTED, "the NW verifier covers max_length <= 256 (the greedy path covers 512 and 1024)");
     const int T = 128;
     const int64_t ntiles = (n + T - 1) / T;
     const int stride = 2 * ctx->params.max_length + 8;

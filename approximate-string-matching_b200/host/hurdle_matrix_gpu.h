@@ -73,12 +73,12 @@ public:
     // run(), hurdle_matrix.h:568-597
     void run() {
         const uint32_t roff[2] = {0u, (uint32_t)read_.size()}, foff[2] = {0u, (uint32_t)ref_.size()};
-        gasma_cigar_op ops[2 * 256 + 8];
+        std::vector<gasma_cigar_op> ops((size_t)(2 * max_length_ + 8));   // two ops per step at most
         uint32_t op_off[2] = {0, 0};
         int32_t cost = 0;
-        check(gasma_greedy_batch(ctx_, read_.data(), roff, ref_.data(), foff, 1, &cost, ops, (int64_t)(sizeof ops / sizeof ops[0]), op_off));
+        check(gasma_greedy_batch(ctx_, read_.data(), roff, ref_.data(), foff, 1, &cost, ops.data(), (int64_t)ops.size(), op_off));
         cost_ = cost;
-        cigar_ = render(ops, (int)op_off[1]);
+        cigar_ = render(ops.data(), (int)op_off[1]);
     }
 
     int get_cost() const { return cost_; }          // hurdle_matrix.h:677

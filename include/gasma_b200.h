@@ -34,7 +34,7 @@ extern "C" {
 
 #define GASMA_MAX_K 50          /* hurdle_matrix.h:8   MAX_K */
 #define GASMA_WORD_BITS 64
-#define GASMA_MAX_WORDS 4       /* thread-per-pair kernels: max_length <= 256 (reference: 128, utils.h:23-25) */
+#define GASMA_MAX_WORDS 16      /* max_length <= 1024 (reference: 128, utils.h:23-25); NW verifier: <= 256 */
 
 typedef enum {
     GASMA_OK = 0,
@@ -56,7 +56,7 @@ typedef struct {
     int32_t alignment_type;   /* gasma_alignment_type */
     int32_t x, o, e;          /* mismatch, gap open, gap extend (hurdle_matrix.h:478-480) */
     int32_t k;                /* band: lanes -k..k (hurdle_matrix.h:643-644) */
-    int32_t max_length;       /* 128, 192 or 256 */
+    int32_t max_length;       /* 64, 128, 192, 256: one alignment per thread; 512, 1024: one alignment per warp */
     double match_prob, mismatch_prob, indel_prob; /* hurdle_matrix.h:557-559 */
 } gasma_params;
 

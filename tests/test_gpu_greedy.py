@@ -208,3 +208,40 @@ def test_gpu_host_call_pipelined_slices(pkg, ol):
     assert np.array_equal(h["op_off"], d_ooff.cpu().numpy().view(np.uint32))
     assert np.array_equal(h["ops"][:h["n_ops"]], d_ops.cpu().numpy().view(np.uint16)[:h["n_ops"]])
     al.close()
+
+
+@pytest.mark.parametrize("W,k", [(8, 3), (8, 24), (16, 3), (16, 24), (16, 50)])
+def test_gpu_long_reads_warp_per_alignment(pkg, ol, W, k):
+    """max_length 512 / 1024 (BASELINE configs[4]: 1 kbp reads, wide band, multi-word bitmasks): the
+    one-alignment-per-warp kernel == the W-word oracle on cost and CIGAR ops, for narrow and wide bands."""
+    rng = np.random.default_rng(8000 + 10 * W + k)
+    al = pkg.Aligner(k=k, max_length=64 * W)
+    for (x, o, e, n, max_err) in [(1, 1, 1, 1500, 0.2), (2, 3, 1, 600, 0.3)]:
+        al2 = al if (x, o, e) == (1, 1, 1) else pkg.Aligner(k=k, x=x, o=o, e=e, max_length=64 * W)
+        b = ol.random_batch(rng, n, 0, 64 * W, max_err, 0.3, 50)
+        r = ol.oracle_greedy(b, ol.make_params(k, x, o, e, W), threads=8)
+        out = al2.greedy_batch(b.reads, b.read_off, b.refs, b.ref_off)
+        assert out["cost"].tolist() == r["cost"].tolist()
+        assert out["op_off"].tolist() == r["op_off"].tolist()
+        assert out["ops"][:out["n_ops"]].tolist() == r["ops"].tolist()
+        if al2 is not al:
+            al2.close()
+    # the named long-read workload: 1 kbp reads at 15 % error (exact edit count), generated on the device
+    if W == 16:
+        cfg = pkg.gen_config(0x47415370, 1000, 0.15)
+        reads, roff, refs, foff = al.generate(cfg, 0, 3000)
+        b = ol.Batch(reads, roff, refs, foff)
+        r = ol.oracle_greedy(b, ol.make_params(k, 1, 1, 1, W), threads=8)
+        out = al.greedy_batch(b.reads, b.read_off, b.refs, b.ref_off)
+        assert out["cost"].tolist() == r["cost"].tolist()
+        assert out["ops"][:out["n_ops"]].tolist() == r["ops"].tolist()
+    # packing at this width
+    seqs = rng.choice(np.frombuffer(b"ACGTNacgt", np.uint8), 64 * W * 40).astype(np.uint8)
+    off = (np.arange(41) * 64 * W).astype(np.uint32)
+    p0, p1 = al.pack2bit_batch(seqs, off)
+    for i in range(0, 40, 7):
+        e0, e1 = ol.oracle_pack(seqs[off[i]:off[i + 1]].tobytes(), W)
+        assert p0[i].tolist() == e0.tolist() and p1[i].tolist() == e1.tolist()
+    with pytest.raises(pkg.GasmaError):   # the NW verifier stops at 256 characters
+        al.nw_batch(b.reads, b.read_off, b.refs, b.ref_off)
+    al.close()
