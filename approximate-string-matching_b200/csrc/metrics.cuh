@@ -4,53 +4,78 @@
 //   total_tests++ ; nw_correct += (nw == correct) ; greedy_correct += (greedy == correct) ;
 //   greedy_coverage += covers(LCM(greedy CIGAR, threshold 1), LCM(NW CIGAR, threshold 3))
 // with long_consecutive_matching_substring (benchmark_coverage.h:26-67) and covers (:73-91).
-// Neither LCM string is materialised: both are streamed from the op lists, and covers() is the
-// subsequence test it amounts to (its length pre-check is implied by the scan).
+// Neither LCM string is materialised.  Both are subsets of the READ's positions (an LCM character is s1[index] for
+// the indices under qualifying M / '=' runs), so each CIGAR is first turned into a bitmask over read positions
+// (two toggles per run + one prefix-XOR fill: no per-character work, no data-dependent inner loops), and covers()
+// -- a greedy subsequence test -- becomes ONE loop over the read positions that every thread of a warp runs in
+// lock-step.  (The first version streamed characters out of the op lists: correct, but 7 of 32 threads active.)
 #pragma once
 #include "common.cuh"
 
 namespace gasma {
 
-// Streams the characters of long_consecutive_matching_substring(s1, ., CIGAR, threshold).
-struct LcmStream {
-    const uint16_t* ops;
-    int nops, thr;
-    const uint8_t* s1;
-    int s1_len;
-    int oi, rem, s1_index;
-    GASMA_HD void init(const uint16_t* ops_, int nops_, int thr_, const uint8_t* s1_, int s1_len_) {
-        ops = ops_; nops = nops_; thr = thr_; s1 = s1_; s1_len = s1_len_; oi = 0; rem = 0; s1_index = 0;
-    }
-    // next LCM character; false when exhausted
-    GASMA_HD bool next(uint8_t& c) {
-        while (rem == 0) {
-            if (oi >= nops) return false;
-            const int len = ops[oi] >> 3, code = ops[oi] & 7;
-            ++oi;
-            if (code == 2) continue;                               // 'D' advances the reference only
-            if (code == 1 || code == 4 || len < thr) { s1_index += len; continue; }  // 'I', 'X', short runs
-            rem = len;                                             // 'M' / '=' run of length >= threshold
-        }
-        c = s1_index < s1_len ? s1[s1_index] : (uint8_t)0;         // the reference indexes s1 unchecked (NUL at the end)
-        ++s1_index;
-        --rem;
-        return true;
-    }
-};
+constexpr int kCovWords = 8;   // read positions covered by the masks: 256 = the NW verifier's max_length
 
-// _check_coverage(s1, s2, greedyCIGAR, nwCIGAR, 1, 3), benchmark_utils.h:214-225
-GASMA_HD int coverage_pair(const uint8_t* s1, int s1_len, const uint16_t* g_ops, int g_n, const uint16_t* n_ops, int n_n) {
-    LcmStream a, b;
-    a.init(g_ops, g_n, 1, s1, s1_len);
-    b.init(n_ops, n_n, 3, s1, s1_len);
-    uint8_t cb, ca;
-    while (b.next(cb)) {
-        for (;;) {
-            if (!a.next(ca)) return 0;
-            if (ca == cb) break;
+// Positions of long_consecutive_matching_substring(s1, ., CIGAR, threshold) (benchmark_coverage.h:26-67):
+// 'D' advances the reference only; 'I', 'X' and runs shorter than the threshold advance the read without
+// contributing; 'M' / '=' runs of length >= threshold contribute their read positions.
+// mask word w lives at mask[w * stride].  Positions >= 256 are dropped (they lie beyond any read the verifier takes;
+// the reference would read the string's NUL there, which never matches an NW character).
+GASMA_HD void lcm_positions(const uint16_t* ops, int nops, int thr, uint32_t* mask, int stride) {
+    for (int w = 0; w < kCovWords; ++w) mask[w * stride] = 0u;
+    int idx = 0;
+    for (int oi = 0; oi < nops; ++oi) {
+        const int len = ops[oi] >> 3, code = ops[oi] & 7;
+        if (code == 2) continue;
+        if (!(code == 1 || code == 4 || len < thr)) {   // toggle the run's first position and the one after its last
+            if (idx < 32 * kCovWords) mask[(idx >> 5) * stride] ^= 1u << (idx & 31);
+            if (idx + len < 32 * kCovWords) mask[((idx + len) >> 5) * stride] ^= 1u << ((idx + len) & 31);
+        }
+        idx += len;
+    }
+    uint32_t carry = 0u;   // prefix XOR over all 256 bits: ones between a run's two toggles
+    for (int w = 0; w < kCovWords; ++w) {
+        uint32_t v = mask[w * stride];
+        v ^= v << 1; v ^= v << 2; v ^= v << 4; v ^= v << 8; v ^= v << 16;
+        v ^= carry;
+        carry = (v >> 31) ? 0xFFFFFFFFu : 0u;
+        mask[w * stride] = v;
+    }
+}
+
+// _check_coverage(s1, s2, greedyCIGAR, nwCIGAR, 1, 3), benchmark_utils.h:214-225; covers() benchmark_coverage.h:73-91.
+// scratch: 2 * kCovWords words for this alignment, word i at scratch[i * stride].
+GASMA_HD int coverage_pair(const uint8_t* s1, int s1_len, const uint16_t* g_ops, int g_n, const uint16_t* n_ops, int n_n,
+                           uint32_t* scratch, int stride) {
+    uint32_t* P1 = scratch;
+    uint32_t* P2 = scratch + (size_t)kCovWords * stride;
+    lcm_positions(g_ops, g_n, 1, P1, stride);
+    lcm_positions(n_ops, n_n, 3, P2, stride);
+    // j = next NW-LCM position still to be found among the greedy-LCM characters
+    int jw = 0;
+    uint32_t jword = P2[0];
+    while (jword == 0u) {
+        if (++jw >= kCovWords) return 1;   // nothing to cover
+        jword = P2[jw * stride];
+    }
+    int j = 32 * jw + ctz64((uint64_t)jword);
+    if (j >= s1_len) return 0;             // cannot happen for NW ops of this read (they consume exactly s1_len)
+    uint8_t cj = s1[j];
+    uint32_t pw = 0u;
+    for (int q = 0; q < s1_len && q < 32 * kCovWords; ++q) {
+        if ((q & 31) == 0) pw = P1[(q >> 5) * stride];
+        if (((pw >> (q & 31)) & 1u) && s1[q] == cj) {
+            jword &= jword - 1u;
+            while (jword == 0u) {
+                if (++jw >= kCovWords) return 1;
+                jword = P2[jw * stride];
+            }
+            j = 32 * jw + ctz64((uint64_t)jword);
+            if (j >= s1_len) return 0;
+            cj = s1[j];
         }
     }
-    return 1;
+    return 0;
 }
 
 #if defined(__CUDACC__)
@@ -64,8 +89,9 @@ metrics_kernel(const uint8_t* __restrict__ reads, const uint32_t* __restrict__ r
                const int32_t* __restrict__ g_cost, const uint16_t* __restrict__ g_ops, const uint32_t* __restrict__ g_off,
                const int32_t* __restrict__ nw_pen, const uint16_t* __restrict__ n_ops, const uint32_t* __restrict__ n_off,
                const int32_t* __restrict__ answers, unsigned long long* __restrict__ counters, int smem_cap) {
-    extern __shared__ __align__(16) unsigned char s_reads[];
+    extern __shared__ __align__(16) unsigned char s_reads[];   // [smem_cap] staged reads, then the position masks
     __shared__ uint32_t s_acc[3];
+    uint32_t* s_masks = reinterpret_cast<uint32_t*>(s_reads + smem_cap);   // [2 * kCovWords][T]
     const int tid = threadIdx.x;
     if (tid < 3) s_acc[tid] = 0;
     const long long p0 = (long long)blockIdx.x * T;
@@ -93,7 +119,8 @@ metrics_kernel(const uint8_t* __restrict__ reads, const uint32_t* __restrict__ r
             const uint32_t r0 = read_off[p];
             const uint8_t* s1 = staged ? s_reads + (r0 - base) : reads + r0;
             cov = (uint32_t)coverage_pair(s1, (int)(read_off[p + 1] - r0), g_ops + g_off[p],
-                                          (int)(g_off[p + 1] - g_off[p]), n_ops + n_off[p], (int)(n_off[p + 1] - n_off[p]));
+                                          (int)(g_off[p + 1] - g_off[p]), n_ops + n_off[p], (int)(n_off[p + 1] - n_off[p]),
+                                          s_masks + tid, T);
         }
     }
     nwc = __reduce_add_sync(0xffffffffu, nwc);

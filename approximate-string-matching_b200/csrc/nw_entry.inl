@@ -186,9 +186,11 @@ int gasma_metrics_dev(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_rea
     if (cov && !aligned16(d_reads)) return fail(ctx, GASMA_E_ARG, "sequence buffers must be 16-byte aligned");
     CU(cudaSetDevice(ctx->device));
     if (n == 0) return GASMA_OK;
-    const int smem_cap = 128 * ctx->params.max_length + 32;   // a tile's reads (+ alignment slack)
-    CU(cudaFuncSetAttribute(metrics_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap));
-    metrics_kernel<128><<<(unsigned)((n + 127) / 128), 128, smem_cap, ctx->stream>>>(
+    if (cov && ctx->W > 4) return fail(ctx, GASMA_E_UNSUPPORTED, "coverage counters cover max_length <= 256");
+    const int smem_cap = (128 * ctx->params.max_length + 32 + 15) / 16 * 16;   // a tile's reads (+ alignment slack)
+    const int smem_all = smem_cap + 2 * kCovWords * 128 * 4;                   // + the position masks
+    CU(cudaFuncSetAttribute(metrics_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_all));
+    metrics_kernel<128><<<(unsigned)((n + 127) / 128), 128, smem_all, ctx->stream>>>(
         (const uint8_t*)d_reads, d_read_off, (long long)n, d_greedy_cost, cov ? d_greedy_ops : nullptr, d_greedy_off,
         d_nw_penalty, cov ? d_nw_ops : nullptr, d_nw_off, d_answers, (unsigned long long*)d_counters, smem_cap);
     CU(cudaGetLastError());

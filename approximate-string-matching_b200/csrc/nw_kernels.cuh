@@ -138,10 +138,10 @@ template <int W>
 __host__ __device__ constexpr size_t myers_smem_bytes(int tile) {
     return 4 * (size_t)stream_elems<W>(tile) * 2 + 2 * (size_t)(tile + 1) * 4 + 64;
 }
-// pass 2 adds the per-alignment traceback windows: 64W columns x (DG, UP) x 4 bytes
+// pass 2 adds the per-alignment traceback windows: half of the 64W columns at a time x (DG, UP) x 4 bytes
 template <int W>
 __host__ __device__ constexpr size_t myers_trace_smem_bytes(int tile) {
-    return myers_smem_bytes<W>(tile) + (size_t)64 * W * 2 * 4 * tile;
+    return myers_smem_bytes<W>(tile) + (size_t)32 * W * 2 * 4 * tile;
 }
 
 template <int W, int T>
@@ -202,7 +202,7 @@ nw_myers_trace_kernel(const uint8_t* __restrict__ reads, const uint32_t* __restr
     constexpr int BITS = 64 * W;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint32_t* s_tb = reinterpret_cast<uint32_t*>(smem_raw);                       // [(col*2 + kind)][T]
-    uint16_t* s_r0 = reinterpret_cast<uint16_t*>(s_tb + (size_t)BITS * 2 * T);
+    uint16_t* s_r0 = reinterpret_cast<uint16_t*>(s_tb + (size_t)(BITS / 2) * 2 * T);
     uint16_t* s_r1 = s_r0 + stream_elems<W>(T);
     uint16_t* s_f0 = s_r1 + stream_elems<W>(T);
     uint16_t* s_f1 = s_f0 + stream_elems<W>(T);
@@ -237,9 +237,8 @@ nw_myers_trace_kernel(const uint8_t* __restrict__ reads, const uint32_t* __restr
                 extract_plane<W>(reinterpret_cast<const uint32_t*>(s_r1), rbit, m, A1);
                 extract_plane<W>(reinterpret_cast<const uint32_t*>(s_f0), fbit, nn, B0);
                 extract_plane<W>(reinterpret_cast<const uint32_t*>(s_f1), fbit, nn, B1);
-                myers_forward_w32<W>(A0, A1, B0, B1, m, nn, s_tb + tid, T, bd.hi);
-                cnt = (uint32_t)myers_traceback_w32<W>(A0, A1, B0, B1, m, nn, s_tb + tid, T, bd.hi,
-                                                       ops_stage + (size_t)p * ops_stride, ops_stride);
+                cnt = (uint32_t)myers_traceback_split<W>(A0, A1, B0, B1, m, nn, s_tb + tid, T, bd.hi,
+                                                         ops_stage + (size_t)p * ops_stride, ops_stride);
             }
         }
         nops_out[p] = cnt;

@@ -132,11 +132,11 @@ GASMA_HD uint32_t window32_of(const uint32_t v[NW32], int s) {
     return funnel32(x0, x1, sh);
 }
 
+// Columns [0, j_end) are computed; the windows of columns j >= j_store are kept at slot (j - j_store).
 template <int W>
 GASMA_HD int myers_forward_w32(const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W], const uint64_t B1[W], int m,
-                               int n, uint32_t* tb, int stride, int band_hi) {
+                               int j_store, int j_end, uint32_t* tb, int stride, int band_hi) {
     constexpr int NW32 = 2 * W;
-    if (m == 0) return n;
     uint32_t a0[NW32], a1[NW32], pv[NW32], mv[NW32];
 #pragma unroll
     for (int j = 0; j < W; ++j) {
@@ -147,7 +147,7 @@ GASMA_HD int myers_forward_w32(const uint64_t A0[W], const uint64_t A1[W], const
     for (int w = 0; w < NW32; ++w) { pv[w] = 0xFFFFFFFFu; mv[w] = 0u; }
     int score = m;
     uint64_t b0 = 0, b1 = 0;
-    for (int j = 0; j < n; ++j) {
+    for (int j = 0; j < j_end; ++j) {
         if ((j & 63) == 0) {
 #pragma unroll
             for (int q = 0; q < W; ++q)
@@ -160,41 +160,74 @@ GASMA_HD int myers_forward_w32(const uint64_t A0[W], const uint64_t A1[W], const
 #pragma unroll
         for (int w = 0; w < NW32; ++w) eq[w] = ~(a0[w] ^ k0) & ~(a1[w] ^ k1);
         score += myers_column<NW32>(eq, pv, mv, dg, m);
-        const int s0 = myers_window_start(j, band_hi);
-        tb[(size_t)(2 * j) * stride] = window32_of<NW32>(dg, s0);
-        tb[(size_t)(2 * j + 1) * stride] = window32_of<NW32>(pv, s0);
+        if (j >= j_store) {
+            const int s0 = myers_window_start(j, band_hi);
+            tb[(size_t)(2 * (j - j_store)) * stride] = window32_of<NW32>(dg, s0);
+            tb[(size_t)(2 * (j - j_store) + 1) * stride] = window32_of<NW32>(pv, s0);
+        }
     }
     return score;
 }
 
+// Resumable walk back: emits ops while j > j_lo (and i > 0), reading the windows stored with base column j_store.
+struct MyersTrace {
+    int i, j, cnt, cur, run;
+};
 template <int W>
-GASMA_HD int myers_traceback_w32(const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W], const uint64_t B1[W], int m,
-                                 int n, const uint32_t* tb, int stride, int band_hi, uint16_t* row, int cap) {
-    int i = m, j = n, cnt = 0, cur = -1, run = 0;
+GASMA_HD void myers_trace_segment(const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W], const uint64_t B1[W],
+                                  MyersTrace& t, int j_lo, int j_store, const uint32_t* tb, int stride, int band_hi,
+                                  uint16_t* row, int cap) {
     auto push = [&](int code, int len) {
-        if (code == cur) { run += len; return; }
-        if (cur >= 0) { ++cnt; if (cnt <= cap) row[cap - cnt] = (uint16_t)((run << 3) | cur); }
-        cur = code; run = len;
+        if (code == t.cur) { t.run += len; return; }
+        if (t.cur >= 0) { ++t.cnt; if (t.cnt <= cap) row[cap - t.cnt] = (uint16_t)((t.run << 3) | t.cur); }
+        t.cur = code; t.run = len;
     };
-    while (i > 0 && j > 0) {
-        const int b = (i - 1) - myers_window_start(j - 1, band_hi);   // 0..31 on any optimal path
-        const uint32_t dgw = tb[(size_t)(2 * (j - 1)) * stride];
-        if ((dgw >> b) & 1u) {
-            const int mis = (bit_of<W>(A0, i - 1) ^ bit_of<W>(B0, j - 1)) | (bit_of<W>(A1, i - 1) ^ bit_of<W>(B1, j - 1));
+    while (t.i > 0 && t.j > j_lo) {
+        const int b = (t.i - 1) - myers_window_start(t.j - 1, band_hi);   // 0..31 on any optimal path
+        const int slot = t.j - 1 - j_store;
+        if ((tb[(size_t)(2 * slot) * stride] >> b) & 1u) {
+            const int mis = (bit_of<W>(A0, t.i - 1) ^ bit_of<W>(B0, t.j - 1)) | (bit_of<W>(A1, t.i - 1) ^ bit_of<W>(B1, t.j - 1));
             push(mis ? 4 : 3, 1);
-            --i; --j;
-        } else if ((tb[(size_t)(2 * (j - 1) + 1) * stride] >> b) & 1u) {
+            --t.i; --t.j;
+        } else if ((tb[(size_t)(2 * slot + 1) * stride] >> b) & 1u) {
             push(1, 1);
-            --i;
+            --t.i;
         } else {
             push(2, 1);
-            --j;
+            --t.j;
         }
     }
-    if (i > 0) push(1, i);
-    if (j > 0) push(2, j);
-    push(-2, 0);  // flush
-    return cnt;
+}
+// the boundary tail (first row / first column) and the flush of the last run; returns the op count
+GASMA_HD int myers_trace_finish(MyersTrace& t, uint16_t* row, int cap) {
+    auto push = [&](int code, int len) {
+        if (code == t.cur) { t.run += len; return; }
+        if (t.cur >= 0) { ++t.cnt; if (t.cnt <= cap) row[cap - t.cnt] = (uint16_t)((t.run << 3) | t.cur); }
+        t.cur = code; t.run = len;
+    };
+    if (t.i > 0) push(1, t.i);
+    if (t.j > 0) push(2, t.j);
+    push(-2, 0);
+    return t.cnt;
+}
+
+// Whole traceback of one alignment with HALF the columns resident: the upper half of the columns is stored and
+// walked first, then the lower half is recomputed into the same slots (1.5x the column work for half the shared
+// memory, i.e. twice the alignments in flight per SM).  tb holds 2 * ((n + 1) / 2) words per alignment.
+template <int W>
+GASMA_HD int myers_traceback_split(const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W], const uint64_t B1[W],
+                                   int m, int n, uint32_t* tb, int stride, int band_hi, uint16_t* row, int cap) {
+    MyersTrace t{m, n, 0, -1, 0};
+    if (m > 0 && n > 0) {
+        const int split = n / 2;
+        myers_forward_w32<W>(A0, A1, B0, B1, m, split, n, tb, stride, band_hi);
+        myers_trace_segment<W>(A0, A1, B0, B1, t, split, split, tb, stride, band_hi, row, cap);
+        if (t.i > 0 && t.j > 0) {
+            myers_forward_w32<W>(A0, A1, B0, B1, m, 0, t.j, tb, stride, band_hi);
+            myers_trace_segment<W>(A0, A1, B0, B1, t, 0, 0, tb, stride, band_hi, row, cap);
+        }
+    }
+    return myers_trace_finish(t, row, cap);
 }
 
 }  // namespace gasma

@@ -369,7 +369,7 @@ def run_b200(a):
     }
     if full is not None:
         line["full_path"] = full
-    if not a.no_cpu_baseline:
+    if not a.no_cpu_baseline and world == 1:   # the CPU path is timed beside the 1-GPU run only
         line["cpu_baseline"] = cpu_baseline(hb, a, ml)
     if world > 1:
         dist.destroy_process_group()

@@ -188,9 +188,8 @@ int sim_myers(const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, c
             const NwBand bd = nw_band(m, nn, 1, 1, pen);
             if (bd.hi - bd.lo + 1 <= 32) {
                 ++nwin;
-                const int again = myers_forward_w32<W>(A0, A1, B0, B1, m, nn, tb.data(), 1, bd.hi);
-                if (again != pen) return -2;
-                nops[p] = (uint32_t)myers_traceback_w32<W>(A0, A1, B0, B1, m, nn, tb.data(), 1, bd.hi, ops_stage + (size_t)p * stride, stride);
+                if (m > 0 && myers_forward_w32<W>(A0, A1, B0, B1, m, nn, nn, tb.data(), 1, bd.hi) != pen) return -2;
+                nops[p] = (uint32_t)myers_traceback_split<W>(A0, A1, B0, B1, m, nn, tb.data(), 1, bd.hi, ops_stage + (size_t)p * stride, stride);
             } else {
                 NwScratch S{H.data(), I.data(), 1, tbw.data(), (2 * BITS + 1 + 7) / 8};
                 if (nw_forward<W>(1, 1, 1, A0, A1, B0, B1, m, nn, bd, S) != pen) return -3;
@@ -230,7 +229,8 @@ int sim_nw_batch(int W, int T, int x, int o, int e, const uint8_t* reads, const 
 }
 
 int sim_coverage(const uint8_t* s1, int s1_len, const uint16_t* g_ops, int g_n, const uint16_t* n_ops, int n_n) {
-    return coverage_pair(s1, s1_len, g_ops, g_n, n_ops, n_n);
+    uint32_t scratch[2 * kCovWords];
+    return coverage_pair(s1, s1_len, g_ops, g_n, n_ops, n_n, scratch, 1);
 }
 
 int sim_generate_pair(uint64_t seed, int length, int mode, int num_errors, uint64_t thr_mismatch, uint64_t thr_sub,
