@@ -315,10 +315,20 @@ compact_ops_kernel(const uint16_t* __restrict__ ops_stage, int ops_stride, const
     if (p < n) {
         op_off[p] = off;
         if (p == n - 1) op_off[n] = off + v;
-        // rows filled back to front (NW traceback) keep their ops at the end of the row
-        const uint16_t* src = ops_stage + (size_t)p * ops_stride + (from_end ? (uint32_t)ops_stride - v : 0u);
-        for (uint32_t i = 0; i < v; ++i)
-            if ((long long)(off + i) < ops_cap) ops_out[off + i] = src[i];
+        // rows filled back to front (NW traceback) keep their ops at the end of the row.  A row starts on a
+        // 16-byte boundary (the stride is a multiple of 8 ops), so it is read 8 ops per load; most pairs need one.
+        const uint32_t skip = from_end ? (uint32_t)ops_stride - v : 0u;
+        const uint16_t* rowp = ops_stage + (size_t)p * ops_stride;
+        for (uint32_t c = skip >> 3; 8u * c < skip + v; ++c) {
+            const uint4 q = *reinterpret_cast<const uint4*>(rowp + 8u * c);
+            const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+            for (uint32_t e = 0; e < 8u; ++e) {
+                const uint32_t i = 8u * c + e;          // position in the row
+                if (i >= skip && i < skip + v && (long long)(off + i - skip) < ops_cap)
+                    ops_out[off + i - skip] = (uint16_t)(w[e >> 1] >> (16u * (e & 1u)));
+            }
+        }
     }
 }
 

@@ -344,6 +344,12 @@ def run_b200(a):
             dist.destroy_process_group()
         return
     peak, peak_src = measured_peak()
+    prof = {}
+    try:   # byte count and pipe utilisation of the same command's ncu capture (profiles/), keyed by workload
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            prof = json.load(f).get("greedy|L=%d|e=%.2f|pairs=%d|k=%d" % (a.length, a.error, a.pairs, a.k), {})
+    except Exception:
+        prof = {}
     k_ms = kernel_ms / max(kernel_launches, 1)
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9
     line = {
@@ -362,7 +368,10 @@ def run_b200(a):
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "kernel": ("greedy_kernel<W=%d,WARPS=4>" if ml <= 256 else "greedy_warp_kernel<W=%d,WARPS=4>") % (ml // 64), "kernel_ms": k_ms,
+                     "traffic": prof.get("traffic_bytes"),
+                     "ncu": {k: prof[k] for k in ("issue_active_pct", "alu_pipe_pct", "avg_active_threads", "source") if k in prof},
+                     "note": "integer bit-vector work: the kernel is bound by instruction issue, not by HBM (see ncu block); "
+                             "frac is reported against the HBM roofline as the contract asks", "kernel": ("greedy_kernel<W=%d,WARPS=4>" if ml <= 256 else "greedy_warp_kernel<W=%d,WARPS=4>") % (ml // 64), "kernel_ms": k_ms,
                      "kernel_share_of_step": k_ms / (ms_total / a.steps), "algorithmic_bytes_per_launch": alg_bytes,
                      "peak_source": peak_src},
         "counters": {"pairs": int(counters[0]), "penalty_sum": int(counters[1]), "cigar_ops": int(counters[2])},
