@@ -12,7 +12,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libgasma_b200.so")
+LIB_PATH = os.environ.get("GASMA_B200_LIB") or os.path.join(HERE, "libgasma_b200.so")   # override: kernel A/B experiments
 
 GLOBAL, SEMI_GLOBAL = 0, 1
 OP_LETTERS = "MID=X"
