@@ -138,7 +138,7 @@ template <int W>
 __host__ __device__ constexpr size_t myers_smem_bytes(int tile) {
     return 4 * (size_t)stream_elems<W>(tile) * 2 + 2 * (size_t)(tile + 1) * 4 + 64;
 }
-// pass 2 adds the per-alignment traceback windows: half of the 64W columns at a time x (DG, UP) x 4 bytes
+// the banded kernel adds the per-alignment traceback windows: half of the 64W columns at a time x 2 words x 4 bytes
 template <int W>
 __host__ __device__ constexpr size_t myers_trace_smem_bytes(int tile) {
     return myers_smem_bytes<W>(tile) + (size_t)32 * W * 2 * 4 * tile;
@@ -191,18 +191,20 @@ nw_myers_kernel(const uint8_t* __restrict__ reads, const uint32_t* __restrict__ 
     if (wst && (tid & 31) == 0) atomicOr(status, wst);
 }
 
-// Pass 2: traceback ops.  `penalty` holds the exact optimum of every pair (pass 1).  Pairs whose band has more than
-// 32 diagonals are appended to `deferred` for nw_wide_kernel (general Gotoh, same traceback rule).
-template <int W, int T>
+// Banded verifier: one 32-bit window per column (nw_myers.cuh), penalty and -- when TRACE -- the traceback ops in
+// one pass.  `bound` is an upper bound on every pair's optimum: the greedy penalty, or the exact optimum from
+// nw_myers_kernel (it may then alias `penalty`).  Pairs whose band has more than 32 diagonals are appended to
+// `deferred` for nw_wide_kernel (general Gotoh, same traceback rule) with their exact optimum in `penalty` as its bound.
+template <int W, int T, bool TRACE>
 __global__ void __launch_bounds__(T)
-nw_myers_trace_kernel(const uint8_t* __restrict__ reads, const uint32_t* __restrict__ read_off, const uint8_t* __restrict__ refs,
-                      const uint32_t* __restrict__ ref_off, long long n, const int32_t* __restrict__ penalty,
-                      uint16_t* __restrict__ ops_stage, int ops_stride, uint32_t* __restrict__ nops_out,
-                      uint32_t* __restrict__ deferred, uint32_t* __restrict__ deferred_count) {
+nw_band_kernel(const uint8_t* __restrict__ reads, const uint32_t* __restrict__ read_off, const uint8_t* __restrict__ refs,
+               const uint32_t* __restrict__ ref_off, long long n, const int32_t* bound, int32_t* penalty,
+               uint16_t* __restrict__ ops_stage, int ops_stride, uint32_t* __restrict__ nops_out,
+               uint32_t* __restrict__ deferred, uint32_t* __restrict__ deferred_count, uint32_t* __restrict__ status) {
     constexpr int BITS = 64 * W;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    uint32_t* s_tb = reinterpret_cast<uint32_t*>(smem_raw);                       // [(col*2 + kind)][T]
-    uint16_t* s_r0 = reinterpret_cast<uint16_t*>(s_tb + (size_t)(BITS / 2) * 2 * T);
+    TraceCol* s_tb = reinterpret_cast<TraceCol*>(smem_raw);                       // [col][T]
+    uint16_t* s_r0 = reinterpret_cast<uint16_t*>(s_tb + (TRACE ? (size_t)(BITS / 2) * T : 0));
     uint16_t* s_r1 = s_r0 + stream_elems<W>(T);
     uint16_t* s_f0 = s_r1 + stream_elems<W>(T);
     uint16_t* s_f1 = s_f0 + stream_elems<W>(T);
@@ -216,33 +218,47 @@ nw_myers_trace_kernel(const uint8_t* __restrict__ reads, const uint32_t* __restr
     for (int i = tid; i < stream_elems<W>(T); i += T) { s_r0[i] = 0; s_r1[i] = 0; s_f0[i] = 0; s_f1[i] = 0; }
     __syncthreads();
     const uint32_t rbase = s_roff[0] & ~15u, fbase = s_foff[0] & ~15u;
-    stage_tile(reads, rbase, s_roff[np], read_off[n], s_r0, s_r1, stream_chunks<W>(T), tid, T);
-    stage_tile(refs, fbase, s_foff[np], ref_off[n], s_f0, s_f1, stream_chunks<W>(T), tid, T);
+    bool ok = stage_tile(reads, rbase, s_roff[np], read_off[n], s_r0, s_r1, stream_chunks<W>(T), tid, T);
+    ok &= stage_tile(refs, fbase, s_foff[np], ref_off[n], s_f0, s_f1, stream_chunks<W>(T), tid, T);
     __syncthreads();
 
+    uint32_t st = 0;
     if (tid < np) {
         const long long p = p0 + tid;
         const int m = (int)(s_roff[tid + 1] - s_roff[tid]);
         const int nn = (int)(s_foff[tid + 1] - s_foff[tid]);
-        const int pen = penalty[p];
-        uint32_t cnt = 0;
-        if (pen != INT32_MIN) {   // INT32_MIN: rejected by pass 1 (status already raised there)
-            const NwBand bd = nw_band(m, nn, 1, 1, pen);
-            if (bd.hi - bd.lo + 1 > 32) {
-                deferred[atomicAdd(deferred_count, 1u)] = (uint32_t)p;
+        if (!ok) st |= kStatusTile;
+        if (m > BITS || nn > BITS) st |= kStatusLength;
+        const int bnd = bound[p];
+        int cnt = 0;
+        if (st != 0 || bnd == INT32_MIN) {   // INT32_MIN: rejected by the pass that produced the bound
+            penalty[p] = INT32_MIN;
+        } else {
+            uint64_t A0[W], A1[W], B0[W], B1[W];
+            const int rbit = (int)(s_roff[tid] - rbase), fbit = (int)(s_foff[tid] - fbase);
+            extract_plane<W>(reinterpret_cast<const uint32_t*>(s_r0), rbit, m, A0);
+            extract_plane<W>(reinterpret_cast<const uint32_t*>(s_r1), rbit, m, A1);
+            extract_plane<W>(reinterpret_cast<const uint32_t*>(s_f0), fbit, nn, B0);
+            extract_plane<W>(reinterpret_cast<const uint32_t*>(s_f1), fbit, nn, B1);
+            NwBand bd = nw_band(m, nn, 1, 1, bnd);
+            if (!myers_band_fits(bd)) {
+                // a loose bound (rare: the greedy penalty is usually close): get the exact optimum from full columns
+                // first; its band is the narrowest there is
+                const int exact = myers_forward<W>(A0, A1, B0, B1, m, nn);
+                bd = nw_band(m, nn, 1, 1, exact);
+                penalty[p] = exact;
+            }
+            if (!myers_band_fits(bd)) {
+                deferred[atomicAdd(deferred_count, 1u)] = (uint32_t)p;   // nw_wide_kernel, bounded by penalty[p]
             } else {
-                uint64_t A0[W], A1[W], B0[W], B1[W];
-                const int rbit = (int)(s_roff[tid] - rbase), fbit = (int)(s_foff[tid] - fbase);
-                extract_plane<W>(reinterpret_cast<const uint32_t*>(s_r0), rbit, m, A0);
-                extract_plane<W>(reinterpret_cast<const uint32_t*>(s_r1), rbit, m, A1);
-                extract_plane<W>(reinterpret_cast<const uint32_t*>(s_f0), fbit, nn, B0);
-                extract_plane<W>(reinterpret_cast<const uint32_t*>(s_f1), fbit, nn, B1);
-                cnt = (uint32_t)myers_traceback_split<W>(A0, A1, B0, B1, m, nn, s_tb + tid, T, bd.hi,
-                                                         ops_stage + (size_t)p * ops_stride, ops_stride);
+                penalty[p] = myers_band_align<W>(A0, A1, B0, B1, m, nn, bd.hi, TRACE ? s_tb + tid : nullptr, T,
+                                                 TRACE ? ops_stage + (size_t)p * ops_stride : nullptr, ops_stride, &cnt);
             }
         }
-        nops_out[p] = cnt;
+        if (TRACE) nops_out[p] = (uint32_t)cnt;
     }
+    const uint32_t wst = __reduce_or_sync(0xffffffffu, st);
+    if (wst && (tid & 31) == 0) atomicOr(status, wst);
 }
 
 // per-tile sums of an op-count array (input of scan_tiles_kernel)

@@ -17,12 +17,9 @@
 // because H[i][j] - H[i-1][j-1] = dv_j(i) + dh_j(i-1) is 0 or 1, is 0 on a match, and a mismatching diagonal is
 // optimal exactly when that difference is 1.
 //
-// Traceback storage.  The verifier runs in two passes: a penalty-only pass (no memory traffic at all), then, when
-// the CIGAR is wanted, a second pass that knows the exact optimum.  An optimal path stays on the diagonals
-// d = j - i of nw_band(optimum) (nw.cuh), at most optimum+1 of them, so of each column only the rows
-// i in [j-hi, j-lo] can be visited; when the band has <= 32 diagonals one 32-bit WINDOW of DG and of UP per column
-// (8 bytes) is all the walk back needs, and a whole alignment's traceback fits in shared memory.  Wider bands go
-// to the general Gotoh kernel (same traceback rule).
+// Two forms live here: full columns (2W words, penalty only: myers_forward, used when no upper bound on the
+// optimum is known) and the banded form (one 32-bit word per column, penalty + traceback in one pass, below).
+// Bands wider than 32 diagonals go to the general Gotoh kernel (same traceback rule).
 #pragma once
 #include "common.cuh"
 #include "nw.cuh"
@@ -115,119 +112,171 @@ GASMA_HD int myers_forward(const uint64_t A0[W], const uint64_t A1[W], const uin
     return score;
 }
 
-// ---- narrow-band variant: 32-bit windows kept in shared memory -----------------------------------------
-// With the exact optimum known (a penalty-only pass), nw_band() has at most penalty+1 diagonals; when that is
-// <= 32 the traceback needs one 32-bit window of DG and of UP per column: 8 bytes, small enough to keep a whole
-// alignment's traceback in shared memory (tb[(j0*2 + kind) * stride], one column of threads per alignment), so the
-// walk back reads shared memory instead of chasing one DRAM sector per step.
-template <int NW32>
-GASMA_HD uint32_t window32_of(const uint32_t v[NW32], int s) {
-    const int idx = s >> 5, sh = s & 31;
-    uint32_t x0 = 0u, x1 = 0u;
+// ---- banded variant: the whole column is ONE 32-bit word that slides down the diagonal ---------------------
+// With an upper bound on the optimum (the greedy penalty, or the exact optimum of a penalty-only pass) every optimal
+// path stays on the diagonals d = j - i of nw_band(bound) (nw.cuh).  When those fit a 32-bit word, column j keeps only
+// the rows i = j - hi + b, b = 0..31 (hi = the band's top diagonal): the window moves one row down per column, so
+// between columns the vertical deltas shift by one bit.  The recurrence is the ordinary column step on that row set
+// with the two cells the band cuts off taken as "+1 from their in-band neighbour":
+//   * the cell above the window (diagonal hi+1) = its left neighbour + 1   -> horizontal delta +1 enters at bit 0
+//   * the cell left of the bottom row (diagonal hi-32) = the cell above it + 1 -> vertical delta +1 enters at bit 31
+// Both are upper bounds of the true values that a diagonal step always matches or beats, so every in-band cell holds
+// the cost of the best path INSIDE the band (>= the true value, == on every optimal path), and the traceback tests
+// "diagonal / up is optimal" come out exactly as on the full matrix for every cell an optimal walk visits.
+// Rows i <= 0 (window still above the matrix, columns j < hi) are virtual: H(i,j) = j + |i|, i.e. vertical deltas
+// of -1, which the recurrence keeps by itself and which makes row 0 read H(0,j) = j.  Rows i > m compare against
+// the 'A' tail; nothing above them depends on them.
+// Cost per column is independent of the read length (one word instead of 2W), and the vectors the traceback wants
+// ARE the windows, so penalty and traceback come out of one pass.
+//
+// Traceback storage: one 8-byte entry per column in shared memory, tb[slot * stride]:
+//   .dg : DG                      (diagonal step optimal)
+//   .sel: DG ? Eq : UP            (match vs mismatch on a diagonal step, insert vs delete otherwise)
+struct alignas(8) TraceCol { uint32_t dg, sel; };
+template <int W>
+GASMA_HD uint32_t word32_of(const uint64_t v[W], int w) {   // 32-bit word w of the vector; 0 outside
+    uint64_t x = 0;
 #pragma unroll
-    for (int w = 0; w < NW32; ++w) {
-        if (w == idx) x0 = v[w];
-        if (w == idx + 1) x1 = v[w];
-    }
-    return funnel32(x0, x1, sh);
+    for (int j = 0; j < W; ++j)
+        if (j == (w >> 1)) x = v[j];
+    return (uint32_t)(x >> ((w & 1) * 32));
+}
+GASMA_HD uint32_t funnel32_l(uint32_t lo, uint32_t hi, int s) {  // high word of (hi:lo) << s, 0 <= s < 32
+#if defined(__CUDA_ARCH__)
+    return __funnelshift_l(lo, hi, s);
+#else
+    return (uint32_t)(((((uint64_t)hi << 32) | lo) << s) >> 32);
+#endif
+}
+GASMA_HD uint32_t brev32(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+    return __brev(x);
+#else
+    x = ((x >> 1) & 0x55555555u) | ((x & 0x55555555u) << 1);
+    x = ((x >> 2) & 0x33333333u) | ((x & 0x33333333u) << 2);
+    x = ((x >> 4) & 0x0F0F0F0Fu) | ((x & 0x0F0F0F0Fu) << 4);
+    x = ((x >> 8) & 0x00FF00FFu) | ((x & 0x00FF00FFu) << 8);
+    return (x >> 16) | (x << 16);
+#endif
 }
 
-// Columns [0, j_end) are computed; the windows of columns j >= j_store are kept at slot (j - j_store).
+// does the band of `bound` fit the 32-bit window?  (hi - 31 <= lo: the window then covers the whole band)
+GASMA_HD bool myers_band_fits(const NwBand& bd) { return bd.hi - bd.lo + 1 <= 32; }
+
+// Columns [1, j_end] of the banded matrix (1-based; j_end <= n).  When tb != nullptr the windows of the columns
+// j > j_store are kept at slot j - 1 - j_store.  Returns H[m][j_end] (meaningful when row m is inside the last
+// window, which it is for j_end == n).
 template <int W>
-GASMA_HD int myers_forward_w32(const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W], const uint64_t B1[W], int m,
-                               int j_store, int j_end, uint32_t* tb, int stride, int band_hi) {
-    constexpr int NW32 = 2 * W;
-    uint32_t a0[NW32], a1[NW32], pv[NW32], mv[NW32];
-#pragma unroll
-    for (int j = 0; j < W; ++j) {
-        a0[2 * j] = (uint32_t)A0[j]; a0[2 * j + 1] = (uint32_t)(A0[j] >> 32);
-        a1[2 * j] = (uint32_t)A1[j]; a1[2 * j + 1] = (uint32_t)(A1[j] >> 32);
-    }
-#pragma unroll
-    for (int w = 0; w < NW32; ++w) { pv[w] = 0xFFFFFFFFu; mv[w] = 0u; }
-    int score = m;
-    uint64_t b0 = 0, b1 = 0;
-    for (int j = 0; j < j_end; ++j) {
-        if ((j & 63) == 0) {
-#pragma unroll
-            for (int q = 0; q < W; ++q)
-                if (q == (j >> 6)) { b0 = B0[q]; b1 = B1[q]; }
+GASMA_HD int myers_band_forward(const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W], const uint64_t B1[W],
+                                int m, int hi, int j_store, int j_end, TraceCol* tb, int stride) {
+    // column 0: H(i,0) = |i|  ->  +1 below row 0, -1 at and above it; bit b is row b - hi
+    uint32_t pv = hi >= 31 ? 0u : 0xFFFFFFFFu << (hi + 1);
+    uint32_t mv = ~pv;
+    int diag0 = 0;   // zero-cost diagonal steps of the window's top cell
+    // read planes shifted up by hi, so that the window of (0-based) column c is bits [c, c+32) of the shifted plane
+    uint32_t c0 = word32_of<W>(A0, 0), c1 = word32_of<W>(A1, 0);
+    uint32_t wl0 = funnel32_l(0u, c0, hi), wl1 = funnel32_l(0u, c1, hi);
+    TraceCol* out = tb;
+    for (int cb = 0; 32 * cb < j_end; ++cb) {
+        const uint32_t n0 = word32_of<W>(A0, cb + 1), n1 = word32_of<W>(A1, cb + 1);
+        const uint32_t wh0 = funnel32_l(c0, n0, hi), wh1 = funnel32_l(c1, n1, hi);
+        c0 = n0; c1 = n1;
+        uint32_t r0 = brev32(word32_of<W>(B0, cb)), r1 = brev32(word32_of<W>(B1, cb));   // next ref character in bit 31
+        const int cend = imin(32, j_end - 32 * cb);
+        for (int s = 0; s < cend; ++s) {
+            const uint32_t k0 = (uint32_t)((int32_t)r0 >> 31), k1 = (uint32_t)((int32_t)r1 >> 31);
+            r0 <<= 1;
+            r1 <<= 1;
+            const uint32_t eq = ~(funnel32(wl0, wh0, s) ^ k0) & ~(funnel32(wl1, wh1, s) ^ k1);
+            const uint32_t pvi = (pv >> 1) | 0x80000000u, mvi = mv >> 1;   // slide down one row
+            const uint32_t xv = eq | mvi;
+            const uint32_t xh = ((((eq & pvi) + pvi) ^ pvi)) | eq;
+            const uint32_t ph = mvi | ~(xh | pvi), mh = pvi & xh;
+            const uint32_t php = (ph << 1) | 1u, mhp = mh << 1;
+            pv = mhp | ~(xv | php);
+            mv = php & xv;
+            const uint32_t zero = (~(pv | mv) & ~(php | mhp)) | (pv & mhp) | (mv & php);   // dv + dh' == 0
+            diag0 += (int)(mv & 1u);   // bit 0: dh' = +1, so the diagonal step is free iff dv = -1
+            if (tb && 32 * cb + s >= j_store) {
+                const uint32_t dg = eq | ~zero;
+                *out = TraceCol{dg, eq | (~dg & pv)};
+                out += stride;
+            }
         }
-        const uint32_t k0 = (uint32_t)0 - (uint32_t)(b0 & 1ull), k1 = (uint32_t)0 - (uint32_t)(b1 & 1ull);
-        b0 >>= 1;
-        b1 >>= 1;
-        uint32_t eq[NW32], dg[NW32];
-#pragma unroll
-        for (int w = 0; w < NW32; ++w) eq[w] = ~(a0[w] ^ k0) & ~(a1[w] ^ k1);
-        score += myers_column<NW32>(eq, pv, mv, dg, m);
-        if (j >= j_store) {
-            const int s0 = myers_window_start(j, band_hi);
-            tb[(size_t)(2 * (j - j_store)) * stride] = window32_of<NW32>(dg, s0);
-            tb[(size_t)(2 * (j - j_store) + 1) * stride] = window32_of<NW32>(pv, s0);
-        }
+        wl0 = wh0; wl1 = wh1;
     }
+    // top cell of the last window: H(-hi,0) = hi, +1 per column unless the diagonal step was free; then down to row m
+    const int b = imax(-1, m - j_end + hi);   // < 0 only in a partial recomputation, whose result is not used
+    const uint32_t mask = (b >= 31 ? 0xFFFFFFFFu : ((1u << (b + 1)) - 1u)) & ~1u;
+    int score = hi + j_end - diag0;
+#if defined(__CUDA_ARCH__)
+    score += __popc(pv & mask) - __popc(mv & mask);
+#else
+    score += __builtin_popcount(pv & mask) - __builtin_popcount(mv & mask);
+#endif
     return score;
 }
 
-// Resumable walk back: emits ops while j > j_lo (and i > 0), reading the windows stored with base column j_store.
+// Resumable walk back: emits ops while j > j_lo (and i > 0), reading the entries stored with base column j_store.
+// Ops are written backwards from the end of the pair's staging row (the walk runs from the end of the alignment);
+// the row holds 2*max_length+8 ops, more than any walk can emit, so there is no capacity test.
 struct MyersTrace {
-    int i, j, cnt, cur, run;
+    int i, j, b;      // b = i - j + hi: the bit of cell (i, j) in column j's window
+    int cur, run;     // the op being extended
+    uint16_t* wp;     // next op is written at *--wp
 };
-template <int W>
-GASMA_HD void myers_trace_segment(const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W], const uint64_t B1[W],
-                                  MyersTrace& t, int j_lo, int j_store, const uint32_t* tb, int stride, int band_hi,
-                                  uint16_t* row, int cap) {
-    auto push = [&](int code, int len) {
-        if (code == t.cur) { t.run += len; return; }
-        if (t.cur >= 0) { ++t.cnt; if (t.cnt <= cap) row[cap - t.cnt] = (uint16_t)((t.run << 3) | t.cur); }
-        t.cur = code; t.run = len;
-    };
+GASMA_HD void myers_trace_push(MyersTrace& t, int code, int len) {
+    if (code != t.cur) {
+        if (t.cur >= 0) *--t.wp = (uint16_t)((t.run << 3) | t.cur);
+        t.cur = code;
+        t.run = 0;
+    }
+    t.run += len;
+}
+GASMA_HD void myers_trace_segment(MyersTrace& t, int j_lo, int j_store, const TraceCol* tb, int stride) {
+    const TraceCol* col = tb + (size_t)(t.j - 1 - j_store) * stride;
     while (t.i > 0 && t.j > j_lo) {
-        const int b = (t.i - 1) - myers_window_start(t.j - 1, band_hi);   // 0..31 on any optimal path
-        const int slot = t.j - 1 - j_store;
-        if ((tb[(size_t)(2 * slot) * stride] >> b) & 1u) {
-            const int mis = (bit_of<W>(A0, t.i - 1) ^ bit_of<W>(B0, t.j - 1)) | (bit_of<W>(A1, t.i - 1) ^ bit_of<W>(B1, t.j - 1));
-            push(mis ? 4 : 3, 1);
-            --t.i; --t.j;
-        } else if ((tb[(size_t)(2 * slot + 1) * stride] >> b) & 1u) {
-            push(1, 1);
-            --t.i;
-        } else {
-            push(2, 1);
-            --t.j;
-        }
+        const TraceCol c = *col;
+        const int dg = (int)((c.dg >> (t.b & 31)) & 1u), sel = (int)((c.sel >> (t.b & 31)) & 1u);
+        // dg: '=' (3) / 'X' (4) by sel;  otherwise I (1) when sel (up is optimal), else D (2)
+        myers_trace_push(t, dg ? 4 - sel : 2 - sel, 1);
+        const int di = dg | sel, dj = dg | (sel ^ 1);
+        t.i -= di;
+        t.j -= dj;
+        t.b += dj - di;
+        col -= dj ? stride : 0;
     }
 }
 // the boundary tail (first row / first column) and the flush of the last run; returns the op count
-GASMA_HD int myers_trace_finish(MyersTrace& t, uint16_t* row, int cap) {
-    auto push = [&](int code, int len) {
-        if (code == t.cur) { t.run += len; return; }
-        if (t.cur >= 0) { ++t.cnt; if (t.cnt <= cap) row[cap - t.cnt] = (uint16_t)((t.run << 3) | t.cur); }
-        t.cur = code; t.run = len;
-    };
-    if (t.i > 0) push(1, t.i);
-    if (t.j > 0) push(2, t.j);
-    push(-2, 0);
-    return t.cnt;
+GASMA_HD int myers_trace_finish(MyersTrace& t, const uint16_t* row_end) {
+    if (t.i > 0) myers_trace_push(t, 1, t.i);
+    if (t.j > 0) myers_trace_push(t, 2, t.j);
+    myers_trace_push(t, -2, 0);
+    return (int)(row_end - t.wp);
 }
 
-// Whole traceback of one alignment with HALF the columns resident: the upper half of the columns is stored and
-// walked first, then the lower half is recomputed into the same slots (1.5x the column work for half the shared
-// memory, i.e. twice the alignments in flight per SM).  tb holds 2 * ((n + 1) / 2) words per alignment.
+// Penalty and (when tb != nullptr) traceback of one alignment whose band fits the window.  HALF the columns are
+// resident: the upper half is stored and walked first, then the lower half is recomputed into the same slots
+// (1.5x the column work for half the shared memory, i.e. twice the alignments in flight per SM).
+// tb holds (n + 1) / 2 entries per alignment.  Returns the penalty; *nops = number of ops written to row's tail.
 template <int W>
-GASMA_HD int myers_traceback_split(const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W], const uint64_t B1[W],
-                                   int m, int n, uint32_t* tb, int stride, int band_hi, uint16_t* row, int cap) {
-    MyersTrace t{m, n, 0, -1, 0};
-    if (m > 0 && n > 0) {
-        const int split = n / 2;
-        myers_forward_w32<W>(A0, A1, B0, B1, m, split, n, tb, stride, band_hi);
-        myers_trace_segment<W>(A0, A1, B0, B1, t, split, split, tb, stride, band_hi, row, cap);
-        if (t.i > 0 && t.j > 0) {
-            myers_forward_w32<W>(A0, A1, B0, B1, m, 0, t.j, tb, stride, band_hi);
-            myers_trace_segment<W>(A0, A1, B0, B1, t, 0, 0, tb, stride, band_hi, row, cap);
-        }
+GASMA_HD int myers_band_align(const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W], const uint64_t B1[W],
+                              int m, int n, int hi, TraceCol* tb, int stride, uint16_t* row, int cap, int* nops) {
+    if (m == 0 || n == 0) {
+        if (tb) { MyersTrace t{m, n, 0, -1, 0, row + cap}; *nops = myers_trace_finish(t, row + cap); }
+        return imax(m, n);
     }
-    return myers_trace_finish(t, row, cap);
+    if (!tb) return myers_band_forward<W>(A0, A1, B0, B1, m, hi, 0, n, nullptr, 0);
+    const int split = n / 2;
+    const int pen = myers_band_forward<W>(A0, A1, B0, B1, m, hi, split, n, tb, stride);
+    MyersTrace t{m, n, m - n + hi, -1, 0, row + cap};
+    myers_trace_segment(t, split, split, tb, stride);
+    if (t.i > 0 && t.j > 0) {
+        myers_band_forward<W>(A0, A1, B0, B1, m, hi, 0, t.j, tb, stride);
+        myers_trace_segment(t, 0, 0, tb, stride);
+    }
+    *nops = myers_trace_finish(t, row + cap);
+    return pen;
 }
 
 }  // namespace gasma

@@ -38,6 +38,8 @@ def parse():
     ap.add_argument("--length", type=int, default=150)
     ap.add_argument("--error", type=float, default=0.10)
     ap.add_argument("--k", type=int, default=3)
+    ap.add_argument("--profile", default="simulated", choices=["simulated", "illumina"],
+                    help="simulated = exact edit budget (Dataset); illumina = per-base SRR611076 rates (BASELINE configs[3])")
     ap.add_argument("--batches", type=int, default=2, help="distinct resident batches cycled through")
     ap.add_argument("--cpu-sample", type=int, default=0, help="pairs in the CPU baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -50,14 +52,23 @@ def max_length_for(length, error):
     (mismatch_rate 0.96), so a ref outgrows its read by a handful of bases, not by the whole edit budget; a pair that
     did exceed max_length would fail the run loudly (GASMA_E_LENGTH), never silently."""
     ne = int(np.ceil(np.float32(length) * np.float32(error)))
-    need = length + min(ne, max(8, int(np.ceil(ne * 0.04 * 4))))
+    need = length + (min(ne, max(8, int(np.ceil(ne * 0.04 * 4)))) if ne else 8)   # ne == 0: per-base profile, a few inserts
     for ml in (64, 128, 192, 256, 512, 1024):
         if need <= ml:
             return ml
     raise SystemExit("workload does not fit max_length 1024")
 
 
+def gen_config_for(pkg, a, seed):
+    if a.profile == "illumina":
+        return pkg.gen_config(seed + 16, a.length, 0.0, mode=2, profile=PROFILE_ILLUMINA)
+    return pkg.gen_config(seed, a.length, a.error)
+
+
 def workload_name(a):
+    if a.profile == "illumina":
+        return ("synthetic Illumina-profile %d bp reads (per base: 2.452%% mismatch, 0.0468%% insert, 0.0553%% delete), "
+                "%d pairs/batch/GPU, greedy k=%d x=o=e=1" % (a.length, a.pairs, a.k))
     return "simulated %d bp reads, error rate %.2f (exact edits, 96%% mismatch), %d pairs/batch/GPU, greedy k=%d x=o=e=1" % (
         a.length, a.error, a.pairs, a.k)
 
@@ -237,11 +248,11 @@ def run_b200(a):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     pkg = load_pkg()
-    ml = max_length_for(a.length, a.error)
+    ml = max_length_for(a.length, a.error if a.profile == "simulated" else 0.0)
     al = pkg.Aligner(k=a.k, max_length=ml, device=local)
     stream = torch.cuda.current_stream()
     al.set_stream(stream.cuda_stream)
-    cfg = pkg.gen_config(SEED + 1, a.length, a.error)
+    cfg = gen_config_for(pkg, a, SEED + 1)
     n = a.pairs
     dev = torch.device("cuda", local)
 
@@ -396,11 +407,11 @@ def run_reference(a):
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_lib as ol
     ol.build_oracle()
-    ml = max_length_for(a.length, a.error)
+    ml = max_length_for(a.length, a.error if a.profile == "simulated" else 0.0)
     threads = len(os.sched_getaffinity(0))
     # bounded sample of the same workload, regenerated from the same (seed, pair index) counters by the CPU twin
     n = min(a.pairs, 200_000)
-    cfg = ol.gen_config(SEED + 1, a.length, a.error)
+    cfg = gen_config_for(ol, a, SEED + 1)
     b = ol.generate(cfg, 0, n)
     batch = (b.reads, b.read_off, b.refs, b.ref_off)
     per_step = []

@@ -157,15 +157,17 @@ int sim_nw(int x, int o, int e, const uint8_t* reads, const uint32_t* roff, cons
     return 0;
 }
 
-// unit-penalty NW the way the kernels run it: pass 1 penalty only (Myers bit-vector columns), pass 2 traceback from
-// 32-bit band windows when the band of the exact optimum has <= 32 diagonals, else the general Gotoh code
+// unit-penalty NW the way the kernels run it: the band comes from `bound` (the greedy penalty) or, without one, from
+// a penalty-only pass over full columns; a band of <= 32 diagonals takes the one-word banded route (penalty and
+// traceback in one pass), anything wider the general Gotoh code
 template <int W>
 int sim_myers(const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, const uint32_t* foff, int64_t n, int T,
-              int32_t* penalty, uint16_t* ops_stage, int stride, uint32_t* nops, int64_t* n_windowed) {
+              const int32_t* bound, int32_t* penalty, uint16_t* ops_stage, int stride, uint32_t* nops, int64_t* n_windowed) {
     constexpr int BITS = 64 * W;
     int64_t nwin = 0;
     std::vector<uint16_t> r0(elems<W>(T)), r1(elems<W>(T)), f0(elems<W>(T)), f1(elems<W>(T));
-    std::vector<uint32_t> tb((size_t)BITS * 2), tbw((size_t)BITS * ((2 * BITS + 1 + 7) / 8));
+    std::vector<TraceCol> tb((size_t)BITS);
+    std::vector<uint32_t> tbw((size_t)BITS * ((2 * BITS + 1 + 7) / 8));
     std::vector<int32_t> H(2 * BITS + 2), I(2 * BITS + 2);
     for (int64_t p0 = 0; p0 < n; p0 += T) {
         const int np = (int)std::min<int64_t>(T, n - p0);
@@ -182,18 +184,31 @@ int sim_myers(const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, c
             extract_plane<W>(reinterpret_cast<const uint32_t*>(r1.data()), (int)(roff[p] - rbase), m, A1);
             extract_plane<W>(reinterpret_cast<const uint32_t*>(f0.data()), (int)(foff[p] - fbase), nn, B0);
             extract_plane<W>(reinterpret_cast<const uint32_t*>(f1.data()), (int)(foff[p] - fbase), nn, B1);
-            const int pen = myers_forward<W>(A0, A1, B0, B1, m, nn);
-            penalty[p] = pen;
-            if (!ops_stage) continue;
-            const NwBand bd = nw_band(m, nn, 1, 1, pen);
-            if (bd.hi - bd.lo + 1 <= 32) {
+            int full = -1;
+            if (!bound) {
+                full = myers_forward<W>(A0, A1, B0, B1, m, nn);
+                penalty[p] = full;
+                if (!ops_stage) continue;
+            }
+            NwBand bd = nw_band(m, nn, 1, 1, bound ? bound[p] : full);
+            if (!myers_band_fits(bd) && full < 0) {   // loose bound: exact optimum from full columns first
+                full = myers_forward<W>(A0, A1, B0, B1, m, nn);
+                bd = nw_band(m, nn, 1, 1, full);
+            }
+            uint16_t* row = ops_stage ? ops_stage + (size_t)p * stride : nullptr;
+            if (myers_band_fits(bd)) {
                 ++nwin;
-                if (m > 0 && myers_forward_w32<W>(A0, A1, B0, B1, m, nn, nn, tb.data(), 1, bd.hi) != pen) return -2;
-                nops[p] = (uint32_t)myers_traceback_split<W>(A0, A1, B0, B1, m, nn, tb.data(), 1, bd.hi, ops_stage + (size_t)p * stride, stride);
+                int cnt = 0;
+                const int pen = myers_band_align<W>(A0, A1, B0, B1, m, nn, bd.hi, ops_stage ? tb.data() : nullptr, 1, row, stride, &cnt);
+                if (full >= 0 && pen != full) return -2;
+                penalty[p] = pen;
+                if (ops_stage) nops[p] = (uint32_t)cnt;
             } else {
-                NwScratch S{H.data(), I.data(), 1, tbw.data(), (2 * BITS + 1 + 7) / 8};
-                if (nw_forward<W>(1, 1, 1, A0, A1, B0, B1, m, nn, bd, S) != pen) return -3;
-                nops[p] = (uint32_t)nw_traceback<W>(A0, A1, B0, B1, m, nn, bd, S, ops_stage + (size_t)p * stride, stride);
+                NwScratch S{H.data(), I.data(), 1, ops_stage ? tbw.data() : nullptr, (2 * BITS + 1 + 7) / 8};
+                const int pen = nw_forward<W>(1, 1, 1, A0, A1, B0, B1, m, nn, bd, S);
+                if (full >= 0 && pen != full) return -3;
+                penalty[p] = pen;
+                if (ops_stage) nops[p] = (uint32_t)nw_traceback<W>(A0, A1, B0, B1, m, nn, bd, S, row, stride);
             }
         }
     }
@@ -206,12 +221,12 @@ int sim_myers(const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, c
 extern "C" {
 
 int sim_myers_batch(int W, int T, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, const uint32_t* foff,
-                    int64_t n, int32_t* penalty, uint16_t* ops_stage, int stride, uint32_t* nops, int64_t* n_windowed) {
+                    int64_t n, const int32_t* bound, int32_t* penalty, uint16_t* ops_stage, int stride, uint32_t* nops, int64_t* n_windowed) {
     switch (W) {
-        case 1: return sim_myers<1>(reads, roff, refs, foff, n, T, penalty, ops_stage, stride, nops, n_windowed);
-        case 2: return sim_myers<2>(reads, roff, refs, foff, n, T, penalty, ops_stage, stride, nops, n_windowed);
-        case 3: return sim_myers<3>(reads, roff, refs, foff, n, T, penalty, ops_stage, stride, nops, n_windowed);
-        case 4: return sim_myers<4>(reads, roff, refs, foff, n, T, penalty, ops_stage, stride, nops, n_windowed);
+        case 1: return sim_myers<1>(reads, roff, refs, foff, n, T, bound, penalty, ops_stage, stride, nops, n_windowed);
+        case 2: return sim_myers<2>(reads, roff, refs, foff, n, T, bound, penalty, ops_stage, stride, nops, n_windowed);
+        case 3: return sim_myers<3>(reads, roff, refs, foff, n, T, bound, penalty, ops_stage, stride, nops, n_windowed);
+        case 4: return sim_myers<4>(reads, roff, refs, foff, n, T, bound, penalty, ops_stage, stride, nops, n_windowed);
     }
     return -1;
 }

@@ -50,15 +50,17 @@ def sim_nw(S, b, W, x, o, e, bound=None, want_ops=True, cap_band=64, T=128):
     return pen, ops, int(wide[0])
 
 
-def sim_myers(S, b, W, want_ops=True, T=128):
-    S.sim_myers_batch.argtypes = [C.c_int] * 2 + [C.c_void_p] * 4 + [C.c_int64, C.c_void_p, C.c_void_p, C.c_int,
+def sim_myers(S, b, W, want_ops=True, T=128, bound=None):
+    S.sim_myers_batch.argtypes = [C.c_int] * 2 + [C.c_void_p] * 4 + [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
                                                                     C.c_void_p, C.c_void_p]
+    if bound is not None:
+        bound = np.ascontiguousarray(bound, np.int32)
     stride = 2 * 64 * W + 8
     pen = np.zeros(b.n, np.int32)
     stage = np.zeros(b.n * stride, np.uint16) if want_ops else None
     nops = np.zeros(b.n, np.uint32)
     nwin = np.zeros(1, np.int64)
-    rc = S.sim_myers_batch(W, T, _p(b.reads), _p(b.read_off), _p(b.refs), _p(b.ref_off), b.n, _p(pen), _p(stage),
+    rc = S.sim_myers_batch(W, T, _p(b.reads), _p(b.read_off), _p(b.refs), _p(b.ref_off), b.n, _p(bound), _p(pen), _p(stage),
                            stride, _p(nops), _p(nwin))
     assert rc == 0
     ops = [stage[(i + 1) * stride - nops[i]:(i + 1) * stride] for i in range(b.n)] if want_ops else None

@@ -43,6 +43,15 @@ def test_unit_penalty_bitvector_nw_matches_oracle(ol, host_sim, W):
         assert [ol.render_ops(v) for v in ops] == ol.render_all(r["ops"], r["op_off"])
         pen2, _ = sim_lib.sim_myers(host_sim, b, W, want_ops=False)
         assert pen2.tolist() == pen.tolist()
+        # any upper bound on the optimum (the greedy penalty plays that role) gives the same penalty and the same walk:
+        # exact, a little loose, and loose enough to push the band to 32 diagonals and beyond
+        for slack in (0, 3, 14, 31, 40):
+            bnd = r["penalty"].astype(np.int32) + rng.integers(0, slack + 1, b.n, dtype=np.int32)
+            pen3, ops3 = sim_lib.sim_myers(host_sim, b, W, bound=bnd)
+            assert pen3.tolist() == r["penalty"].tolist(), slack
+            assert [ol.render_ops(v) for v in ops3] == ol.render_all(r["ops"], r["op_off"]), slack
+            pen4, _ = sim_lib.sim_myers(host_sim, b, W, want_ops=False, bound=bnd)
+            assert pen4.tolist() == r["penalty"].tolist(), slack
         # both traceback routes were exercised: 32-bit band windows and the wide (Gotoh) route
         if max_err <= 0.3:
             assert 0 < windowed
