@@ -11,8 +11,9 @@ double last_kernel_ms(gasma_ctx* ctx, int which) {
     return ms;
 }
 
-// greedy -> NW (band from the greedy penalty) -> counters, all on the context's stream.
-// Returns after enqueueing; *g_total / *n_total (pinned words) hold the op counts once the stream is idle.
+// greedy -> NW (band from the greedy penalty) -> counters, all enqueued on the context's stream without a host
+// round trip.  The two CIGAR CSR arrays are sized for the worst case (2*max_length+8 ops per pair, the staging row
+// of either kernel), so no batch can overflow them and no op total has to travel to the host before the counters run.
 int benchmark_dev_impl(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_read_off, const char* d_refs,
                        const uint32_t* d_ref_off, int64_t n, const int32_t* d_answers, uint64_t* d_counters,
                        int32_t* d_gcost, int32_t* d_nwpen) {
@@ -28,32 +29,15 @@ int benchmark_dev_impl(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_re
     if (!d_nwpen) { if ((rc = reserve(ctx, ctx->bm_nwpen, (size_t)n * 4))) return rc; d_nwpen = (int32_t*)ctx->bm_nwpen.p; }
     if ((rc = reserve(ctx, ctx->bm_goff, ob))) return rc;
     if ((rc = reserve(ctx, ctx->bm_noff, ob))) return rc;
-    // op capacities: generous first guess, exact retry when a batch needs more (op_off[n] always holds the need)
-    int64_t gcap = ctx->bm_gcap > 0 ? ctx->bm_gcap : 24 * n + 64;
-    int64_t ncap = ctx->bm_ncap > 0 ? ctx->bm_ncap : 64 * n + 64;
-    for (int attempt = 0; attempt < 2; ++attempt) {
-        if ((rc = reserve(ctx, ctx->bm_gops, (size_t)gcap * 2))) return rc;
-        if ((rc = reserve(ctx, ctx->bm_nops, (size_t)ncap * 2))) return rc;
-        uint32_t* goff = (uint32_t*)ctx->bm_goff.p;
-        uint32_t* noff = (uint32_t*)ctx->bm_noff.p;
-        if ((rc = greedy_dev_impl(ctx, d_reads, d_read_off, d_refs, d_ref_off, n, d_gcost, (gasma_cigar_op*)ctx->bm_gops.p, gcap, goff))) return rc;
-        if ((rc = nw_dev_impl(ctx, d_reads, d_read_off, d_refs, d_ref_off, n, d_gcost, d_nwpen, (gasma_cigar_op*)ctx->bm_nops.p, ncap, noff))) return rc;
-        // the totals decide whether the compacted op arrays are complete before the counters may be trusted
-        CU(cudaMemcpyAsync(ctx->h_misc + 8, goff + n, 4, cudaMemcpyDeviceToHost, ctx->stream));
-        CU(cudaMemcpyAsync(ctx->h_misc + 9, noff + n, 4, cudaMemcpyDeviceToHost, ctx->stream));
-        CU(cudaStreamSynchronize(ctx->stream));
-        const int64_t gt = ctx->h_misc[8], nt = ctx->h_misc[9];
-        if (gt <= gcap && nt <= ncap) {
-            rc = gasma_metrics_dev(ctx, d_reads, d_read_off, n, d_gcost, (const gasma_cigar_op*)ctx->bm_gops.p, goff, d_nwpen,
-                                   (const gasma_cigar_op*)ctx->bm_nops.p, noff, d_answers, d_counters);
-            return rc;
-        }
-        gcap = gt > gcap ? gt + gt / 8 + 64 : gcap;
-        ncap = nt > ncap ? nt + nt / 8 + 64 : ncap;
-        ctx->bm_gcap = gcap;
-        ctx->bm_ncap = ncap;
-    }
-    return fail(ctx, GASMA_E_INTERNAL, "CIGAR op capacity retry failed");
+    const int64_t cap = n * (2 * (int64_t)ctx->params.max_length + 8);
+    if ((rc = reserve(ctx, ctx->bm_gops, (size_t)cap * 2))) return rc;
+    if ((rc = reserve(ctx, ctx->bm_nops, (size_t)cap * 2))) return rc;
+    uint32_t* goff = (uint32_t*)ctx->bm_goff.p;
+    uint32_t* noff = (uint32_t*)ctx->bm_noff.p;
+    if ((rc = greedy_dev_impl(ctx, d_reads, d_read_off, d_refs, d_ref_off, n, d_gcost, (gasma_cigar_op*)ctx->bm_gops.p, cap, goff))) return rc;
+    if ((rc = nw_dev_impl(ctx, d_reads, d_read_off, d_refs, d_ref_off, n, d_gcost, d_nwpen, (gasma_cigar_op*)ctx->bm_nops.p, cap, noff))) return rc;
+    return gasma_metrics_dev(ctx, d_reads, d_read_off, n, d_gcost, (const gasma_cigar_op*)ctx->bm_gops.p, goff, d_nwpen,
+                             (const gasma_cigar_op*)ctx->bm_nops.p, noff, d_answers, d_counters);
 }
 
 }  // namespace

@@ -432,7 +432,7 @@ int greedy_dev_impl(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_read_
         CU(cudaGetLastError());
         scan_tiles_kernel<<<1, 1024, 0, ctx->stream>>>((uint32_t*)ctx->tile_sums.p, (uint32_t*)ctx->tile_bases.p, (int)ntiles, misc + 1, carry_ops ? misc + 1 : nullptr);
         CU(cudaGetLastError());
-        compact_ops_kernel<T><<<(unsigned)ntiles, T, 0, ctx->stream>>>(stage, stride, nops, (uint32_t*)ctx->tile_bases.p,
+        compact_ops_kernel<T, false><<<(unsigned)ntiles, T, 0, ctx->stream>>>(stage, stride, nops, (uint32_t*)ctx->tile_bases.p,
                                                                      (long long)n, d_ops, (long long)ops_cap, d_op_off, 0);
         CU(cudaGetLastError());
         ctx->launches += 3;

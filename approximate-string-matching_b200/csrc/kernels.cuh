@@ -291,12 +291,17 @@ __global__ void __launch_bounds__(1024) scan_tiles_kernel(const uint32_t* __rest
 // CSR compaction: op_off[p] = tile_base + exclusive prefix inside the tile; ops copied from the
 // per-pair staging rows.  op_off[n] = total.  Writes beyond ops_cap are dropped (status bit set by host).
 // ---------------------------------------------------------------------------------------------
-template <int T>
+constexpr int kCompactSmemOps = 128 * 72;   // ops of one tile gathered in shared memory before the coalesced write-out
+
+// GATHER: collect the tile's ops in shared memory and write them out coalesced (pays off for the NW verifier's
+// ~m/3 ops per pair; the greedy path's handful of ops per pair is cheaper written straight from the rows).
+template <int T, bool GATHER>
 __global__ void __launch_bounds__(T)
 compact_ops_kernel(const uint16_t* __restrict__ ops_stage, int ops_stride, const uint32_t* __restrict__ nops,
                    const uint32_t* __restrict__ tile_bases, long long n, uint16_t* __restrict__ ops_out,
                    long long ops_cap, uint32_t* __restrict__ op_off, int from_end) {
     __shared__ uint32_t s_warp[T / 32];
+    __shared__ __align__(16) uint16_t s_ops[GATHER ? kCompactSmemOps + 8 : 8];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const long long p = (long long)blockIdx.x * T + tid;
     const uint32_t v = p < n ? nops[p] : 0u;
@@ -308,10 +313,20 @@ compact_ops_kernel(const uint16_t* __restrict__ ops_stage, int ops_stride, const
     }
     if (lane == 31) s_warp[warp] = inc;
     __syncthreads();
-    uint32_t wbase = 0;
+    uint32_t wbase = 0, tile_total = 0;
 #pragma unroll
-    for (int i = 0; i < T / 32; ++i) wbase += (i < warp) ? s_warp[i] : 0u;
-    const uint32_t off = tile_bases[blockIdx.x] + wbase + inc - v;
+    for (int i = 0; i < T / 32; ++i) {
+        wbase += (i < warp) ? s_warp[i] : 0u;
+        tile_total += s_warp[i];
+    }
+    const uint32_t tile_base = tile_bases[blockIdx.x];
+    const uint32_t local = wbase + inc - v;      // this pair's first op inside the tile
+    const uint32_t off = tile_base + local;
+    // The tile's ops are one contiguous range of the output.  They are gathered in shared memory (each thread
+    // reads its own row, 8 ops per load) shifted by the output's misalignment, then written out 16 bytes at a time;
+    // a tile with more ops than the buffer holds writes straight from the rows.
+    const uint32_t shift = (uint32_t)((reinterpret_cast<uintptr_t>(ops_out + tile_base) >> 1) & 7u);
+    const bool via_smem = GATHER && tile_total <= (uint32_t)kCompactSmemOps && (long long)tile_base + tile_total <= ops_cap;
     if (p < n) {
         op_off[p] = off;
         if (p == n - 1) op_off[n] = off + v;
@@ -325,9 +340,25 @@ compact_ops_kernel(const uint16_t* __restrict__ ops_stage, int ops_stride, const
 #pragma unroll
             for (uint32_t e = 0; e < 8u; ++e) {
                 const uint32_t i = 8u * c + e;          // position in the row
-                if (i >= skip && i < skip + v && (long long)(off + i - skip) < ops_cap)
-                    ops_out[off + i - skip] = (uint16_t)(w[e >> 1] >> (16u * (e & 1u)));
+                if (i >= skip && i < skip + v) {
+                    const uint16_t op = (uint16_t)(w[e >> 1] >> (16u * (e & 1u)));
+                    if (via_smem) s_ops[shift + local + i - skip] = op;
+                    else if ((long long)(off + i - skip) < ops_cap) ops_out[off + i - skip] = op;
+                }
             }
+        }
+    }
+    if (!via_smem) return;   // block-uniform
+    __syncthreads();
+    // s_ops[shift + k] -> ops_out[tile_base + k]; dst = ops_out + tile_base - shift is 16-byte aligned
+    uint16_t* dst = ops_out + tile_base - shift;
+    const uint32_t end = shift + tile_total;
+    for (uint32_t c = tid; 8u * c < end; c += T) {
+        const uint32_t lo = 8u * c;
+        if (lo >= shift && lo + 8u <= end) {
+            *reinterpret_cast<uint4*>(dst + lo) = *reinterpret_cast<const uint4*>(s_ops + lo);
+        } else {
+            for (uint32_t e = lo < shift ? shift : lo; e < lo + 8u && e < end; ++e) dst[e] = s_ops[e];
         }
     }
 }

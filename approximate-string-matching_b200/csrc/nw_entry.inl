@@ -127,7 +127,7 @@ int nw_dev_impl(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_read_off,
         CU(cudaGetLastError());
         scan_tiles_kernel<<<1, 1024, 0, ctx->stream>>>((uint32_t*)ctx->tile_sums.p, (uint32_t*)ctx->tile_bases.p, (int)ntiles, misc + 1, nullptr);
         CU(cudaGetLastError());
-        compact_ops_kernel<128><<<(unsigned)ntiles, 128, 0, ctx->stream>>>(stage, stride, nops, (uint32_t*)ctx->tile_bases.p,
+        compact_ops_kernel<128, true><<<(unsigned)ntiles, 128, 0, ctx->stream>>>(stage, stride, nops, (uint32_t*)ctx->tile_bases.p,
                                                                          (long long)n, d_ops, (long long)ops_cap, d_op_off, 1);
         CU(cudaGetLastError());
         ctx->launches += 3;
