@@ -12,7 +12,8 @@ double last_kernel_ms(gasma_ctx* ctx, int which) {
 }
 
 // greedy -> NW (band from the greedy penalty) -> counters, all enqueued on the context's stream without a host
-// round trip.  The two CIGAR CSR arrays are sized for the worst case (2*max_length+8 ops per pair, the staging row
+// round trip.  With unit penalties the verifier kernel also produces the counters (no NW CIGAR is materialised);
+// other penalties run verifier and counter kernel separately.  The CIGAR CSR arrays are sized for the worst case (2*max_length+8 ops per pair, the staging row
 // of either kernel), so no batch can overflow them and no op total has to travel to the host before the counters run.
 int benchmark_dev_impl(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_read_off, const char* d_refs,
                        const uint32_t* d_ref_off, int64_t n, const int32_t* d_answers, uint64_t* d_counters,
@@ -28,13 +29,17 @@ int benchmark_dev_impl(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_re
     if (!d_gcost) { if ((rc = reserve(ctx, ctx->bm_gcost, (size_t)n * 4))) return rc; d_gcost = (int32_t*)ctx->bm_gcost.p; }
     if (!d_nwpen) { if ((rc = reserve(ctx, ctx->bm_nwpen, (size_t)n * 4))) return rc; d_nwpen = (int32_t*)ctx->bm_nwpen.p; }
     if ((rc = reserve(ctx, ctx->bm_goff, ob))) return rc;
-    if ((rc = reserve(ctx, ctx->bm_noff, ob))) return rc;
     const int64_t cap = n * (2 * (int64_t)ctx->params.max_length + 8);
     if ((rc = reserve(ctx, ctx->bm_gops, (size_t)cap * 2))) return rc;
-    if ((rc = reserve(ctx, ctx->bm_nops, (size_t)cap * 2))) return rc;
     uint32_t* goff = (uint32_t*)ctx->bm_goff.p;
-    uint32_t* noff = (uint32_t*)ctx->bm_noff.p;
     if ((rc = greedy_dev_impl(ctx, d_reads, d_read_off, d_refs, d_ref_off, n, d_gcost, (gasma_cigar_op*)ctx->bm_gops.p, cap, goff))) return rc;
+    if (ctx->kp.x == 1 && ctx->kp.o == 1 && ctx->kp.e == 1 && ctx->W <= 4)
+        // unit penalties (what the reference's benchmark always runs): verifier and counters are one kernel
+        return nw_counters_dev_impl(ctx, d_reads, d_read_off, d_refs, d_ref_off, n, d_gcost, d_nwpen,
+                                    (const gasma_cigar_op*)ctx->bm_gops.p, goff, d_answers, d_counters);
+    if ((rc = reserve(ctx, ctx->bm_noff, ob))) return rc;
+    if ((rc = reserve(ctx, ctx->bm_nops, (size_t)cap * 2))) return rc;
+    uint32_t* noff = (uint32_t*)ctx->bm_noff.p;
     if ((rc = nw_dev_impl(ctx, d_reads, d_read_off, d_refs, d_ref_off, n, d_gcost, d_nwpen, (gasma_cigar_op*)ctx->bm_nops.p, cap, noff))) return rc;
     return gasma_metrics_dev(ctx, d_reads, d_read_off, n, d_gcost, (const gasma_cigar_op*)ctx->bm_gops.p, goff, d_nwpen,
                              (const gasma_cigar_op*)ctx->bm_nops.p, noff, d_answers, d_counters);

@@ -78,6 +78,135 @@ GASMA_HD int coverage_pair(const uint8_t* s1, int s1_len, const uint16_t* g_ops,
     return 0;
 }
 
+// ---- the same test on 2-bit planes and 32-bit position-mask words (fused into the NW verifier's kernel) -------
+// Used by the benchmark body, where the NW walk hands over its '=' steps as bit masks (CoverTrace, nw_myers.cuh) and
+// no NW CIGAR is ever written.  Same semantics as coverage_pair: identical characters = identical plane bits
+// (inputs outside {A,C,G,T} count as 'A' here, as they do everywhere on the 2-bit path).  NW = number of 32-bit words.
+template <int NW>
+GASMA_HD uint32_t word32_sel(const uint32_t v[NW], int w) {
+    uint32_t x = 0u;
+#pragma unroll
+    for (int j = 0; j < NW; ++j)
+        if (j == w) x = v[j];
+    return x;
+}
+// Read positions under '=' runs of length >= 3, from E (row consumed by '=') and B (a D between this row and the one
+// above): p and p+1 are in the same run iff E[p] & E[p+1] & ~B[p]; three in a row make a qualifying triple.
+template <int NW>
+GASMA_HD void runs3_positions(const uint32_t E[NW], const uint32_t B[NW], uint32_t P2[NW]) {
+    uint32_t C[NW];
+#pragma unroll
+    for (int w = 0; w < NW; ++w) {
+        const uint32_t up = (E[w] >> 1) | (w + 1 < NW ? E[w + 1] << 31 : 0u);   // E[p+1] at bit p
+        C[w] = E[w] & up & ~B[w];
+    }
+#pragma unroll
+    for (int w = 0; w < NW; ++w) {
+        const uint32_t up = (C[w] >> 1) | (w + 1 < NW ? C[w + 1] << 31 : 0u);
+        P2[w] = C[w] & up;                                                      // p, p+1, p+2 in one run
+    }
+    uint32_t c1 = 0u, c2 = 0u;
+#pragma unroll
+    for (int w = 0; w < NW; ++w) {
+        const uint32_t t3 = P2[w];
+        P2[w] = t3 | (t3 << 1) | c1 | (t3 << 2) | c2;
+        c1 = t3 >> 31;
+        c2 = t3 >> 30;
+    }
+}
+// toggles of a CIGAR's qualifying runs (see lcm_positions) in NW words; positions >= 32*NW are dropped
+template <int NW>
+GASMA_HD void lcm_toggles(const uint16_t* ops, int nops, int thr, uint32_t t[NW]) {
+#pragma unroll
+    for (int w = 0; w < NW; ++w) t[w] = 0u;
+    int idx = 0;
+    for (int oi = 0; oi < nops; ++oi) {
+        const int len = ops[oi] >> 3, code = ops[oi] & 7;
+        if (code == 2) continue;
+        if (!(code == 1 || code == 4 || len < thr)) {
+            const int a = idx, z = idx + len;
+#pragma unroll
+            for (int w = 0; w < NW; ++w) {
+                if ((a >> 5) == w) t[w] ^= 1u << (a & 31);
+                if ((z >> 5) == w) t[w] ^= 1u << (z & 31);
+            }
+        }
+        idx += len;
+    }
+}
+// prefix XOR over all bits: ones between a run's two toggles
+template <int NW>
+GASMA_HD void prefix_xor_fill(uint32_t t[NW]) {
+    uint32_t carry = 0u;
+#pragma unroll
+    for (int w = 0; w < NW; ++w) {
+        uint32_t v = t[w];
+        v ^= v << 1; v ^= v << 2; v ^= v << 4; v ^= v << 8; v ^= v << 16;
+        v ^= carry;
+        carry = (v >> 31) ? 0xFFFFFFFFu : 0u;
+        t[w] = v;
+    }
+}
+GASMA_HD int ctz32m(uint32_t x) {  // x != 0
+#if defined(__CUDA_ARCH__)
+    return __ffs((int)x) - 1;
+#else
+    return __builtin_ctz(x);
+#endif
+}
+// covers(): P2's characters (in position order) are a subsequence of P1's characters.  Instead of stepping over
+// every read position, each round jumps to the next P1 position that carries the wanted character.
+template <int NW>
+GASMA_HD int covers_planes(const uint32_t a0[NW], const uint32_t a1[NW], int m, const uint32_t P1[NW], const uint32_t P2[NW]) {
+    int jw = 0;
+    uint32_t jword = P2[0];
+    while (jword == 0u) {
+        if (++jw >= NW) return 1;   // nothing to cover
+        jword = word32_sel<NW>(P2, jw);
+    }
+    uint32_t a0j = word32_sel<NW>(a0, jw), a1j = word32_sel<NW>(a1, jw);
+    int jb = ctz32m(jword);
+    if (32 * jw + jb >= m) return 0;
+    uint32_t c0 = 0u - ((a0j >> jb) & 1u), c1 = 0u - ((a1j >> jb) & 1u);   // wanted character, broadcast
+#pragma unroll
+    for (int w = 0; w < NW; ++w) {
+        const int left = m - 32 * w;
+        const uint32_t valid = left >= 32 ? 0xFFFFFFFFu : (left <= 0 ? 0u : ((1u << left) - 1u));
+        uint32_t prem = P1[w] & valid;
+        const uint32_t x0 = a0[w], x1 = a1[w];
+        for (;;) {
+            const uint32_t cand = prem & ~((x0 ^ c0) | (x1 ^ c1));
+            if (cand == 0u) break;
+            const uint32_t low = cand & (0u - cand);   // the match: lowest P1 position left with the wanted character
+            if (jw == w && low == (1u << jb)) {
+                // the wanted position matches itself.  Then so does every directly following position that is in
+                // both sets (its own position is the first one left and carries its own character): take the
+                // whole run in one round -- '=' runs of the verifier mostly lie inside M runs of the greedy path
+                const uint32_t both = (jword & prem) >> jb;
+                const uint32_t stop = ~both;
+                const int run = stop ? ctz32m(stop) : 32;
+                const uint32_t taken = (run >= 32 ? 0xFFFFFFFFu : ((1u << run) - 1u)) << jb;
+                jword &= ~taken;
+                prem &= ~(taken | (low - 1u));
+            } else {
+                prem &= ~(low | (low - 1u));     // drop everything up to and including the match
+                jword &= jword - 1u;
+            }
+            while (jword == 0u) {
+                if (++jw >= NW) return 1;
+                jword = word32_sel<NW>(P2, jw);
+                a0j = word32_sel<NW>(a0, jw);
+                a1j = word32_sel<NW>(a1, jw);
+            }
+            jb = ctz32m(jword);
+            if (32 * jw + jb >= m) return 0;
+            c0 = 0u - ((a0j >> jb) & 1u);
+            c1 = 0u - ((a1j >> jb) & 1u);
+        }
+    }
+    return 0;
+}
+
 #if defined(__CUDACC__)
 // One pair per thread.  The tile's reads are one contiguous byte range of the CSR buffer: it is copied to shared
 // memory with coalesced 16-byte loads first, because the coverage test walks each read character by character

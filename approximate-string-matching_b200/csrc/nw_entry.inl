@@ -34,17 +34,17 @@ int launch_nw_w(gasma_ctx* ctx, const uint8_t* reads, const uint32_t* roff, cons
             CU(cudaMemsetAsync(dcount, 0, 4, ctx->stream));
             if (want_ops) {
                 constexpr int TT = 64;
-                auto tk = nw_band_kernel<W, TT, true>;
+                auto tk = nw_band_kernel<W, TT, kNwOps>;
                 const size_t tsmem = myers_trace_smem_bytes<W>(TT);
                 CU(cudaFuncSetAttribute(tk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsmem));
                 tk<<<(unsigned)((n + TT - 1) / TT), TT, tsmem, ctx->stream>>>(reads, roff, refs, foff, (long long)n, bound, penalty, stage,
-                                                                            stride, nops, (uint32_t*)ctx->nw_deferred.p, dcount, misc);
+                                                                            stride, nops, (uint32_t*)ctx->nw_deferred.p, dcount, misc, NwCounterArgs{});
             } else {
-                auto tk = nw_band_kernel<W, T, false>;
+                auto tk = nw_band_kernel<W, T, kNwPenalty>;
                 const size_t tsmem = myers_smem_bytes<W>(T);
                 CU(cudaFuncSetAttribute(tk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsmem));
                 tk<<<(unsigned)((n + T - 1) / T), T, tsmem, ctx->stream>>>(reads, roff, refs, foff, (long long)n, bound, penalty, nullptr,
-                                                                          0, nullptr, (uint32_t*)ctx->nw_deferred.p, dcount, misc);
+                                                                          0, nullptr, (uint32_t*)ctx->nw_deferred.p, dcount, misc, NwCounterArgs{});
             }
             CU(cudaGetLastError());
             nw_wide_kernel<W><<<nslots / 128, 128, 0, ctx->stream>>>(
@@ -82,6 +82,69 @@ int launch_nw_w(gasma_ctx* ctx, const uint8_t* reads, const uint32_t* roff, cons
     CU(cudaEventRecord(evp[1], ctx->stream));
     ctx->ev_count[1]++;
     return GASMA_OK;
+}
+
+// The benchmark body's verifier (unit penalties): NW penalties + the four counters in one kernel, bounded by the
+// greedy penalties; the NW CIGAR only exists for the few pairs the banded kernel defers.
+template <int W>
+int launch_nw_counters_w(gasma_ctx* ctx, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, const uint32_t* foff,
+                         int64_t n, const int32_t* gcost, int32_t* penalty, const NwCounterArgs& ca, uint16_t* stage, int stride,
+                         uint32_t* nops) {
+    constexpr int TT = 64;
+    constexpr int BITS = 64 * W;
+    uint32_t* misc = (uint32_t*)ctx->misc.p;
+    uint32_t* dcount = misc + 4;
+    int rc;
+    if ((rc = reserve(ctx, ctx->nw_deferred, (size_t)n * 4))) return rc;
+    const int nslots = W <= 2 ? 8192 : 4096;
+    if ((rc = reserve(ctx, ctx->nw_pool_hi, (size_t)nslots * 2 * (2 * BITS + 2) * 4))) return rc;
+    if ((rc = reserve(ctx, ctx->nw_pool_tb, (size_t)nslots * BITS * nw_tb_words_wide<W>() * 4))) return rc;
+    cudaEvent_t* mev = ctx->ev[1][ctx->ev_count[1] % gasma_ctx::kRing];
+    CU(cudaEventRecord(mev[0], ctx->stream));
+    CU(cudaMemsetAsync(dcount, 0, 8, ctx->stream));   // deferred count + hard count (misc[4], misc[5])
+    auto tk = nw_band_kernel<W, TT, kNwCounters>;
+    const size_t tsmem = myers_trace_smem_bytes<W>(TT);
+    CU(cudaFuncSetAttribute(tk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsmem));
+    tk<<<(unsigned)((n + TT - 1) / TT), TT, tsmem, ctx->stream>>>(reads, roff, refs, foff, (long long)n, gcost, penalty, nullptr, stride,
+                                                                nullptr, (uint32_t*)ctx->nw_deferred.p, dcount, misc, ca);
+    CU(cudaGetLastError());
+    nw_wide_kernel<W><<<nslots / 128, 128, 0, ctx->stream>>>(
+        1, 1, 1, reads, roff, refs, foff, penalty, penalty, (int32_t*)ctx->nw_pool_hi.p, (uint32_t*)ctx->nw_pool_tb.p, nslots,
+        stage, stride, nops, (const uint32_t*)ctx->nw_deferred.p, dcount);
+    CU(cudaGetLastError());
+    nw_deferred_counters_kernel<<<8, 128, 0, ctx->stream>>>(reads, roff, gcost, penalty, stage, stride, nops, ca,
+                                                           (const uint32_t*)ctx->nw_deferred.p, dcount);
+    CU(cudaGetLastError());
+    // sized for the worst case (every pair queued); blocks beyond the queue's length return at once
+    cover_hard_kernel<W><<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>(ca.hard, ca.hard_count, ca.hard_cap, ca.counters);
+    CU(cudaGetLastError());
+    ctx->launches += 4;
+    CU(cudaEventRecord(mev[1], ctx->stream));
+    ctx->ev_count[1]++;
+    return GASMA_OK;
+}
+
+int nw_counters_dev_impl(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_read_off, const char* d_refs,
+                         const uint32_t* d_ref_off, int64_t n, const int32_t* d_gcost, int32_t* d_penalty,
+                         const gasma_cigar_op* d_gops, const uint32_t* d_goff, const int32_t* d_answers, uint64_t* d_counters) {
+    const int stride = 2 * ctx->params.max_length + 8;
+    int rc;
+    if ((rc = reserve(ctx, ctx->ops_stage, (size_t)n * stride * sizeof(uint16_t)))) return rc;
+    if ((rc = reserve(ctx, ctx->nops, (size_t)n * 4))) return rc;
+    if ((rc = reserve(ctx, ctx->bm_hard, (size_t)n * (8 * ctx->W + 1) * 4))) return rc;
+    const NwCounterArgs ca{d_gops, d_goff, d_answers, (unsigned long long*)d_counters,
+                           (uint32_t*)ctx->bm_hard.p, (uint32_t*)ctx->misc.p + 5, (uint32_t)n};
+    const uint8_t* r = (const uint8_t*)d_reads;
+    const uint8_t* f = (const uint8_t*)d_refs;
+    uint16_t* stage = (uint16_t*)ctx->ops_stage.p;
+    uint32_t* nops = (uint32_t*)ctx->nops.p;
+    switch (ctx->W) {
+        case 1: return launch_nw_counters_w<1>(ctx, r, d_read_off, f, d_ref_off, n, d_gcost, d_penalty, ca, stage, stride, nops);
+        case 2: return launch_nw_counters_w<2>(ctx, r, d_read_off, f, d_ref_off, n, d_gcost, d_penalty, ca, stage, stride, nops);
+        case 3: return launch_nw_counters_w<3>(ctx, r, d_read_off, f, d_ref_off, n, d_gcost, d_penalty, ca, stage, stride, nops);
+        case 4: return launch_nw_counters_w<4>(ctx, r, d_read_off, f, d_ref_off, n, d_gcost, d_penalty, ca, stage, stride, nops);
+    }
+    return fail(ctx, GASMA_E_UNSUPPORTED, "the NW verifier covers max_length <= 256 (the greedy path covers 512 and 1024)");
 }
 
 int nw_dev_impl(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_read_off, const char* d_refs,

@@ -191,17 +191,37 @@ nw_myers_kernel(const uint8_t* __restrict__ reads, const uint32_t* __restrict__ 
     if (wst && (tid & 31) == 0) atomicOr(status, wst);
 }
 
-// Banded verifier: one 32-bit window per column (nw_myers.cuh), penalty and -- when TRACE -- the traceback ops in
-// one pass.  `bound` is an upper bound on every pair's optimum: the greedy penalty, or the exact optimum from
-// nw_myers_kernel (it may then alias `penalty`).  Pairs whose band has more than 32 diagonals are appended to
-// `deferred` for nw_wide_kernel (general Gotoh, same traceback rule) with their exact optimum in `penalty` as its bound.
-template <int W, int T, bool TRACE>
+// Banded verifier: one 32-bit window per column (nw_myers.cuh), penalty and traceback in one pass.
+// `bound` is an upper bound on every pair's optimum: the greedy penalty, or the exact optimum from nw_myers_kernel
+// (it may then alias `penalty`).  Pairs whose band has more than 32 diagonals are appended to `deferred` for
+// nw_wide_kernel (general Gotoh, same traceback rule) with their exact optimum in `penalty` as its bound.
+//   MODE 0: penalty only (no shared-memory windows)
+//   MODE 1: penalty + CIGAR ops into the pair's staging row (back to front) + nops_out
+//   MODE 2: penalty + the benchmark's counters (metrics.cuh): the walk hands its '=' steps to the coverage test
+//           as bit masks, no NW CIGAR is written.  bound = the greedy penalty, g_ops/g_off = the greedy CIGAR CSR.
+//           A deferred pair is not counted here: nw_wide_kernel writes its CIGAR and
+//           nw_deferred_counters_kernel counts it from there.
+constexpr int kNwPenalty = 0, kNwOps = 1, kNwCounters = 2;
+
+struct NwCounterArgs {
+    const uint16_t* g_ops;        // greedy CIGAR (CSR)
+    const uint32_t* g_off;
+    const int32_t* answers;       // optional (read_answer_file); INT32_MIN or null = use the NW penalty
+    unsigned long long* counters; // total, nw_correct, greedy_correct, greedy_coverage
+    uint32_t* hard;               // [8W+1][hard_cap]: pairs whose coverage needs the sequential test (cover_hard_kernel)
+    uint32_t* hard_count;
+    uint32_t hard_cap;
+};
+
+template <int W, int T, int MODE>
 __global__ void __launch_bounds__(T)
 nw_band_kernel(const uint8_t* __restrict__ reads, const uint32_t* __restrict__ read_off, const uint8_t* __restrict__ refs,
                const uint32_t* __restrict__ ref_off, long long n, const int32_t* bound, int32_t* penalty,
                uint16_t* __restrict__ ops_stage, int ops_stride, uint32_t* __restrict__ nops_out,
-               uint32_t* __restrict__ deferred, uint32_t* __restrict__ deferred_count, uint32_t* __restrict__ status) {
+               uint32_t* __restrict__ deferred, uint32_t* __restrict__ deferred_count, uint32_t* __restrict__ status,
+               NwCounterArgs ca) {
     constexpr int BITS = 64 * W;
+    constexpr bool TRACE = MODE != kNwPenalty;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     TraceCol* s_tb = reinterpret_cast<TraceCol*>(smem_raw);                       // [col][T]
     uint16_t* s_r0 = reinterpret_cast<uint16_t*>(s_tb + (TRACE ? (size_t)(BITS / 2) * T : 0));
@@ -223,6 +243,7 @@ nw_band_kernel(const uint8_t* __restrict__ reads, const uint32_t* __restrict__ r
     __syncthreads();
 
     uint32_t st = 0;
+    uint32_t c_tot = 0, c_nw = 0, c_gr = 0, c_cov = 0;   // MODE 2
     if (tid < np) {
         const long long p = p0 + tid;
         const int m = (int)(s_roff[tid + 1] - s_roff[tid]);
@@ -250,15 +271,115 @@ nw_band_kernel(const uint8_t* __restrict__ reads, const uint32_t* __restrict__ r
             }
             if (!myers_band_fits(bd)) {
                 deferred[atomicAdd(deferred_count, 1u)] = (uint32_t)p;   // nw_wide_kernel, bounded by penalty[p]
+            } else if (MODE == kNwCounters) {
+                CoverTrace<W> t;
+                const int pen = myers_band_cover<W>(A0, A1, B0, B1, m, nn, bd.hi, s_tb + tid, T, t);
+                penalty[p] = pen;
+                uint32_t P1[2 * W], P2[2 * W], a0[2 * W], a1[2 * W];
+                runs3_positions<2 * W>(t.E, t.B, P2);                    // LCM2: read positions under '=' runs >= 3
+                const uint32_t g0 = ca.g_off[p];
+                lcm_toggles<2 * W>(ca.g_ops + g0, (int)(ca.g_off[p + 1] - g0), 1, P1);
+                prefix_xor_fill<2 * W>(P1);                              // LCM1: read positions under greedy M runs
+#pragma unroll
+                for (int w = 0; w < W; ++w) {
+                    a0[2 * w] = (uint32_t)A0[w]; a0[2 * w + 1] = (uint32_t)(A0[w] >> 32);
+                    a1[2 * w] = (uint32_t)A1[w]; a1[2 * w + 1] = (uint32_t)(A1[w] >> 32);
+                }
+                const int correct = (ca.answers && ca.answers[p] != INT32_MIN) ? ca.answers[p] : pen;   // benchmark_utils.h:245-248
+                c_tot = 1;
+                c_nw = pen == correct;
+                c_gr = bnd == correct;
+                // covers(): when every LCM2 position is an LCM1 position too, each one matches itself at the latest --
+                // covered.  Otherwise the sequential subsequence test decides; those pairs (a minority) are queued
+                // for cover_hard_kernel, which runs it with full warps instead of a few straggler threads here.
+                uint32_t outside = 0u;
+#pragma unroll
+                for (int w = 0; w < 2 * W; ++w) outside |= P2[w] & ~P1[w];
+                if (outside == 0u) {
+                    c_cov = 1;
+                } else {
+                    const uint32_t slot = atomicAdd(ca.hard_count, 1u);
+                    uint32_t* h = ca.hard + slot;
+#pragma unroll
+                    for (int w = 0; w < 2 * W; ++w) {
+                        h[(size_t)(4 * w + 0) * ca.hard_cap] = a0[w];
+                        h[(size_t)(4 * w + 1) * ca.hard_cap] = a1[w];
+                        h[(size_t)(4 * w + 2) * ca.hard_cap] = P1[w];
+                        h[(size_t)(4 * w + 3) * ca.hard_cap] = P2[w];
+                    }
+                    h[(size_t)(8 * W) * ca.hard_cap] = (uint32_t)m;
+                }
             } else {
-                penalty[p] = myers_band_align<W>(A0, A1, B0, B1, m, nn, bd.hi, TRACE ? s_tb + tid : nullptr, T,
-                                                 TRACE ? ops_stage + (size_t)p * ops_stride : nullptr, ops_stride, &cnt);
+                OpsBackSink sink{MODE == kNwOps ? ops_stage + (size_t)p * ops_stride + ops_stride : nullptr};
+                const uint16_t* row_end = sink.wp;
+                penalty[p] = myers_band_align<W>(A0, A1, B0, B1, m, nn, bd.hi, TRACE ? s_tb + tid : nullptr, T, sink);
+                cnt = (int)(row_end - sink.wp);
             }
         }
-        if (TRACE) nops_out[p] = (uint32_t)cnt;
+        if (MODE == kNwOps) nops_out[p] = (uint32_t)cnt;
     }
     const uint32_t wst = __reduce_or_sync(0xffffffffu, st);
     if (wst && (tid & 31) == 0) atomicOr(status, wst);
+    if (MODE == kNwCounters) {
+        c_tot = __reduce_add_sync(0xffffffffu, c_tot);
+        c_nw = __reduce_add_sync(0xffffffffu, c_nw);
+        c_gr = __reduce_add_sync(0xffffffffu, c_gr);
+        c_cov = __reduce_add_sync(0xffffffffu, c_cov);
+        if ((tid & 31) == 0 && c_tot) {
+            atomicAdd(&ca.counters[0], (unsigned long long)c_tot);
+            atomicAdd(&ca.counters[1], (unsigned long long)c_nw);
+            atomicAdd(&ca.counters[2], (unsigned long long)c_gr);
+            atomicAdd(&ca.counters[3], (unsigned long long)c_cov);
+        }
+    }
+}
+
+// The sequential coverage test for the pairs nw_band_kernel (MODE 2) queued: one pair per thread, every lane busy.
+template <int W>
+__global__ void __launch_bounds__(128)
+cover_hard_kernel(const uint32_t* __restrict__ hard, const uint32_t* __restrict__ hard_count, uint32_t hard_cap,
+                  unsigned long long* __restrict__ counters) {
+    const uint32_t total = *hard_count;
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (blockIdx.x * blockDim.x >= total) return;
+    uint32_t cov = 0;
+    if (slot < total) {
+        uint32_t a0[2 * W], a1[2 * W], P1[2 * W], P2[2 * W];
+        const uint32_t* h = hard + slot;
+#pragma unroll
+        for (int w = 0; w < 2 * W; ++w) {
+            a0[w] = h[(size_t)(4 * w + 0) * hard_cap];
+            a1[w] = h[(size_t)(4 * w + 1) * hard_cap];
+            P1[w] = h[(size_t)(4 * w + 2) * hard_cap];
+            P2[w] = h[(size_t)(4 * w + 3) * hard_cap];
+        }
+        cov = (uint32_t)covers_planes<2 * W>(a0, a1, (int)h[(size_t)(8 * W) * hard_cap], P1, P2);
+    }
+    cov = __reduce_add_sync(0xffffffffu, cov);
+    if ((threadIdx.x & 31) == 0 && cov) atomicAdd(&counters[3], (unsigned long long)cov);
+}
+
+// Counters of the pairs the banded kernel deferred in MODE 2 (their NW CIGAR is in the staging rows, written back
+// to front by nw_wide_kernel).  A handful of pairs per batch at most: one thread each, everything from global memory.
+__global__ void __launch_bounds__(128)
+nw_deferred_counters_kernel(const uint8_t* __restrict__ reads, const uint32_t* __restrict__ read_off,
+                            const int32_t* __restrict__ g_cost, const int32_t* __restrict__ penalty,
+                            const uint16_t* __restrict__ n_stage, int ops_stride, const uint32_t* __restrict__ n_cnt,
+                            NwCounterArgs ca, const uint32_t* __restrict__ deferred, const uint32_t* __restrict__ deferred_count) {
+    const uint32_t total = *deferred_count;
+    for (uint32_t it = blockIdx.x * blockDim.x + threadIdx.x; it < total; it += gridDim.x * blockDim.x) {
+        const uint32_t p = deferred[it];
+        const int pen = penalty[p];
+        const int correct = (ca.answers && ca.answers[p] != INT32_MIN) ? ca.answers[p] : pen;
+        uint32_t scratch[2 * kCovWords];
+        const uint32_t r0 = read_off[p], g0 = ca.g_off[p], cnt = n_cnt[p];
+        const int cov = coverage_pair(reads + r0, (int)(read_off[p + 1] - r0), ca.g_ops + g0, (int)(ca.g_off[p + 1] - g0),
+                                      n_stage + (size_t)p * ops_stride + (ops_stride - cnt), (int)cnt, scratch, 1);
+        atomicAdd(&ca.counters[0], 1ull);
+        atomicAdd(&ca.counters[1], (unsigned long long)(pen == correct));
+        atomicAdd(&ca.counters[2], (unsigned long long)(g_cost[p] == correct));
+        atomicAdd(&ca.counters[3], (unsigned long long)cov);
+    }
 }
 
 // per-tile sums of an op-count array (input of scan_tiles_kernel)

@@ -217,29 +217,36 @@ GASMA_HD int myers_band_forward(const uint64_t A0[W], const uint64_t A1[W], cons
     return score;
 }
 
-// Resumable walk back: emits ops while j > j_lo (and i > 0), reading the entries stored with base column j_store.
-// Ops are written backwards from the end of the pair's staging row (the walk runs from the end of the alignment);
-// the row holds 2*max_length+8 ops, more than any walk can emit, so there is no capacity test.
+// Resumable walk back: emits runs while j > j_lo (and i > 0), reading the entries stored with base column j_store.
+// A finished run goes to the sink: sink.flush(code, length, i) with i = the read row the run started after (walking
+// backwards), i.e. the run covers the 0-based read positions [i, i + rows it consumed).
 struct MyersTrace {
     int i, j, b;      // b = i - j + hi: the bit of cell (i, j) in column j's window
-    int cur, run;     // the op being extended
-    uint16_t* wp;     // next op is written at *--wp
+    int cur, run;     // the run being extended
 };
-GASMA_HD void myers_trace_push(MyersTrace& t, int code, int len) {
+// Sink 1: CIGAR ops, written backwards from the end of the pair's staging row (the walk runs from the end of the
+// alignment); the row holds 2*max_length+8 ops, more than any walk can emit, so there is no capacity test.
+struct OpsBackSink {
+    uint16_t* wp;     // next op is written at *--wp
+    GASMA_HD void flush(int code, int run, int) { *--wp = (uint16_t)((run << 3) | code); }
+};
+template <class Sink>
+GASMA_HD void myers_trace_push(MyersTrace& t, Sink& sink, int code, int len) {
     if (code != t.cur) {
-        if (t.cur >= 0) *--t.wp = (uint16_t)((t.run << 3) | t.cur);
+        if (t.cur >= 0) sink.flush(t.cur, t.run, t.i);
         t.cur = code;
         t.run = 0;
     }
     t.run += len;
 }
-GASMA_HD void myers_trace_segment(MyersTrace& t, int j_lo, int j_store, const TraceCol* tb, int stride) {
+template <class Sink>
+GASMA_HD void myers_trace_segment(MyersTrace& t, Sink& sink, int j_lo, int j_store, const TraceCol* tb, int stride) {
     const TraceCol* col = tb + (size_t)(t.j - 1 - j_store) * stride;
     while (t.i > 0 && t.j > j_lo) {
         const TraceCol c = *col;
         const int dg = (int)((c.dg >> (t.b & 31)) & 1u), sel = (int)((c.sel >> (t.b & 31)) & 1u);
         // dg: '=' (3) / 'X' (4) by sel;  otherwise I (1) when sel (up is optimal), else D (2)
-        myers_trace_push(t, dg ? 4 - sel : 2 - sel, 1);
+        myers_trace_push(t, sink, dg ? 4 - sel : 2 - sel, 1);
         const int di = dg | sel, dj = dg | (sel ^ 1);
         t.i -= di;
         t.j -= dj;
@@ -247,35 +254,94 @@ GASMA_HD void myers_trace_segment(MyersTrace& t, int j_lo, int j_store, const Tr
         col -= dj ? stride : 0;
     }
 }
-// the boundary tail (first row / first column) and the flush of the last run; returns the op count
-GASMA_HD int myers_trace_finish(MyersTrace& t, const uint16_t* row_end) {
-    if (t.i > 0) myers_trace_push(t, 1, t.i);
-    if (t.j > 0) myers_trace_push(t, 2, t.j);
-    myers_trace_push(t, -2, 0);
-    return (int)(row_end - t.wp);
+// the boundary tail (first row / first column) and the flush of the last run
+template <class Sink>
+GASMA_HD void myers_trace_finish(MyersTrace& t, Sink& sink) {
+    if (t.i > 0) { myers_trace_push(t, sink, 1, t.i); t.i = 0; }
+    if (t.j > 0) myers_trace_push(t, sink, 2, t.j);
+    myers_trace_push(t, sink, -2, 0);
 }
 
 // Penalty and (when tb != nullptr) traceback of one alignment whose band fits the window.  HALF the columns are
 // resident: the upper half is stored and walked first, then the lower half is recomputed into the same slots
 // (1.5x the column work for half the shared memory, i.e. twice the alignments in flight per SM).
-// tb holds (n + 1) / 2 entries per alignment.  Returns the penalty; *nops = number of ops written to row's tail.
-template <int W>
+// tb holds (n + 1) / 2 entries per alignment.  Returns the penalty; the runs of the walk go to `sink`.
+template <int W, class Sink>
 GASMA_HD int myers_band_align(const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W], const uint64_t B1[W],
-                              int m, int n, int hi, TraceCol* tb, int stride, uint16_t* row, int cap, int* nops) {
+                              int m, int n, int hi, TraceCol* tb, int stride, Sink& sink) {
     if (m == 0 || n == 0) {
-        if (tb) { MyersTrace t{m, n, 0, -1, 0, row + cap}; *nops = myers_trace_finish(t, row + cap); }
+        if (tb) { MyersTrace t{m, n, 0, -1, 0}; myers_trace_finish(t, sink); }
         return imax(m, n);
     }
     if (!tb) return myers_band_forward<W>(A0, A1, B0, B1, m, hi, 0, n, nullptr, 0);
     const int split = n / 2;
     const int pen = myers_band_forward<W>(A0, A1, B0, B1, m, hi, split, n, tb, stride);
-    MyersTrace t{m, n, m - n + hi, -1, 0, row + cap};
-    myers_trace_segment(t, split, split, tb, stride);
+    MyersTrace t{m, n, m - n + hi, -1, 0};
+    myers_trace_segment(t, sink, split, split, tb, stride);
     if (t.i > 0 && t.j > 0) {
         myers_band_forward<W>(A0, A1, B0, B1, m, hi, 0, t.j, tb, stride);
-        myers_trace_segment(t, 0, 0, tb, stride);
+        myers_trace_segment(t, sink, 0, 0, tb, stride);
     }
-    *nops = myers_trace_finish(t, row + cap);
+    myers_trace_finish(t, sink);
+    return pen;
+}
+
+// ---- the walk without a CIGAR: what the coverage counter needs from it, as bit masks over read positions ----
+// benchmark_coverage.h:26-67 with threshold 3 keeps the read positions under '=' runs of length >= 3.  The walk
+// consumes the read rows in descending order, so it just records, per consumed row p (0-based position),
+//   E[p] = the row was consumed by an '=' step,   B[p] = a D step happened between row p and the row above it
+// (a D does not consume a row but ends a run), 32 positions per word, accumulated in registers and flushed when a
+// word is complete.  No run lengths, no per-run branches; metrics.cuh:runs3_positions turns E, B into the positions.
+template <int W>
+struct CoverTrace {
+    int i, j, b;
+    uint32_t e, brk;       // word under construction
+    uint32_t pend;         // a D step since the last consumed row
+    uint32_t E[2 * W], B[2 * W];
+};
+template <int W>
+GASMA_HD void myers_cover_segment(CoverTrace<W>& t, int j_lo, int j_store, const TraceCol* tb, int stride) {
+    const TraceCol* col = tb + (size_t)(t.j - 1 - j_store) * stride;
+    while (t.i > 0 && t.j > j_lo) {
+        const TraceCol c = *col;
+        const uint32_t dg = (c.dg >> (t.b & 31)) & 1u, sel = (c.sel >> (t.b & 31)) & 1u;
+        const uint32_t di = dg | sel, dj = dg | (sel ^ 1u);   // diagonal: both; up (I): row only; left (D): column only
+        const int p = t.i - 1;
+        const uint32_t bit = di << (p & 31);
+        t.e |= (dg & sel) ? bit : 0u;
+        t.brk |= t.pend ? bit : 0u;
+        t.pend = di ^ 1u;
+        if (di && (p & 31) == 0) {
+            t.E[p >> 5] = t.e;
+            t.B[p >> 5] = t.brk;
+            t.e = t.brk = 0u;
+        }
+        t.i -= (int)di;
+        t.j -= (int)dj;
+        t.b += (int)dj - (int)di;
+        col -= dj ? stride : 0;
+    }
+}
+// Penalty + E/B masks of one alignment whose band fits the window (same half-resident scheme as myers_band_align).
+template <int W>
+GASMA_HD int myers_band_cover(const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W], const uint64_t B1[W],
+                              int m, int n, int hi, TraceCol* tb, int stride, CoverTrace<W>& t) {
+    t.i = m; t.j = n; t.b = m - n + hi;
+    t.e = t.brk = t.pend = 0u;
+#pragma unroll
+    for (int w = 0; w < 2 * W; ++w) { t.E[w] = 0u; t.B[w] = 0u; }
+    if (m == 0 || n == 0) return imax(m, n);   // only I or only D: no '=' at all
+    const int split = n / 2;
+    const int pen = myers_band_forward<W>(A0, A1, B0, B1, m, hi, split, n, tb, stride);
+    myers_cover_segment<W>(t, split, split, tb, stride);
+    if (t.i > 0 && t.j > 0) {
+        myers_band_forward<W>(A0, A1, B0, B1, m, hi, 0, t.j, tb, stride);
+        myers_cover_segment<W>(t, 0, 0, tb, stride);
+    }
+    if (t.i > 0) {   // rows left at column 0 are an I run; the word under construction still has to land
+        t.E[(t.i - 1) >> 5] = t.e;
+        t.B[(t.i - 1) >> 5] = t.brk;
+    }
     return pen;
 }
 

@@ -198,11 +198,11 @@ int sim_myers(const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, c
             uint16_t* row = ops_stage ? ops_stage + (size_t)p * stride : nullptr;
             if (myers_band_fits(bd)) {
                 ++nwin;
-                int cnt = 0;
-                const int pen = myers_band_align<W>(A0, A1, B0, B1, m, nn, bd.hi, ops_stage ? tb.data() : nullptr, 1, row, stride, &cnt);
+                OpsBackSink sink{row ? row + stride : nullptr};
+                const int pen = myers_band_align<W>(A0, A1, B0, B1, m, nn, bd.hi, ops_stage ? tb.data() : nullptr, 1, sink);
                 if (full >= 0 && pen != full) return -2;
                 penalty[p] = pen;
-                if (ops_stage) nops[p] = (uint32_t)cnt;
+                if (ops_stage) nops[p] = (uint32_t)(row + stride - sink.wp);
             } else {
                 NwScratch S{H.data(), I.data(), 1, ops_stage ? tbw.data() : nullptr, (2 * BITS + 1 + 7) / 8};
                 const int pen = nw_forward<W>(1, 1, 1, A0, A1, B0, B1, m, nn, bd, S);
@@ -213,6 +213,72 @@ int sim_myers(const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, c
         }
     }
     if (n_windowed) *n_windowed = nwin;
+    return 0;
+}
+
+// the benchmark body's fused verifier + counters (nw_band_kernel MODE 2): band from the greedy penalty, the walk's
+// '=' runs go straight into the coverage test on 2-bit planes; pairs whose band does not fit take the Gotoh route
+// and the character-based coverage test, like nw_wide_kernel + nw_deferred_counters_kernel
+template <int W>
+int sim_counters(const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, const uint32_t* foff, int64_t n, int T,
+                 const int32_t* gcost, const uint16_t* gops, const uint32_t* goff, const int32_t* answers,
+                 int32_t* penalty, uint64_t* counters, int64_t* n_deferred) {
+    constexpr int BITS = 64 * W;
+    const int stride = 2 * BITS + 8;
+    std::vector<uint16_t> r0(elems<W>(T)), r1(elems<W>(T)), f0(elems<W>(T)), f1(elems<W>(T)), row(stride);
+    std::vector<TraceCol> tb((size_t)BITS);
+    std::vector<uint32_t> tbw((size_t)BITS * ((2 * BITS + 1 + 7) / 8));
+    std::vector<int32_t> H(2 * BITS + 2), I(2 * BITS + 2);
+    int64_t ndef = 0;
+    for (int64_t p0 = 0; p0 < n; p0 += T) {
+        const int np = (int)std::min<int64_t>(T, n - p0);
+        std::fill(r0.begin(), r0.end(), 0); std::fill(r1.begin(), r1.end(), 0);
+        std::fill(f0.begin(), f0.end(), 0); std::fill(f1.begin(), f1.end(), 0);
+        const uint32_t rbase = roff[p0] & ~15u, fbase = foff[p0] & ~15u;
+        stage(reads, rbase, roff[p0 + np], roff[n], r0.data(), r1.data(), chunks<W>(T));
+        stage(refs, fbase, foff[p0 + np], foff[n], f0.data(), f1.data(), chunks<W>(T));
+        for (int t = 0; t < np; ++t) {
+            const int64_t p = p0 + t;
+            const int m = (int)(roff[p + 1] - roff[p]), nn = (int)(foff[p + 1] - foff[p]);
+            uint64_t A0[W], A1[W], B0[W], B1[W];
+            extract_plane<W>(reinterpret_cast<const uint32_t*>(r0.data()), (int)(roff[p] - rbase), m, A0);
+            extract_plane<W>(reinterpret_cast<const uint32_t*>(r1.data()), (int)(roff[p] - rbase), m, A1);
+            extract_plane<W>(reinterpret_cast<const uint32_t*>(f0.data()), (int)(foff[p] - fbase), nn, B0);
+            extract_plane<W>(reinterpret_cast<const uint32_t*>(f1.data()), (int)(foff[p] - fbase), nn, B1);
+            NwBand bd = nw_band(m, nn, 1, 1, gcost[p]);
+            if (!myers_band_fits(bd)) bd = nw_band(m, nn, 1, 1, myers_forward<W>(A0, A1, B0, B1, m, nn));
+            int pen, cov;
+            if (myers_band_fits(bd)) {
+                CoverTrace<W> ct;
+                pen = myers_band_cover<W>(A0, A1, B0, B1, m, nn, bd.hi, tb.data(), 1, ct);
+                uint32_t P1[2 * W], P2[2 * W], a0[2 * W], a1[2 * W];
+                runs3_positions<2 * W>(ct.E, ct.B, P2);
+                lcm_toggles<2 * W>(gops + goff[p], (int)(goff[p + 1] - goff[p]), 1, P1);
+                prefix_xor_fill<2 * W>(P1);
+                for (int w = 0; w < W; ++w) {
+                    a0[2 * w] = (uint32_t)A0[w]; a0[2 * w + 1] = (uint32_t)(A0[w] >> 32);
+                    a1[2 * w] = (uint32_t)A1[w]; a1[2 * w + 1] = (uint32_t)(A1[w] >> 32);
+                }
+                uint32_t outside = 0;
+                for (int w = 0; w < 2 * W; ++w) outside |= P2[w] & ~P1[w];
+                cov = outside == 0 ? 1 : covers_planes<2 * W>(a0, a1, m, P1, P2);   // kernel: queued for cover_hard_kernel
+            } else {
+                ++ndef;
+                NwScratch S{H.data(), I.data(), 1, tbw.data(), (2 * BITS + 1 + 7) / 8};
+                pen = nw_forward<W>(1, 1, 1, A0, A1, B0, B1, m, nn, bd, S);
+                const int cnt = nw_traceback<W>(A0, A1, B0, B1, m, nn, bd, S, row.data(), stride);
+                uint32_t scratch[2 * kCovWords];
+                cov = coverage_pair(reads + roff[p], m, gops + goff[p], (int)(goff[p + 1] - goff[p]), row.data() + stride - cnt, cnt, scratch, 1);
+            }
+            penalty[p] = pen;
+            const int correct = (answers && answers[p] != INT32_MIN) ? answers[p] : pen;
+            counters[0] += 1;
+            counters[1] += pen == correct;
+            counters[2] += gcost[p] == correct;
+            counters[3] += (uint64_t)cov;
+        }
+    }
+    if (n_deferred) *n_deferred = ndef;
     return 0;
 }
 
@@ -227,6 +293,18 @@ int sim_myers_batch(int W, int T, const uint8_t* reads, const uint32_t* roff, co
         case 2: return sim_myers<2>(reads, roff, refs, foff, n, T, bound, penalty, ops_stage, stride, nops, n_windowed);
         case 3: return sim_myers<3>(reads, roff, refs, foff, n, T, bound, penalty, ops_stage, stride, nops, n_windowed);
         case 4: return sim_myers<4>(reads, roff, refs, foff, n, T, bound, penalty, ops_stage, stride, nops, n_windowed);
+    }
+    return -1;
+}
+
+int sim_counters_batch(int W, int T, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, const uint32_t* foff,
+                       int64_t n, const int32_t* gcost, const uint16_t* gops, const uint32_t* goff, const int32_t* answers,
+                       int32_t* penalty, uint64_t* counters, int64_t* n_deferred) {
+    switch (W) {
+        case 1: return sim_counters<1>(reads, roff, refs, foff, n, T, gcost, gops, goff, answers, penalty, counters, n_deferred);
+        case 2: return sim_counters<2>(reads, roff, refs, foff, n, T, gcost, gops, goff, answers, penalty, counters, n_deferred);
+        case 3: return sim_counters<3>(reads, roff, refs, foff, n, T, gcost, gops, goff, answers, penalty, counters, n_deferred);
+        case 4: return sim_counters<4>(reads, roff, refs, foff, n, T, gcost, gops, goff, answers, penalty, counters, n_deferred);
     }
     return -1;
 }

@@ -66,3 +66,20 @@ def sim_myers(S, b, W, want_ops=True, T=128, bound=None):
     ops = [stage[(i + 1) * stride - nops[i]:(i + 1) * stride] for i in range(b.n)] if want_ops else None
     sim_myers.last_windowed = int(nwin[0])
     return pen, ops
+
+
+def sim_counters(S, b, W, greedy, answers=None, T=128):
+    """Fused verifier + counters of the benchmark body; returns (penalties, counters[4], deferred pairs)."""
+    S.sim_counters_batch.argtypes = [C.c_int] * 2 + [C.c_void_p] * 4 + [C.c_int64] + [C.c_void_p] * 7
+    pen = np.zeros(b.n, np.int32)
+    counters = np.zeros(4, np.uint64)
+    ndef = np.zeros(1, np.int64)
+    gcost = np.ascontiguousarray(greedy["cost"], np.int32)
+    gops = np.ascontiguousarray(greedy["ops"], np.uint16)
+    goff = np.ascontiguousarray(greedy["op_off"], np.uint32)
+    if answers is not None:
+        answers = np.ascontiguousarray(answers, np.int32)
+    rc = S.sim_counters_batch(W, T, _p(b.reads), _p(b.read_off), _p(b.refs), _p(b.ref_off), b.n, _p(gcost), _p(gops), _p(goff),
+                              _p(answers), _p(pen), _p(counters), _p(ndef))
+    assert rc == 0
+    return pen, counters, int(ndef[0])

@@ -81,3 +81,22 @@ def test_gpu_benchmark_batch_host_call(pkg, ol):
     out2 = al.benchmark_batch(b.reads, b.read_off, b.refs, b.ref_off, answers=ans, counters=out["counters"])
     assert out2["counters"].tolist() == [a + c for a, c in zip(exp, exp2)]
     al.close()
+
+
+@pytest.mark.parametrize("W,penalties", [(1, (1, 1, 1)), (2, (1, 1, 1)), (4, (1, 1, 1)), (2, (2, 3, 1))])
+def test_gpu_benchmark_batch_noisy_pairs(pkg, ol, W, penalties):
+    """The fused verifier + counters kernel (unit penalties) including the pairs it defers to the Gotoh kernel
+    (very noisy pairs: band > 32 diagonals), and the separate verifier / counter kernels for other penalties."""
+    x, o, e = penalties
+    rng = np.random.default_rng(800 + W + x)
+    b = ol.random_batch(rng, 6000, 0, 64 * W, 0.6, 0.4, 50)
+    og = ol.oracle_greedy(b, ol.make_params(3, x, o, e, W, 1), threads=8)
+    on = ol.oracle_nw(b, x, o, e, threads=8)
+    exp = [int(v) for v in ol.oracle_metrics(b, og, on)]
+    al = pkg.Aligner(x=x, o=o, e=e, max_length=64 * W)
+    out = al.benchmark_batch(b.reads, b.read_off, b.refs, b.ref_off, want_penalties=True)
+    assert out["greedy_cost"].tolist() == og["cost"].tolist()
+    assert out["nw_penalty"].tolist() == on["penalty"].tolist()
+    assert out["counters"].tolist() == exp
+    assert 0 < exp[3] < b.n
+    al.close()

@@ -84,6 +84,30 @@ def test_coverage_logic_matches_oracle(ol, host_sim):
     assert cov == int(exp[3]) and 0 < cov < b.n
 
 
+@pytest.mark.parametrize("W", [1, 2, 3, 4])
+def test_fused_verifier_counters_match_oracle(ol, host_sim, W):
+    """nw_band_kernel's counter mode: no NW CIGAR, the walk's '=' runs feed the coverage test on 2-bit planes."""
+    rng = np.random.default_rng(4100 + W)
+    seen_deferred = 0
+    for max_err, indel, k in ((0.08, 0.1, 3), (0.25, 0.3, 3), (0.25, 0.04, 5), (0.7, 0.4, 3)):
+        b = ol.random_batch(rng, 700, 0, 64 * W, max_err, indel, 50)
+        g = ol.oracle_greedy(b, ol.make_params(k, 1, 1, 1, W, 1))
+        nw = ol.oracle_nw(b, 1, 1, 1, threads=4)
+        exp = ol.oracle_metrics(b, g, nw)
+        pen, counters, ndef = sim_lib.sim_counters(host_sim, b, W, g)
+        seen_deferred += ndef
+        assert pen.tolist() == nw["penalty"].tolist()
+        assert counters.tolist() == exp.tolist()
+        assert 0 < counters[3] < b.n or max_err < 0.1
+        # stored answers (read_answer_file) replace the NW penalty as the truth for some pairs
+        ans = np.where(rng.random(b.n) < 0.5, nw["penalty"] + rng.integers(0, 2, b.n), np.iinfo(np.int32).min).astype(np.int32)
+        exp2 = ol.oracle_metrics(b, g, nw, ans)
+        _, c2, _ = sim_lib.sim_counters(host_sim, b, W, g, answers=ans)
+        assert c2.tolist() == exp2.tolist()
+    if W >= 2:
+        assert seen_deferred > 0     # the Gotoh + character-based route was exercised too
+
+
 def test_generator_logic_matches_oracle_twin(ol, host_sim):
     host_sim.sim_generate_pair.argtypes = [C.c_uint64] + [C.c_int] * 3 + [C.c_uint64] * 5 + [C.c_void_p] * 3
     for mode, e, prof in [(0, 0.10, None), (1, 0.20, None), (2, 0.0, (0.02452, 0.0468, 0.0553)), (0, 0.15, None)]:
