@@ -9,6 +9,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <chrono>
 #include <string>
 
 #include "kernels.cuh"
@@ -40,7 +41,10 @@ struct gasma_ctx {
     cudaStream_t own_stream = nullptr;  // created by us
     // host-pointer calls on large batches are pipelined in slices: H2D of slice i+1 and D2H of slice i-1 overlap
     // the kernels of slice i
-    static constexpr int kSlices = 4;
+    static constexpr int kSlices = 16;  // most slices a call is cut into
+    int slices = 8;                     // slices actually used (env GASMA_SLICES)
+    bool trace = false;                 // env GASMA_TRACE: per-call timing of the host-pointer path on stderr
+    cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr, ev_t2 = nullptr;
     cudaStream_t copy_in = nullptr, copy_out = nullptr;
     cudaEvent_t ev_in[kSlices] = {}, ev_comp[kSlices] = {}, ev_off[kSlices] = {}, ev_fence = nullptr;
     int64_t launches = 0;
@@ -235,6 +239,11 @@ int gasma_create(const gasma_params* params, int device, gasma_ctx** out) {
     if (const char* env = getenv("GASMA_REFILL_THRESHOLD")) {   // tuning knob; results do not depend on it
         const int v = atoi(env);
         if (v >= 1 && v <= 32) c->refill_threshold = v;
+    }
+    c->trace = getenv("GASMA_TRACE") != nullptr;
+    if (const char* env = getenv("GASMA_SLICES")) {             // pipeline depth of the host-pointer calls; same results
+        const int v = atoi(env);
+        if (v >= 1 && v <= gasma_ctx::kSlices) c->slices = v;
     }
     derive(c);
     if (greedy_tile_threads(c) == 0) {
@@ -440,15 +449,17 @@ int greedy_dev_impl(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_read_
     return GASMA_OK;
 }
 
+int check_offsets(gasma_ctx* ctx, const uint32_t* off, int64_t n, const char* what);
+
 // Host-pointer greedy call on a large batch, pipelined over kSlices slices of pairs (slice edges on multiples of
 // 128 pairs).  Device mirrors are already reserved by the caller.  Streams: copy_in (H2D), ctx->stream (kernels),
 // copy_out (D2H); the CSR op array is shared by all slices, op_off continues across them on the device.
 int greedy_batch_pipelined(gasma_ctx* ctx, const char* reads, const uint32_t* read_off, const char* refs,
                            const uint32_t* ref_off, int64_t n, int32_t* cost, gasma_cigar_op* ops, int64_t ops_cap,
                            uint32_t* op_off) {
-    constexpr int S = gasma_ctx::kSlices;
+    const int S = ctx->slices;
     const size_t ob = (size_t)(n + 1) * 4;
-    int64_t edge[S + 1];
+    int64_t edge[gasma_ctx::kSlices + 1];
     for (int i = 0; i <= S; ++i) edge[i] = i == S ? n : ((n * i / S) / 128) * 128;
     char* d_reads = (char*)ctx->d_reads.p;
     char* d_refs = (char*)ctx->d_refs.p;
@@ -462,13 +473,27 @@ int greedy_batch_pipelined(gasma_ctx* ctx, const char* reads, const uint32_t* re
     CU(cudaEventRecord(ctx->ev_fence, ctx->stream));
     CU(cudaStreamWaitEvent(ctx->copy_in, ctx->ev_fence, 0));
     CU(cudaStreamWaitEvent(ctx->copy_out, ctx->ev_fence, 0));
+    const auto wall0 = std::chrono::steady_clock::now();
+    if (ctx->trace) {
+        if (!ctx->ev_t0) { CU(cudaEventCreate(&ctx->ev_t0)); CU(cudaEventCreate(&ctx->ev_t1)); CU(cudaEventCreate(&ctx->ev_t2)); }
+        CU(cudaEventRecord(ctx->ev_t0, ctx->copy_in));
+    }
     CU(cudaMemcpyAsync(d_roff, read_off, ob, cudaMemcpyHostToDevice, ctx->copy_in));
     CU(cudaMemcpyAsync(d_foff, ref_off, ob, cudaMemcpyHostToDevice, ctx->copy_in));
+    for (int i = 0; i < S; ++i)   // the copies below only trust the slice edges; everything else is validated while they run
+        if (read_off[edge[i]] > read_off[edge[i + 1]] || ref_off[edge[i]] > ref_off[edge[i + 1]])
+            return fail(ctx, GASMA_E_ARG, "offsets are not non-decreasing around pair %lld", (long long)edge[i]);
     for (int i = 0; i < S; ++i) {
         const size_t r0 = read_off[edge[i]], r1 = read_off[edge[i + 1]], f0 = ref_off[edge[i]], f1 = ref_off[edge[i + 1]];
         if (r1 > r0) CU(cudaMemcpyAsync(d_reads + r0, reads + r0, r1 - r0, cudaMemcpyHostToDevice, ctx->copy_in));
         if (f1 > f0) CU(cudaMemcpyAsync(d_refs + f0, refs + f0, f1 - f0, cudaMemcpyHostToDevice, ctx->copy_in));
         CU(cudaEventRecord(ctx->ev_in[i], ctx->copy_in));
+    }
+    if (ctx->trace) CU(cudaEventRecord(ctx->ev_t1, ctx->copy_in));
+    {   // full validation of both offset arrays, hidden behind the first slice's DMA (8 MB of host reads for 1 M pairs)
+        int vrc = check_offsets(ctx, read_off, n, "read");
+        if (!vrc) vrc = check_offsets(ctx, ref_off, n, "ref");
+        if (vrc) { cudaStreamSynchronize(ctx->copy_in); return vrc; }
     }
     CU(cudaMemsetAsync(misc + 1, 0, 4, ctx->stream));   // running op total
     for (int i = 0; i < S; ++i) {
@@ -497,15 +522,35 @@ int greedy_batch_pipelined(gasma_ctx* ctx, const char* reads, const uint32_t* re
     CU(cudaStreamSynchronize(ctx->copy_out));
     int rc = gasma_synchronize(ctx);
     if (rc) return rc;
+    if (ctx->trace) {
+        float h2d_ms = 0.f, all_ms = 0.f;
+        cudaEventRecord(ctx->ev_t2, ctx->copy_out);
+        cudaEventSynchronize(ctx->ev_t2);
+        cudaEventElapsedTime(&h2d_ms, ctx->ev_t0, ctx->ev_t1);
+        cudaEventElapsedTime(&all_ms, ctx->ev_t0, ctx->ev_t2);
+        const double wall = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - wall0).count();
+        fprintf(stderr, "[gasma] pipelined call: %d slices, H2D %.3f ms (%.1f GB/s), first copy -> last offsets on host %.3f ms, wall %.3f ms\n",
+                S, h2d_ms, (double)(read_off[n] + ref_off[n] + 2 * ob) / h2d_ms / 1e6, all_ms, wall);
+    }
     if (overflow)
         return fail(ctx, GASMA_E_CAPACITY, "ops buffer holds %lld ops, %lld needed", (long long)ops_cap, (long long)op_off[n]);
     return GASMA_OK;
 }
 
-// host-side validation of a CSR offset array
+// host-side validation of a CSR offset array.  This runs before the first byte is copied, so it must not cost
+// milliseconds on a 1 M-pair batch: blocks are checked with a branch-free reduction the compiler vectorises, and
+// only a block that failed is searched for the position.
 int check_offsets(gasma_ctx* ctx, const uint32_t* off, int64_t n, const char* what) {
-    for (int64_t i = 0; i < n; ++i)
-        if (off[i + 1] < off[i]) return fail(ctx, GASMA_E_ARG, "%s offsets are not non-decreasing at %lld", what, (long long)i);
+    constexpr int64_t kBlock = 4096;
+    for (int64_t b = 0; b < n; b += kBlock) {
+        const int64_t e = b + kBlock < n ? b + kBlock : n;
+        uint32_t bad = 0;
+        for (int64_t i = b; i < e; ++i) bad |= (uint32_t)(off[i + 1] < off[i]);
+        if (bad)
+            for (int64_t i = b; i < e; ++i)
+                if (off[i + 1] < off[i])
+                    return fail(ctx, GASMA_E_ARG, "%s offsets are not non-decreasing at %lld", what, (long long)i);
+    }
     return GASMA_OK;
 }
 
@@ -568,8 +613,11 @@ int gasma_greedy_batch(gasma_ctx* ctx, const char* reads, const uint32_t* read_o
     if ((ops != nullptr) != (op_off != nullptr)) return fail(ctx, GASMA_E_ARG, "ops and op_off must be given together");
     if (n == 0) { if (op_off) op_off[0] = 0; return GASMA_OK; }
     int rc;
-    if ((rc = check_offsets(ctx, read_off, n, "read"))) return rc;
-    if ((rc = check_offsets(ctx, ref_off, n, "ref"))) return rc;
+    const bool pipelined = n >= 65536;
+    if (!pipelined) {   // the pipelined path validates while its first copies are in flight
+        if ((rc = check_offsets(ctx, read_off, n, "read"))) return rc;
+        if ((rc = check_offsets(ctx, ref_off, n, "ref"))) return rc;
+    }
     CU(cudaSetDevice(ctx->device));
     const size_t rb = read_off[n], fb = ref_off[n], ob = (size_t)(n + 1) * 4;
     if ((rc = reserve(ctx, ctx->d_reads, rb + 16))) return rc;
@@ -581,7 +629,7 @@ int gasma_greedy_batch(gasma_ctx* ctx, const char* reads, const uint32_t* read_o
         if ((rc = reserve(ctx, ctx->d_op_off, ob))) return rc;
         if ((rc = reserve(ctx, ctx->d_ops, (size_t)(ops_cap > 0 ? ops_cap : 1) * 2))) return rc;
     }
-    if (n >= 65536) return greedy_batch_pipelined(ctx, reads, read_off, refs, ref_off, n, cost, ops, ops_cap, op_off);
+    if (pipelined) return greedy_batch_pipelined(ctx, reads, read_off, refs, ref_off, n, cost, ops, ops_cap, op_off);
     if (rb) CU(cudaMemcpyAsync(ctx->d_reads.p, reads, rb, cudaMemcpyHostToDevice, ctx->stream));
     if (fb) CU(cudaMemcpyAsync(ctx->d_refs.p, refs, fb, cudaMemcpyHostToDevice, ctx->stream));
     CU(cudaMemcpyAsync(ctx->d_read_off.p, read_off, ob, cudaMemcpyHostToDevice, ctx->stream));

@@ -375,7 +375,7 @@ def run_b200(a):
         "e2e": {"value": world * n * e2e_steps / e2e_s, "unit": "alignments/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "steps": e2e_steps,
                 "h2d_gb_per_s": h2d * e2e_steps / e2e_s / 1e9,
-                "note": "host-pointer C-ABI call, pinned buffers, 4 pipelined slices; bound by the host-to-device link (ASCII in)"},
+                "note": "host-pointer C-ABI call, pinned buffers, 8 pipelined slices; bound by the host-to-device link (ASCII in; PCIe 5 x16 measured at 55 GB/s by tools/link_probe.py)"},
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
