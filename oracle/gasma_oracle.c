@@ -440,6 +440,93 @@ int go_nw_batch(const char* reads, const uint32_t* read_off, const char* refs, c
 }
 
 /* ------------------------------------------------------------------------------------------
+ * LEAP comparator: banded affine Landau-Vishkin, class LV of GASMA/benchmark/LEAP_SIMD/LV_BAG.cpp,
+ * driven as benchmark::_run_LEAP does (benchmark_utils.h:156-178) on an object set up with
+ * init(k, af_threshold = 200, ED_GLOBAL, x, o, e) (benchmark_utils.h:289).
+ *   lanes: 2k+3 of them, lane k+1 is the main diagonal; lanes 0 and 2k+2 are never-valid sentinels
+ *   (LV_BAG.cpp:76-77,129).  Below the middle the read is offset, above it the reference (:9-23).
+ *   load_reads pads both strings with NUL up to L = max(m, n) (strncpy, :112-123), so a position past
+ *   the end of the shorter string mismatches.
+ *   cells start/end/I_pos/D_pos[lane][e] are -2 until reached; which cells get reached depends only on
+ *   (lane, e, penalties), never on the data, so reusing the object across pairs (as the benchmark does)
+ *   gives the same results as a fresh one -- checked against the reference in tests/test_oracle.py.
+ * Returns the penalty the benchmark records (get_ED() = final_ED, :360: the error level at which the
+ * best converging lane reached the end, WITHOUT the cost of returning to the main lane), or INT32_MIN
+ * when no lane converges within af_threshold (the reference would then report the previous pair's
+ * value).  Needs o >= e ("Assuming gap_open_penalty > gap_ext_penalty", :165) and m, n <= 256.
+ * ---------------------------------------------------------------------------------------- */
+#define LV_MAXLEN 256
+#define LV_AF 200
+int go_leap(const char* read, int m, const char* ref, int n, int k, int x, int o, int e) {
+    if (m > LV_MAXLEN || n > LV_MAXLEN || k < 0 || k > GO_MAX_K || x < 1 || e < 1 || o < e) return INT32_MIN;
+    const int total = 2 * k + 3, mid = k + 1, L = m > n ? m : n;
+    char A[LV_MAXLEN + 1], B[LV_MAXLEN + 1];
+    memset(A, 0, sizeof A); memset(B, 0, sizeof B);
+    memcpy(A, read, (size_t)m); memcpy(B, ref, (size_t)n);
+    /* [lane][e] tables, -2 = not reached */
+    static __thread int st[2 * GO_MAX_K + 3][LV_AF + 1], en[2 * GO_MAX_K + 3][LV_AF + 1];
+    static __thread int ip[2 * GO_MAX_K + 3][LV_AF + 1], dp[2 * GO_MAX_K + 3][LV_AF + 1];
+    for (int l = 0; l < total; ++l)
+        for (int q = 0; q <= LV_AF; ++q) st[l][q] = en[l][q] = ip[l][q] = dp[l][q] = -2;
+    st[mid][0] = 0;   /* ED_GLOBAL: only the main lane starts at error level 0 (:99-101) */
+#define LV_EXT(l, pos, out) do { \
+        int ao_ = (l) < mid ? mid - (l) : 0, bo_ = (l) > mid ? (l) - mid : 0, p_ = (pos); \
+        while (p_ < L && p_ - ao_ >= 0 && p_ - bo_ >= 0 && A[p_ - ao_] == B[p_ - bo_]) ++p_; \
+        (out) = p_; } while (0)
+    int pass = 0, final_ed = 0, converge = 1000000;
+    for (int l = 1; l < total - 1; ++l) {
+        if (st[l][0] >= 0) {
+            LV_EXT(l, st[l][0], en[l][0]);
+            if (en[l][0] == L) return 0;
+        }
+    }
+    for (int q = 1; q <= LV_AF; ++q) {
+        for (int l = 1; l < total - 1; ++l) {
+            const int top = l >= mid, bot = l <= mid;
+            if (q >= o && en[l - 1][q - o] >= 0 && en[l - 1][q - o] > ip[l - 1][q - e]) ip[l][q] = en[l - 1][q - o] + top;
+            else if (q >= e && ip[l - 1][q - e] >= 0) ip[l][q] = ip[l - 1][q - e] + top;
+            if (q >= o && en[l + 1][q - o] >= 0 && en[l + 1][q - o] > dp[l + 1][q - e]) dp[l][q] = en[l + 1][q - o] + bot;
+            else if (q >= e && dp[l + 1][q - e] >= 0) dp[l][q] = dp[l + 1][q - e] + bot;
+            int s0 = -2;
+            if (q >= x && en[l][q - x] >= 0) s0 = en[l][q - x] + 1;
+            if (ip[l][q] > s0) s0 = ip[l][q];
+            if (dp[l][q] > s0) s0 = dp[l][q];
+            st[l][q] = s0;
+            if (s0 >= 0) {
+                LV_EXT(l, s0, en[l][q]);
+                if (en[l][q] == L) {
+                    const int d = abs(mid - l);
+                    const int conv = q + (d ? o + (d - 1) * e : 0);
+                    if (conv <= LV_AF && conv < converge) { final_ed = q; pass = 1; converge = conv; }
+                }
+            }
+        }
+        if (pass) break;
+    }
+#undef LV_EXT
+    return pass ? final_ed : INT32_MIN;
+}
+
+static void* leap_shard(void* arg) {
+    shard_t* s = (shard_t*)arg;
+    for (int64_t i = s->lo; i < s->hi; ++i)
+        s->cost[i] = go_leap(s->reads + s->read_off[i], (int)(s->read_off[i + 1] - s->read_off[i]),
+                             s->refs + s->ref_off[i], (int)(s->ref_off[i + 1] - s->ref_off[i]), s->stride, s->x, s->o, s->e);
+    return NULL;
+}
+
+int go_leap_batch(const char* reads, const uint32_t* read_off, const char* refs, const uint32_t* ref_off,
+                  int64_t n, int k, int x, int o, int e, int threads, int32_t* penalty) {
+    shard_t proto; memset(&proto, 0, sizeof proto);
+    proto.reads = reads; proto.read_off = read_off; proto.refs = refs; proto.ref_off = ref_off;
+    proto.cost = penalty; proto.x = x; proto.o = o; proto.e = e; proto.stride = k;
+    shard_t sh[256];
+    if (threads > 256) threads = 256;
+    run_shards(leap_shard, &proto, n, threads, sh);
+    return 0;
+}
+
+/* ------------------------------------------------------------------------------------------
  * coverage metric, benchmark_coverage.h:26-67 and :73-91, on encoded ops
  * ---------------------------------------------------------------------------------------- */
 int go_lcm(const char* s1, int s1_len, const uint16_t* ops, int nops, int threshold, char* out, int cap) {

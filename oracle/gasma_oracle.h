@@ -63,6 +63,12 @@ int go_nw_batch(const char* reads, const uint32_t* read_off, const char* refs, c
                 int64_t n, int x, int o, int e, int threads, int32_t* penalty,
                 uint16_t* ops, uint32_t* op_off, int64_t ops_cap);
 
+/* LEAP comparator (GASMA/benchmark/LEAP_SIMD/LV_BAG.cpp as driven by benchmark_utils.h:156-178,289):
+ * the penalty the benchmark records for it, INT32_MIN if no lane converges within 200 errors. */
+int go_leap(const char* read, int m, const char* ref, int n, int k, int x, int o, int e);
+int go_leap_batch(const char* reads, const uint32_t* read_off, const char* refs, const uint32_t* ref_off,
+                  int64_t n, int k, int x, int o, int e, int threads, int32_t* penalty);
+
 /* benchmark_coverage.h:26-67 / :73-91 on encoded ops */
 int go_lcm(const char* s1, int s1_len, const uint16_t* ops, int nops, int threshold, char* out, int cap);
 int go_covers(const char* a, int na, const char* b, int nb);

@@ -70,6 +70,8 @@ def oracle():
         L.go_lcm.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int]
         L.go_covers.restype = C.c_int
         L.go_covers.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+        L.go_leap_batch.restype = C.c_int
+        L.go_leap_batch.argtypes = [C.c_void_p] * 4 + [C.c_int64] + [C.c_int] * 5 + [C.c_void_p]
         _oracle = L
     return _oracle
 
@@ -91,6 +93,9 @@ def ref():
         L.gasma_ref_covers.restype = C.c_int
         L.gasma_ref_covers.argtypes = [C.c_char_p, C.c_char_p]
         L.gasma_ref_significance.argtypes = [C.c_double] * 3 + [C.c_void_p]
+        if hasattr(L, "gasma_ref_leap_batch"):
+            L.gasma_ref_leap_batch.restype = C.c_int
+            L.gasma_ref_leap_batch.argtypes = [C.c_void_p] * 4 + [C.c_int64] + [C.c_int] * 6 + [C.c_void_p] * 2
         _ref = L
     return _ref
 
@@ -272,6 +277,24 @@ def ref_greedy(b, k=3, x=1, o=1, e=1, probs=DEFAULT_PROBS, mode=0, threads=1, wa
     if want_text:
         out["text"] = [text[i * stride:(i + 1) * stride].tobytes().split(b"\0")[0].decode() for i in range(b.n)]
     return out
+
+
+def oracle_leap(b, k=3, x=1, o=1, e=1, threads=1):
+    """LEAP comparator penalties (plain-C restatement); INT32_MIN = no lane converged."""
+    pen = np.zeros(b.n, np.int32)
+    rc = oracle().go_leap_batch(_ptr(b.reads), _ptr(b.read_off), _ptr(b.refs), _ptr(b.ref_off), b.n, k, x, o, e, threads, _ptr(pen))
+    assert rc == 0
+    return pen
+
+
+def ref_leap(b, k=3, x=1, o=1, e=1, mode=0, threads=1):
+    """The unmodified class LV driven like benchmark::_run_LEAP; mode 0 = one object per thread, 1 = fresh per pair."""
+    pen = np.zeros(b.n, np.int32)
+    ok = np.zeros(b.n, np.uint8)
+    rc = ref().gasma_ref_leap_batch(_ptr(b.reads), _ptr(b.read_off), _ptr(b.refs), _ptr(b.ref_off), b.n, k, x, o, e, mode,
+                                    threads, _ptr(pen), _ptr(ok))
+    assert rc == 0
+    return pen, ok
 
 
 def ref_convert2bit1(buf128):
