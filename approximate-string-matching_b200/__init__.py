@@ -44,7 +44,7 @@ EXPORTS = [
     "gasma_pack2bit_batch", "gasma_pack2bit_batch_dev", "gasma_greedy_batch", "gasma_greedy_batch_dev",
     "gasma_nw_batch", "gasma_nw_batch_dev", "gasma_metrics_dev",
     "gasma_generate_ref_capacity", "gasma_generate_dev", "gasma_generate", "gasma_render_cigar",
-    "gasma_benchmark_batch", "gasma_benchmark_batch_dev",
+    "gasma_benchmark_batch", "gasma_benchmark_batch_dev", "gasma_leap_batch", "gasma_leap_batch_dev",
 ]
 
 _lib = None
@@ -90,6 +90,8 @@ def lib():
     L.gasma_generate.argtypes = [vp, C.POINTER(GenConfig), C.c_uint64, i64, vp, vp, vp, vp]
     L.gasma_benchmark_batch.argtypes = [vp, vp, vp, vp, vp, i64, vp, vp, vp, vp, vp]
     L.gasma_benchmark_batch_dev.argtypes = [vp, vp, vp, vp, vp, i64, vp, vp, vp, vp]
+    for name in ("gasma_leap_batch", "gasma_leap_batch_dev"):
+        getattr(L, name).argtypes = [vp, vp, vp, vp, vp, i64, vp]
     _lib = L
     return L
 
@@ -197,6 +199,18 @@ class Aligner:
         if want_ops:
             out["n_ops"] = int(out["op_off"][n])
         return out
+
+    def leap_batch(self, reads, read_off, refs, ref_off):
+        """LEAP comparator penalties (benchmark::_run_LEAP); INT32_MIN where no lane converges."""
+        n = len(read_off) - 1
+        pen = np.empty(n, np.int32)
+        self._check(self._L.gasma_leap_batch(self._ctx, _np_ptr(reads), _np_ptr(read_off), _np_ptr(refs), _np_ptr(ref_off), n,
+                                             _np_ptr(pen)))
+        return pen
+
+    def leap_batch_dev(self, d_reads, d_read_off, d_refs, d_ref_off, n, d_penalty):
+        self._check(self._L.gasma_leap_batch_dev(self._ctx, _dev_ptr(d_reads), _dev_ptr(d_read_off), _dev_ptr(d_refs),
+                                                 _dev_ptr(d_ref_off), n, _dev_ptr(d_penalty)))
 
     def nw_batch(self, reads, read_off, refs, ref_off, bound=None, want_ops=True, ops_cap=None):
         n = len(read_off) - 1

@@ -13,6 +13,7 @@
 #include <string>
 
 #include "kernels.cuh"
+#include "leap.cuh"
 #include "greedy_warp.cuh"
 #include "nw_kernels.cuh"
 #include "generate.cuh"
@@ -58,10 +59,10 @@ struct gasma_ctx {
     DevBuf bm_gops, bm_goff, bm_nops, bm_noff, bm_gcost, bm_nwpen, bm_counters, bm_answers, bm_hard;
     int64_t bm_gcap = 0, bm_ncap = 0;
     uint32_t* h_misc = nullptr;  // pinned, 32 words: [0..3] device misc mirror, [8..9] op totals, [10..17] counters
-    // timing hooks: a ring of event pairs per dominant kernel (0 = greedy, 1 = NW), read by gasma_kernel_time_ms
+    // timing hooks: a ring of event pairs per dominant kernel (0 = greedy, 1 = NW, 2 = LEAP), read by gasma_kernel_time_ms
     static constexpr int kRing = 64;
-    cudaEvent_t ev[2][kRing][2] = {};
-    int64_t ev_count[2] = {0, 0};   // launches recorded since the last read
+    cudaEvent_t ev[3][kRing][2] = {};
+    int64_t ev_count[3] = {0, 0, 0};   // launches recorded since the last read
 };
 
 namespace {
@@ -291,6 +292,7 @@ void gasma_destroy(gasma_ctx* c) {
         if (c->ev_off[i]) cudaEventDestroy(c->ev_off[i]);
     }
     if (c->ev_fence) cudaEventDestroy(c->ev_fence);
+    for (cudaEvent_t e : {c->ev_t0, c->ev_t1, c->ev_t2}) if (e) cudaEventDestroy(e);
     if (c->copy_in) cudaStreamDestroy(c->copy_in);
     if (c->copy_out) cudaStreamDestroy(c->copy_out);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -333,7 +335,7 @@ int64_t gasma_launch_count(const gasma_ctx* ctx) { return ctx ? ctx->launches : 
 
 double gasma_kernel_time_ms(gasma_ctx* ctx, int which, int64_t* launches) {
     if (launches) *launches = 0;
-    if (!ctx || which < 0 || which > 1) return -1.0;
+    if (!ctx || which < 0 || which > 2) return -1.0;
     const int64_t cnt = ctx->ev_count[which];
     const int64_t take = cnt < gasma_ctx::kRing ? cnt : gasma_ctx::kRing;
     double total = 0.0;
@@ -698,4 +700,5 @@ int gasma_generate_dev(gasma_ctx* ctx, const gasma_gen_config* cfg, uint64_t fir
 // K4 / K5 entry points (nw.cuh / metrics.cuh)
 // =================================================================================================
 #include "nw_entry.inl"
+#include "leap_entry.inl"
 #include "bench_entry.inl"

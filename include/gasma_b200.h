@@ -89,7 +89,7 @@ int gasma_synchronize(gasma_ctx* ctx);
 int64_t gasma_launch_count(const gasma_ctx* ctx);
 /* Measurement hook for bench.py: summed device time (CUDA events recorded on the context's stream around
  * every launch) of the dominant kernel since the previous call -- which = 0 the greedy kernel (K2+K3),
- * 1 the NW kernel (K4).  *launches receives how many launches the sum covers (the last 64 at most).
+ * 1 the NW kernel (K4), 2 the LEAP comparator kernel.  *launches receives how many launches the sum covers (the last 64 at most).
  * Blocks until those launches have finished. */
 double gasma_kernel_time_ms(gasma_ctx* ctx, int which, int64_t* launches);
 /* Sum of _step() calls (hurdle_matrix.h:407) over all pairs since the last call; resets the counter. */
@@ -119,6 +119,19 @@ int gasma_greedy_batch_dev(gasma_ctx* ctx,
                            const char* d_reads, const uint32_t* d_read_off,
                            const char* d_refs, const uint32_t* d_ref_off, int64_t n_pairs,
                            int32_t* d_cost, gasma_cigar_op* d_ops, int64_t ops_cap, uint32_t* d_op_off);
+
+/* -- LEAP comparator ----------------------------------------------------------- */
+/* Replaces benchmark::_run_LEAP (GASMA/benchmark/benchmark_utils.h:156-178): class LV of
+ * GASMA/benchmark/LEAP_SIMD/LV_BAG.cpp set up as init(k, 200, ED_GLOBAL, x, o, e) (:289); k, x, o, e are the
+ * context's.  penalty[i] = LV::get_ED() after run() -- the only LEAP output the report uses (its accuracy line)
+ * -- or INT32_MIN when no lane converges within 200 error levels (the reference then repeats the previous pair's
+ * value).  Needs 1 <= e <= o, x and o <= 7, max_length <= 256; characters outside {A,C,G,T} count as 'A'. */
+int gasma_leap_batch(gasma_ctx* ctx,
+                     const char* reads, const uint32_t* read_off,
+                     const char* refs, const uint32_t* ref_off, int64_t n_pairs, int32_t* penalty);
+int gasma_leap_batch_dev(gasma_ctx* ctx,
+                         const char* d_reads, const uint32_t* d_read_off,
+                         const char* d_refs, const uint32_t* d_ref_off, int64_t n_pairs, int32_t* d_penalty);
 
 /* -- K4: NW verifier ---------------------------------------------------------------------------- */
 /* Replaces benchmark::_run_nw / _run_nw_sse (benchmark_utils.h:104-150; parasail_nw_trace* with

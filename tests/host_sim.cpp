@@ -14,6 +14,7 @@
 #include "../approximate-string-matching_b200/csrc/greedy.cuh"
 #include "../approximate-string-matching_b200/csrc/nw.cuh"
 #include "../approximate-string-matching_b200/csrc/nw_myers.cuh"
+#include "../approximate-string-matching_b200/csrc/leap.cuh"
 #include "../approximate-string-matching_b200/csrc/metrics.cuh"
 #include "../approximate-string-matching_b200/csrc/generate.cuh"
 
@@ -282,6 +283,38 @@ int sim_counters(const uint8_t* reads, const uint32_t* roff, const uint8_t* refs
     return 0;
 }
 
+// LEAP comparator the way leap_kernel runs it: staged streams -> planes -> leap_pair on per-pair tables
+template <int W>
+int sim_leap(int k, int x, int o, int e, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, const uint32_t* foff,
+             int64_t n, int T, int32_t* penalty) {
+    const int depth = leap_depth(x, o, e);
+    const int nl = (2 * k + 1) * 2 * W, nr = (2 * k + 3) * depth;
+    std::vector<uint32_t> words((size_t)leap_words_per_pair(k, 2 * W, depth));
+    std::vector<uint16_t> r0(elems<W>(T)), r1(elems<W>(T)), f0(elems<W>(T)), f1(elems<W>(T));
+    for (int64_t p0 = 0; p0 < n; p0 += T) {
+        const int np = (int)std::min<int64_t>(T, n - p0);
+        std::fill(r0.begin(), r0.end(), 0); std::fill(r1.begin(), r1.end(), 0);
+        std::fill(f0.begin(), f0.end(), 0); std::fill(f1.begin(), f1.end(), 0);
+        const uint32_t rbase = roff[p0] & ~15u, fbase = foff[p0] & ~15u;
+        stage(reads, rbase, roff[p0 + np], roff[n], r0.data(), r1.data(), chunks<W>(T));
+        stage(refs, fbase, foff[p0 + np], foff[n], f0.data(), f1.data(), chunks<W>(T));
+        for (int t = 0; t < np; ++t) {
+            const int64_t p = p0 + t;
+            const int m = (int)(roff[p + 1] - roff[p]), nn = (int)(foff[p + 1] - foff[p]);
+            uint64_t A0[W], A1[W], B0[W], B1[W];
+            extract_plane<W>(reinterpret_cast<const uint32_t*>(r0.data()), (int)(roff[p] - rbase), m, A0);
+            extract_plane<W>(reinterpret_cast<const uint32_t*>(r1.data()), (int)(roff[p] - rbase), m, A1);
+            extract_plane<W>(reinterpret_cast<const uint32_t*>(f0.data()), (int)(foff[p] - fbase), nn, B0);
+            extract_plane<W>(reinterpret_cast<const uint32_t*>(f1.data()), (int)(foff[p] - fbase), nn, B1);
+            std::fill(words.begin(), words.end(), 0xDEADBEEFu);   // the tables start as garbage on the device too
+            LeapStore S{words.data(), reinterpret_cast<int*>(words.data() + nl), reinterpret_cast<int*>(words.data() + nl + nr),
+                        reinterpret_cast<int*>(words.data() + nl + 2 * nr), 1, depth};
+            penalty[p] = leap_pair<W>(k, x, o, e, A0, A1, B0, B1, m, nn, S);
+        }
+    }
+    return 0;
+}
+
 }  // namespace
 
 extern "C" {
@@ -305,6 +338,17 @@ int sim_counters_batch(int W, int T, const uint8_t* reads, const uint32_t* roff,
         case 2: return sim_counters<2>(reads, roff, refs, foff, n, T, gcost, gops, goff, answers, penalty, counters, n_deferred);
         case 3: return sim_counters<3>(reads, roff, refs, foff, n, T, gcost, gops, goff, answers, penalty, counters, n_deferred);
         case 4: return sim_counters<4>(reads, roff, refs, foff, n, T, gcost, gops, goff, answers, penalty, counters, n_deferred);
+    }
+    return -1;
+}
+
+int sim_leap_batch(int W, int T, int k, int x, int o, int e, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs,
+                   const uint32_t* foff, int64_t n, int32_t* penalty) {
+    switch (W) {
+        case 1: return sim_leap<1>(k, x, o, e, reads, roff, refs, foff, n, T, penalty);
+        case 2: return sim_leap<2>(k, x, o, e, reads, roff, refs, foff, n, T, penalty);
+        case 3: return sim_leap<3>(k, x, o, e, reads, roff, refs, foff, n, T, penalty);
+        case 4: return sim_leap<4>(k, x, o, e, reads, roff, refs, foff, n, T, penalty);
     }
     return -1;
 }

@@ -83,3 +83,11 @@ def sim_counters(S, b, W, greedy, answers=None, T=128):
                               _p(answers), _p(pen), _p(counters), _p(ndef))
     assert rc == 0
     return pen, counters, int(ndef[0])
+
+
+def sim_leap(S, b, W, k=3, x=1, o=1, e=1, T=128):
+    S.sim_leap_batch.argtypes = [C.c_int] * 6 + [C.c_void_p] * 4 + [C.c_int64, C.c_void_p]
+    pen = np.zeros(b.n, np.int32)
+    rc = S.sim_leap_batch(W, T, k, x, o, e, _p(b.reads), _p(b.read_off), _p(b.refs), _p(b.ref_off), b.n, _p(pen))
+    assert rc == 0
+    return pen

@@ -108,6 +108,22 @@ def test_fused_verifier_counters_match_oracle(ol, host_sim, W):
         assert seen_deferred > 0     # the Gotoh + character-based route was exercised too
 
 
+@pytest.mark.parametrize("W", [1, 2, 3, 4])
+def test_leap_logic_matches_oracle(ol, host_sim, W):
+    """leap_pair (lane bit masks + ring tables) == the LV restatement, which is pinned to the unmodified class."""
+    rng = np.random.default_rng(5200 + W)
+    for (k, x, o, e) in ((3, 1, 1, 1), (5, 1, 2, 1), (3, 2, 3, 1), (8, 4, 6, 2)):
+        for max_err, indel in ((0.08, 0.2), (0.3, 0.4), (0.95, 0.5)):
+            b = ol.random_batch(rng, 500, 0, 64 * W, max_err, indel, 50)
+            exp = ol.oracle_leap(b, k, x, o, e, threads=4)
+            got = sim_lib.sim_leap(host_sim, b, W, k, x, o, e)
+            assert got.tolist() == exp.tolist(), (k, x, o, e, max_err)
+    pairs = [(b"", b""), (b"ACGT", b""), (b"", b"ACGT"), (b"A" * (64 * W), b"T" * (64 * W)), (b"ACGT" * (16 * W), b"ACGT" * (16 * W)),
+             (b"ACGTACGTAC", b"ACGTTACGTAC"), (b"C" * 40, b"C" * 37)]
+    b = ol.Batch.from_pairs(pairs)
+    assert sim_lib.sim_leap(host_sim, b, W).tolist() == ol.oracle_leap(b).tolist()
+
+
 def test_generator_logic_matches_oracle_twin(ol, host_sim):
     host_sim.sim_generate_pair.argtypes = [C.c_uint64] + [C.c_int] * 3 + [C.c_uint64] * 5 + [C.c_void_p] * 3
     for mode, e, prof in [(0, 0.10, None), (1, 0.20, None), (2, 0.0, (0.02452, 0.0468, 0.0553)), (0, 0.15, None)]:
