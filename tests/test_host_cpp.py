@@ -84,3 +84,8 @@ def test_benchmark_driver_report_matches_oracle(drivers, ol, tmp_path):
     assert acc.group(1) == "%.3f" % (nwc / total * 100)
     assert acc.group(2) == "%.3f" % (gc / total * 100)
     assert covm.group(1) == "%.3f" % (cov / total * 100)
+    # the LEAP rows: penalties of the LV restatement (pinned to the unmodified class) against the NW optimum
+    leap = ol.oracle_leap(b, threads=8)
+    lacc = re.search(r"\[Accuracy\].*?=> LEAP             \| ([\d.]+) %", txt, re.S)
+    assert lacc.group(1) == "%.3f" % (int((leap == on["penalty"]).sum()) / total * 100)
+    assert re.search(r"\[Time\].*?=> LEAP             \| \d+\.\d{3} s", txt, re.S)
