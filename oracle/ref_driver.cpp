@@ -39,14 +39,15 @@ void run_range(const char* reads, const uint32_t* read_off, const char* refs, co
     char fill[MAX_LENGTH];
     memset(fill, 'A', sizeof(fill));
     // one aligner object per thread, exactly as benchmark_utils.h:287 builds it
-    hurdle_matrix<int_128bit> matrix(GLOBAL, p.x, p.o, p.e, p.pm, p.pmm, p.pid);
+    // mode bit 1 selects SEMI_GLOBAL (utils.h:554-558); bit 0 = benchmark mode (no canonical prefill)
+    hurdle_matrix<int_128bit> matrix((p.mode & 2) ? SEMI_GLOBAL : GLOBAL, p.x, p.o, p.e, p.pm, p.pmm, p.pid);
     int32_t local_need = 0;
     for (int64_t i = lo; i < hi; ++i) {
         const char* s1 = reads + read_off[i];
         const char* s2 = refs + ref_off[i];
         int l1 = (int)(read_off[i + 1] - read_off[i]);
         int l2 = (int)(ref_off[i + 1] - ref_off[i]);
-        if (p.mode == 0) matrix.reset(fill, MAX_LENGTH, fill, MAX_LENGTH, p.k);  // canonical prefill
+        if ((p.mode & 1) == 0) matrix.reset(fill, MAX_LENGTH, fill, MAX_LENGTH, p.k);  // canonical prefill
         matrix.reset(s1, l1, s2, l2, p.k);
         matrix.run();
         if (cost) cost[i] = matrix.get_cost();

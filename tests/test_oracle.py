@@ -79,6 +79,22 @@ def test_oracle_vs_reference_fresh(ol):
         assert r["text"] == f["text"]
 
 
+def test_oracle_semi_global_vs_reference(ol):
+    """SEMI_GLOBAL (no switch cost on the first step, no final lane switch; hurdle_matrix.h:314,336,578) against the
+    unmodified reference constructed with that alignment type."""
+    if not ol.ref_available():
+        pytest.skip("oracle/_ref not built (needs /root/reference)")
+    rng = np.random.default_rng(4343)
+    for (k, x, o, e) in [(3, 1, 1, 1), (5, 2, 3, 1)]:
+        b = ol.random_batch(rng, 3000, 1, 128, 0.3, 0.3, 50)
+        r = ol.oracle_greedy(b, ol.make_params(k, x, o, e, 2, 0), threads=4, want_text=True)
+        f = ol.ref_greedy(b, k, x, o, e, mode=2, threads=4)
+        assert r["cost"].tolist() == f["cost"].tolist()
+        assert r["text"] == f["text"]
+        glob = ol.ref_greedy(b, k, x, o, e, mode=0, threads=4)
+        assert (f["cost"] != glob["cost"]).mean() > 0.05     # the mode matters on this data
+
+
 def test_generator_is_deterministic_and_shaped(ol):
     cfg = ol.gen_config(0x47415341, 100, 0.10)
     assert cfg.num_errors == 10
