@@ -138,10 +138,10 @@ template <int W>
 __host__ __device__ constexpr size_t myers_smem_bytes(int tile) {
     return 4 * (size_t)stream_elems<W>(tile) * 2 + 2 * (size_t)(tile + 1) * 4 + 64;
 }
-// the banded kernel adds the per-alignment traceback windows: half of the 64W columns at a time x 2 words x 4 bytes
+// the banded kernel adds the per-alignment traceback windows: 1/kTraceParts of the 64W columns at a time x 8 bytes
 template <int W>
 __host__ __device__ constexpr size_t myers_trace_smem_bytes(int tile) {
-    return myers_smem_bytes<W>(tile) + (size_t)32 * W * 2 * 4 * tile;
+    return myers_smem_bytes<W>(tile) + (size_t)myers_trace_slots(64 * W) * sizeof(TraceCol) * tile;
 }
 
 template <int W, int T>
@@ -224,7 +224,7 @@ nw_band_kernel(const uint8_t* __restrict__ reads, const uint32_t* __restrict__ r
     constexpr bool TRACE = MODE != kNwPenalty;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     TraceCol* s_tb = reinterpret_cast<TraceCol*>(smem_raw);                       // [col][T]
-    uint16_t* s_r0 = reinterpret_cast<uint16_t*>(s_tb + (TRACE ? (size_t)(BITS / 2) * T : 0));
+    uint16_t* s_r0 = reinterpret_cast<uint16_t*>(s_tb + (TRACE ? (size_t)myers_trace_slots(BITS) * T : 0));
     uint16_t* s_r1 = s_r0 + stream_elems<W>(T);
     uint16_t* s_f0 = s_r1 + stream_elems<W>(T);
     uint16_t* s_f1 = s_f0 + stream_elems<W>(T);

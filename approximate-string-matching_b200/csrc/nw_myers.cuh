@@ -195,8 +195,8 @@ GASMA_HD int myers_band_forward(const uint64_t A0[W], const uint64_t A1[W], cons
             const uint32_t php = (ph << 1) | 1u, mhp = mh << 1;
             pv = mhp | ~(xv | php);
             mv = php & xv;
-            const uint32_t zero = (~(pv | mv) & ~(php | mhp)) | (pv & mhp) | (mv & php);   // dv + dh' == 0
-            diag0 += (int)(mv & 1u);   // bit 0: dh' = +1, so the diagonal step is free iff dv = -1
+            const uint32_t zero = xh | mvi;   // Hyyro's D0: H(i,j) == H(i-1,j-1), i.e. dv + dh' == 0
+            diag0 += (int)(zero & 1u);
             if (tb && 32 * cb + s >= j_store) {
                 const uint32_t dg = eq | ~zero;
                 *out = TraceCol{dg, eq | (~dg & pv)};
@@ -262,10 +262,17 @@ GASMA_HD void myers_trace_finish(MyersTrace& t, Sink& sink) {
     myers_trace_push(t, sink, -2, 0);
 }
 
-// Penalty and (when tb != nullptr) traceback of one alignment whose band fits the window.  HALF the columns are
-// resident: the upper half is stored and walked first, then the lower half is recomputed into the same slots
-// (1.5x the column work for half the shared memory, i.e. twice the alignments in flight per SM).
-// tb holds (n + 1) / 2 entries per alignment.  Returns the penalty; the runs of the walk go to `sink`.
+// Penalty and (when tb != nullptr) traceback of one alignment whose band fits the window.  Only 1/kTraceParts of the
+// columns is resident at a time: the last part is stored and walked first, then the columns below are recomputed
+// part by part into the same slots ((kTraceParts+1)/2 x the column work for 1/kTraceParts of the shared memory,
+// i.e. that many more alignments in flight per SM).  tb holds myers_trace_slots(n) entries per alignment.
+// Returns the penalty; the runs of the walk go to `sink`.
+#ifndef GASMA_TRACE_PARTS
+#define GASMA_TRACE_PARTS 3
+#endif
+constexpr int kTraceParts = GASMA_TRACE_PARTS;
+GASMA_HD int myers_part_start(int n, int part) { return (int)((long long)n * part / kTraceParts); }
+GASMA_HD constexpr int myers_trace_slots(int max_n) { return (max_n + kTraceParts - 1) / kTraceParts; }
 template <int W, class Sink>
 GASMA_HD int myers_band_align(const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W], const uint64_t B1[W],
                               int m, int n, int hi, TraceCol* tb, int stride, Sink& sink) {
@@ -274,13 +281,15 @@ GASMA_HD int myers_band_align(const uint64_t A0[W], const uint64_t A1[W], const 
         return imax(m, n);
     }
     if (!tb) return myers_band_forward<W>(A0, A1, B0, B1, m, hi, 0, n, nullptr, 0);
-    const int split = n / 2;
-    const int pen = myers_band_forward<W>(A0, A1, B0, B1, m, hi, split, n, tb, stride);
     MyersTrace t{m, n, m - n + hi, -1, 0};
-    myers_trace_segment(t, sink, split, split, tb, stride);
-    if (t.i > 0 && t.j > 0) {
-        myers_band_forward<W>(A0, A1, B0, B1, m, hi, 0, t.j, tb, stride);
-        myers_trace_segment(t, sink, 0, 0, tb, stride);
+    int pen = 0;
+#pragma unroll
+    for (int part = kTraceParts - 1; part >= 0; --part) {
+        if (!(t.i > 0 && t.j > 0)) break;
+        const int lo = myers_part_start(n, part);
+        const int h = myers_band_forward<W>(A0, A1, B0, B1, m, hi, lo, t.j, tb, stride);   // t.j == n the first time
+        if (part == kTraceParts - 1) pen = h;
+        myers_trace_segment(t, sink, lo, lo, tb, stride);
     }
     myers_trace_finish(t, sink);
     return pen;
@@ -322,7 +331,7 @@ GASMA_HD void myers_cover_segment(CoverTrace<W>& t, int j_lo, int j_store, const
         col -= dj ? stride : 0;
     }
 }
-// Penalty + E/B masks of one alignment whose band fits the window (same half-resident scheme as myers_band_align).
+// Penalty + E/B masks of one alignment whose band fits the window (same part-resident scheme as myers_band_align).
 template <int W>
 GASMA_HD int myers_band_cover(const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W], const uint64_t B1[W],
                               int m, int n, int hi, TraceCol* tb, int stride, CoverTrace<W>& t) {
@@ -331,12 +340,14 @@ GASMA_HD int myers_band_cover(const uint64_t A0[W], const uint64_t A1[W], const 
 #pragma unroll
     for (int w = 0; w < 2 * W; ++w) { t.E[w] = 0u; t.B[w] = 0u; }
     if (m == 0 || n == 0) return imax(m, n);   // only I or only D: no '=' at all
-    const int split = n / 2;
-    const int pen = myers_band_forward<W>(A0, A1, B0, B1, m, hi, split, n, tb, stride);
-    myers_cover_segment<W>(t, split, split, tb, stride);
-    if (t.i > 0 && t.j > 0) {
-        myers_band_forward<W>(A0, A1, B0, B1, m, hi, 0, t.j, tb, stride);
-        myers_cover_segment<W>(t, 0, 0, tb, stride);
+    int pen = 0;
+#pragma unroll
+    for (int part = kTraceParts - 1; part >= 0; --part) {
+        if (!(t.i > 0 && t.j > 0)) break;
+        const int lo = myers_part_start(n, part);
+        const int h = myers_band_forward<W>(A0, A1, B0, B1, m, hi, lo, t.j, tb, stride);
+        if (part == kTraceParts - 1) pen = h;
+        myers_cover_segment<W>(t, lo, lo, tb, stride);
     }
     if (t.i > 0) {   // rows left at column 0 are an I run; the word under construction still has to land
         t.E[(t.i - 1) >> 5] = t.e;
