@@ -40,7 +40,7 @@ class GenConfig(C.Structure):
 # every symbol include/gasma_b200.h declares (tests check that the library exports all of them)
 EXPORTS = [
     "gasma_default_params", "gasma_create", "gasma_destroy", "gasma_last_error", "gasma_set_band",
-    "gasma_set_stream", "gasma_synchronize", "gasma_launch_count", "gasma_kernel_time_ms", "gasma_last_step_count",
+    "gasma_set_correction", "gasma_set_stream", "gasma_synchronize", "gasma_launch_count", "gasma_kernel_time_ms", "gasma_last_step_count",
     "gasma_pack2bit_batch", "gasma_pack2bit_batch_dev", "gasma_greedy_batch", "gasma_greedy_batch_dev",
     "gasma_nw_batch", "gasma_nw_batch_dev", "gasma_metrics_dev",
     "gasma_generate_ref_capacity", "gasma_generate_dev", "gasma_generate", "gasma_render_cigar",
@@ -68,6 +68,7 @@ def lib():
     L.gasma_last_error.argtypes = [vp]
     L.gasma_last_error.restype = C.c_char_p
     L.gasma_set_band.argtypes = [vp, i32]
+    L.gasma_set_correction.argtypes = [vp, i32, i32]
     L.gasma_set_stream.argtypes = [vp, vp]
     L.gasma_synchronize.argtypes = [vp]
     L.gasma_launch_count.argtypes = [vp]
@@ -151,6 +152,11 @@ class Aligner:
     def set_band(self, k):
         self._check(self._L.gasma_set_band(self._ctx, k))
         self.params.k = k
+
+    def set_correction(self, enabled, max_delta=0):
+        """The reference's -DCORRECTION band (hurdle_matrix.h:634-641): lanes widened towards lane n-m; max_delta =
+        largest |ref_len - read_len| the context keeps lane slots for."""
+        self._check(self._L.gasma_set_correction(self._ctx, 1 if enabled else 0, max_delta))
 
     def set_stream(self, cuda_stream_ptr):
         self._check(self._L.gasma_set_stream(self._ctx, C.c_void_p(cuda_stream_ptr)))

@@ -35,6 +35,11 @@ struct KParams {
     int k, x, o, e;
     int global;          // 1 = GLOBAL (utils.h:554)
     double ms, mms, ids;
+    // hurdle_matrix.h:501-512, :634-641 (-DCORRECTION build of the reference): band widened towards lane n-m.
+    // nl = lane slots kept per alignment: 2k+1, or 2k+1+max_delta when correction is on (pairs with a larger
+    // |n-m| are flagged kStatusBand)
+    int correction = 0;
+    int nl = 0;
 };
 
 // ---- clamped 64-bit shifts: amount >= 64 gives 0 (PTX shl/shr.b64 semantics; C++ << would be UB) ----

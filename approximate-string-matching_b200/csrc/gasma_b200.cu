@@ -38,6 +38,8 @@ struct gasma_ctx {
     int device = 0;
     int sm_count = 148;
     int refill_threshold = 8;   // idle threads in a warp that trigger a refill from the pool (greedy kernel)
+    int correction = 0;         // gasma_set_correction: widened band of the reference's -DCORRECTION build
+    int max_delta = 0;          // largest |ref_len - read_len| the widened band has lane slots for
     cudaStream_t stream = nullptr;      // stream all work goes to
     cudaStream_t own_stream = nullptr;  // created by us
     // host-pointer calls on large batches are pipelined in slices: H2D of slice i+1 and D2H of slice i-1 overlap
@@ -119,24 +121,26 @@ void derive(gasma_ctx* c) {
     c->kp.ms = log(p.match_prob / 0.25);
     c->kp.mms = log(p.mismatch_prob / 0.25);
     c->kp.ids = log(p.indel_prob / 2 / 0.25);
+    c->kp.correction = c->correction;
+    c->kp.nl = 2 * p.k + 1 + (c->correction ? c->max_delta : 0);
 }
 
 constexpr size_t kMaxSmem = 227 * 1024;
 
 // warps per CTA of the greedy kernel: 4 when the lanes of 128 alignments fit shared memory, else 1
 template <int W>
-int greedy_warps_for(int k) {
-    if (greedy_smem_bytes<W>(4, k) <= kMaxSmem) return 4;
-    if (greedy_smem_bytes<W>(1, k) <= kMaxSmem) return 1;
+int greedy_warps_for(int nl) {
+    if (greedy_smem_bytes<W>(4, nl) <= kMaxSmem) return 4;
+    if (greedy_smem_bytes<W>(1, nl) <= kMaxSmem) return 1;
     return 0;
 }
 
-template <int W, int WARPS>
+template <int W, int WARPS, bool CORR>
 int launch_greedy_t(gasma_ctx* ctx, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, const uint32_t* foff,
                     int64_t n, int32_t* cost, uint16_t* stage, int stride, uint32_t* nops, uint32_t* chunk_counter,
                     uint32_t* status, unsigned long long* steps) {
-    const size_t smem = greedy_smem_bytes<W>(WARPS, ctx->kp.k);
-    auto kern = greedy_kernel<W, WARPS>;
+    const size_t smem = greedy_smem_bytes<W>(WARPS, ctx->kp.nl);
+    auto kern = greedy_kernel<W, WARPS, CORR>;
     CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 32 * WARPS, smem));
@@ -157,18 +161,22 @@ template <int W>
 int launch_greedy_w(gasma_ctx* ctx, int warps, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs,
                     const uint32_t* foff, int64_t n, int32_t* cost, uint16_t* stage, int stride, uint32_t* nops,
                     uint32_t* chunk_counter, uint32_t* status, unsigned long long* steps) {
-    if (warps == 4) return launch_greedy_t<W, 4>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, chunk_counter, status, steps);
-    return launch_greedy_t<W, 1>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, chunk_counter, status, steps);
+    if (ctx->kp.correction) {
+        if (warps == 4) return launch_greedy_t<W, 4, true>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, chunk_counter, status, steps);
+        return launch_greedy_t<W, 1, true>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, chunk_counter, status, steps);
+    }
+    if (warps == 4) return launch_greedy_t<W, 4, false>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, chunk_counter, status, steps);
+    return launch_greedy_t<W, 1, false>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, chunk_counter, status, steps);
 }
 
 int greedy_tile_threads(const gasma_ctx* c) {   // 0 = configuration does not fit
     switch (c->W) {
-        case 1: return 32 * greedy_warps_for<1>(c->kp.k);
-        case 2: return 32 * greedy_warps_for<2>(c->kp.k);
-        case 3: return 32 * greedy_warps_for<3>(c->kp.k);
-        case 4: return 32 * greedy_warps_for<4>(c->kp.k);
-        case 8: return 4 * WarpLayout<8>::bytes_per_warp(c->kp.k) + 64 <= kMaxSmem ? 128 : 0;
-        default: return 4 * WarpLayout<16>::bytes_per_warp(c->kp.k) + 64 <= kMaxSmem ? 128 : 0;
+        case 1: return 32 * greedy_warps_for<1>(c->kp.nl);
+        case 2: return 32 * greedy_warps_for<2>(c->kp.nl);
+        case 3: return 32 * greedy_warps_for<3>(c->kp.nl);
+        case 4: return 32 * greedy_warps_for<4>(c->kp.nl);
+        case 8: return 4 * WarpLayout<8>::bytes_per_warp(c->kp.nl) + 64 <= kMaxSmem ? 128 : 0;
+        default: return 4 * WarpLayout<16>::bytes_per_warp(c->kp.nl) + 64 <= kMaxSmem ? 128 : 0;
     }
 }
 
@@ -178,7 +186,7 @@ int launch_greedy_warp(gasma_ctx* ctx, const uint8_t* reads, const uint32_t* rof
                        int64_t n, int32_t* cost, uint16_t* stage, int stride, uint32_t* nops, uint32_t* pair_counter,
                        uint32_t* status, unsigned long long* steps) {
     constexpr int WARPS = 4;
-    const size_t smem = WARPS * ((WarpLayout<W>::bytes_per_warp(ctx->kp.k) + 15) / 16 * 16);
+    const size_t smem = WARPS * ((WarpLayout<W>::bytes_per_warp(ctx->kp.nl) + 15) / 16 * 16);
     auto kern = greedy_warp_kernel<W, WARPS>;
     CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
@@ -196,7 +204,12 @@ int launch_greedy_warp(gasma_ctx* ctx, const uint8_t* reads, const uint32_t* rof
 
 int check_status(gasma_ctx* ctx, uint32_t st) {
     if (st & (kStatusLength | kStatusTile)) return fail(ctx, GASMA_E_LENGTH, "a string is longer than max_length=%d", ctx->params.max_length);
-    if (st & kStatusBand) return fail(ctx, GASMA_E_BAND, "|ref_len - read_len| > MAX_K=%d (out of bounds in the reference)", GASMA_MAX_K);
+    if (st & kStatusBand) {
+        if (ctx->correction)
+            return fail(ctx, GASMA_E_BAND, "|ref_len - read_len| > max_delta=%d of the widened band, or |ref_len - read_len| + k > MAX_K=%d",
+                        ctx->max_delta, GASMA_MAX_K);
+        return fail(ctx, GASMA_E_BAND, "|ref_len - read_len| > MAX_K=%d (out of bounds in the reference)", GASMA_MAX_K);
+    }
     if (st & kStatusSteps) return fail(ctx, GASMA_E_INTERNAL, "greedy traversal hit the step limit");
     return GASMA_OK;
 }
@@ -304,6 +317,8 @@ const char* gasma_last_error(const gasma_ctx* ctx) { return ctx ? ctx->err.c_str
 int gasma_set_band(gasma_ctx* ctx, int k) {
     if (!ctx) return GASMA_E_ARG;
     if (k < 0 || k > GASMA_MAX_K) return fail(ctx, GASMA_E_BAND, "k=%d outside [0, %d]", k, GASMA_MAX_K);
+    if (ctx->correction && k + ctx->max_delta > GASMA_MAX_K)
+        return fail(ctx, GASMA_E_BAND, "k=%d + max_delta=%d of the widened band exceeds MAX_K=%d", k, ctx->max_delta, GASMA_MAX_K);
     int old = ctx->params.k;
     ctx->params.k = k;
     derive(ctx);
@@ -311,6 +326,23 @@ int gasma_set_band(gasma_ctx* ctx, int k) {
         ctx->params.k = old;
         derive(ctx);
         return fail(ctx, GASMA_E_UNSUPPORTED, "k=%d with max_length=%d does not fit shared memory", k, ctx->params.max_length);
+    }
+    return GASMA_OK;
+}
+
+int gasma_set_correction(gasma_ctx* ctx, int enabled, int max_delta) {
+    if (!ctx) return GASMA_E_ARG;
+    if (enabled && (max_delta < 0 || max_delta + ctx->params.k > GASMA_MAX_K))
+        return fail(ctx, GASMA_E_BAND, "max_delta=%d: need 0 <= max_delta and max_delta + k <= MAX_K=%d", max_delta, GASMA_MAX_K);
+    const int old_c = ctx->correction, old_d = ctx->max_delta;
+    ctx->correction = enabled ? 1 : 0;
+    ctx->max_delta = enabled ? max_delta : 0;
+    derive(ctx);
+    if (greedy_tile_threads(ctx) == 0) {
+        ctx->correction = old_c; ctx->max_delta = old_d;
+        derive(ctx);
+        return fail(ctx, GASMA_E_UNSUPPORTED, "k=%d + max_delta=%d lanes with max_length=%d do not fit shared memory", ctx->params.k,
+                    max_delta, ctx->params.max_length);
     }
     return GASMA_OK;
 }

@@ -234,29 +234,42 @@ struct PairState {
     int cl, cc;      // current lane / column
     int cost, steps;
     bool first;      // is_first_step (hurdle_matrix.h:572)
+    int lb, ub;      // lane range of this pair; only read by the CORR instantiations (otherwise it is -k..k)
 };
 
+// Lane range of one pair (hurdle_matrix.h:634-644).  The reference's default build uses -k..k; built with
+// -DCORRECTION it widens the band towards the destination lane n-m: [-k, n-m+k] for m <= n, [n-m-k, k] otherwise.
+// CORR selects that variant at compile time, as the reference does, so the default kernels carry none of it.
+template <bool CORR>
+GASMA_HD void lane_range(int k, int m, int n, int& lb, int& ub) {
+    lb = -k; ub = k;
+    if (CORR) { if (m <= n) ub = n - m + k; else lb = n - m - k; }
+}
+
 // reset(): highways::reset (:106-119) + _construct_hurdles (:441-455)
-template <int W>
+template <int W, bool CORR = false>
 GASMA_HD void pair_init(const KParams& P, const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W],
                         const uint64_t B1[W], int m, int n, const LaneStore& S, PairState& ps) {
     constexpr int BITS = 64 * W;
-    const int k = P.k;
-    for (int l = -k; l <= k; ++l) {
+    int lb, ub;
+    lane_range<CORR>(P.k, m, n, lb, ub);
+    for (int l = lb; l <= ub; ++l) {
         uint64_t og[W];
         build_lane<W>(A0, A1, B0, B1, l, og);
-        lane_store<W>(S, l + k, og);
-        S.state[(l + k) * S.stride] = st_pack(-1, 0, BITS, BITS);
+        lane_store<W>(S, l - lb, og);
+        S.state[(l - lb) * S.stride] = st_pack(-1, 0, BITS, BITS);
     }
+    ps.lb = lb; ps.ub = ub;
     ps.m = m; ps.n = n; ps.cl = 0; ps.cc = 0; ps.cost = 0; ps.steps = 0; ps.first = true;
 }
 
 // One _step() (hurdle_matrix.h:407-434) including its _update_highway_list and _choose_best_highway.
 // Returns true when the traversal is over (the caller then runs pair_finish).
-template <int W>
+template <int W, bool CORR = false>
 GASMA_HD bool pair_step(const KParams& P, const LaneStore& S, PairState& ps, OpSink& sink, uint32_t& status) {
     constexpr int BITS = 64 * W;
-    const int k = P.k, x = P.x, o = P.o, e = P.e;
+    const int x = P.x, o = P.o, e = P.e;
+    const int lb = CORR ? ps.lb : -P.k, ub = CORR ? ps.ub : P.k;
     const bool GLOBAL = P.global != 0;
     const int m = ps.m, n = ps.n, cl = ps.cl, cc = ps.cc;
     const bool leap_cost = GLOBAL || !ps.first;
@@ -268,8 +281,8 @@ GASMA_HD bool pair_step(const KParams& P, const LaneStore& S, PairState& ps, OpS
     bool reach = false;
     double bestH_s = 0.0; int bestLeap_s = 0, bl_s = 0; uint64_t st_s = 0; bool have_s = false;
     int bestH_r = 0, bestLeap_r = 0, bl_r = 0; uint64_t st_r = 0; bool have_r = false;
-    for (int l = -k; l <= k; ++l) {
-        const int li = l + k;
+    for (int l = lb; l <= ub; ++l) {
+        const int li = l - lb;
         const int sc = cc + sfc(cl, l);
         const int de = lane_destination(m, n, l);
         uint64_t st = S.state[li * S.stride];
@@ -307,10 +320,10 @@ GASMA_HD bool pair_step(const KParams& P, const LaneStore& S, PairState& ps, OpS
     const int swb = leap_cost ? slp(cl, bl, o, e) : 0;
     int sT = x * st_nh(st_bl) + swb, sI = sT, b = bl;
     uint64_t st_b = st_bl;
-    const uint32_t* ob = lane_base<W>(S, bl + k);
-    for (int l = -k; l <= k; ++l) {
+    const uint32_t* ob = lane_base<W>(S, bl - lb);
+    for (int l = lb; l <= ub; ++l) {
         if (l == bl) continue;
-        const uint64_t st = S.state[(l + k) * S.stride];
+        const uint64_t st = S.state[(l - lb) * S.stride];
         const int sp = st_sp(st), s_l = sfc(l, bl);
         if (sp + s_l > spb) continue;
         const int end = sp + st_len(st);
@@ -333,15 +346,16 @@ GASMA_HD bool pair_step(const KParams& P, const LaneStore& S, PairState& ps, OpS
 
 // run() fix-up (hurdle_matrix.h:575-590).  A destination lane outside the band keeps the state of a fresh
 // object: lane value 1 (utils.h:57-59) and destination -|lane| (hurdle_matrix.h:79-92 with m=n=0).
-template <int W>
+template <int W, bool CORR = false>
 GASMA_HD void pair_finish(const KParams& P, const LaneStore& S, PairState& ps, OpSink& sink) {
-    const int k = P.k, x = P.x;
+    const int x = P.x;
+    const int lb = CORR ? ps.lb : -P.k, ub = CORR ? ps.ub : P.k;
     const int dl = ps.n - ps.m, cl = ps.cl, cc = ps.cc;
-    const bool in_band = iabs(dl) <= k;
+    const bool in_band = dl >= lb && dl <= ub;   // always true with CORR
     const int dc = in_band ? lane_destination(ps.m, ps.n, dl) : -iabs(dl);
     if (cl != dl || cc < dc) {
         int d = 0;
-        if (in_band) d = pcb<W>(lane_base<W>(S, dl + k), S.stride, cc + sfc(cl, dl), dc);
+        if (in_band) d = pcb<W>(lane_base<W>(S, dl - lb), S.stride, cc + sfc(cl, dl), dc);
         // out of band: dc < 0 <= from, so pop_count_between of the default value 1 is 0 as well
         ps.cost += (P.global ? slp(cl, dl, P.o, P.e) : 0) + imax(0, x * d);
         sink.update(dl, cl, d);
@@ -349,15 +363,15 @@ GASMA_HD void pair_finish(const KParams& P, const LaneStore& S, PairState& ps, O
 }
 
 // The whole alignment of one pair (host harness, and kernels that do not interleave pairs).  Returns status bits.
-template <int W>
+template <int W, bool CORR = false>
 GASMA_HD uint32_t greedy_pair(const KParams& P, const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W],
                               const uint64_t B1[W], int m, int n, const LaneStore& S, OpSink& sink, int& cost_out,
                               int& steps_out) {
     PairState ps;
     uint32_t status = 0;
-    pair_init<W>(P, A0, A1, B0, B1, m, n, S, ps);
-    while (!pair_step<W>(P, S, ps, sink, status)) {}
-    pair_finish<W>(P, S, ps, sink);
+    pair_init<W, CORR>(P, A0, A1, B0, B1, m, n, S, ps);
+    while (!pair_step<W, CORR>(P, S, ps, sink, status)) {}
+    pair_finish<W, CORR>(P, S, ps, sink);
     cost_out = ps.cost;
     steps_out = ps.steps;
     return status;

@@ -19,8 +19,8 @@ struct WarpLayout {
     static constexpr int PITCH = NW + 1;          // odd pitch: threads reading the same word of 32 lanes hit 32 banks
     static constexpr int PLANE = NW + 2;          // plane words + zero padding for shifted reads
     static constexpr int STREAM = ((4 * W + 2) + 2 * 2 + 7) / 8 * 8;   // uint16 chunks of one string (+ window slack)
-    __host__ __device__ static constexpr size_t bytes_per_warp(int k) {
-        return (size_t)(2 * k + 1) * PITCH * 4 + (size_t)(2 * k + 1) * 8 + 4 * PLANE * 4 + 4 * STREAM * 2 + 16;
+    __host__ __device__ static constexpr size_t bytes_per_warp(int nl) {   // nl = lane slots per alignment (KParams::nl)
+        return (size_t)nl * PITCH * 4 + (size_t)nl * 8 + 4 * PLANE * 4 + 4 * STREAM * 2 + 16;
     }
 };
 
@@ -68,12 +68,12 @@ greedy_warp_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t*
     constexpr int BITS = 64 * W, NW = L::NW, PITCH = L::PITCH;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int k = P.k, nl = 2 * k + 1, x = P.x, o = P.o, e = P.e;
+    const int k = P.k, nl_cap = P.nl, x = P.x, o = P.o, e = P.e;
     const bool GLOBAL = P.global != 0;
-    unsigned char* mine = smem_raw + (size_t)warp * ((L::bytes_per_warp(k) + 15) / 16 * 16);
+    unsigned char* mine = smem_raw + (size_t)warp * ((L::bytes_per_warp(nl_cap) + 15) / 16 * 16);
     uint64_t* s_state = reinterpret_cast<uint64_t*>(mine);
-    uint32_t* s_lanes = reinterpret_cast<uint32_t*>(s_state + nl);
-    uint32_t* s_plane = s_lanes + (size_t)nl * PITCH;            // [4][PLANE]: A0, A1, B0, B1
+    uint32_t* s_lanes = reinterpret_cast<uint32_t*>(s_state + nl_cap);
+    uint32_t* s_plane = s_lanes + (size_t)nl_cap * PITCH;        // [4][PLANE]: A0, A1, B0, B1
     uint16_t* s_stream = reinterpret_cast<uint16_t*>(s_plane + 4 * L::PLANE);   // [4][STREAM]
     for (int i = lane; i < 4 * L::STREAM; i += 32) s_stream[i] = 0;
     const uint32_t rtotal = read_off[n], ftotal = ref_off[n];
@@ -91,6 +91,7 @@ greedy_warp_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t*
         uint32_t bad = 0;
         if (m > BITS || nn > BITS) bad |= kStatusLength;
         else if (iabs(nn - m) > kMaxK) bad |= kStatusBand;
+        else if (P.correction && (iabs(nn - m) + k > kMaxK || 2 * k + 1 + iabs(nn - m) > nl_cap)) bad |= kStatusBand;
         if (bad) {
             st_bits |= bad;
             if (lane == 0) { cost[p] = INT32_MIN; if (nops_out) nops_out[p] = 0u; }
@@ -112,8 +113,12 @@ greedy_warp_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t*
         }
         __syncwarp();
         // ---- K2: lanes (_construct_hurdles, hurdle_matrix.h:441-455) and highway cache reset (:106-119) ----
+        // lane range of this pair: -k..k, or the widened band of the -DCORRECTION build (hurdle_matrix.h:634-641)
+        int lb = -k, ub = k;
+        if (P.correction) { if (m <= nn) ub = nn - m + k; else lb = nn - m - k; }
+        const int nl = ub - lb + 1;
         for (int li = lane; li < nl; li += 32) {
-            const int l = li - k, a = iabs(l), aw = a >> 5, ab = a & 31;
+            const int l = li + lb, a = iabs(l), aw = a >> 5, ab = a & 31;
             const uint32_t* X0 = s_plane + (l < 0 ? 0 : 2) * L::PLANE;   // the shifted string: read for l<0, ref for l>=0
             const uint32_t* X1 = X0 + L::PLANE;
             const uint32_t* Y0 = s_plane + (l < 0 ? 2 : 0) * L::PLANE;
@@ -150,7 +155,7 @@ greedy_warp_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t*
             bool reach_local = false;
             WarpCand cs{0.0, 0, 0, 0ull, false}, cr{0.0, 0, 0, 0ull, false};
             for (int li = lane; li < nl; li += 32) {
-                const int l = li - k;
+                const int l = li + lb;
                 const uint32_t* row = s_lanes + (size_t)li * PITCH;
                 const int sc = cc + sfc(cl, l);
                 const int de = lane_destination(m, nn, l);
@@ -187,9 +192,9 @@ greedy_warp_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t*
             const int spb = st_sp(best.st);
             int sT = x * st_nh(best.st) + (leap_cost ? slp(cl, bl, o, e) : 0), sI = sT, b = bl;
             uint64_t st_b = best.st;
-            const uint32_t* ob = s_lanes + (size_t)(bl + k) * PITCH;
+            const uint32_t* ob = s_lanes + (size_t)(bl - lb) * PITCH;
             for (int base = 0; base < nl; base += 32) {
-                const int li = base + lane, l = li - k;
+                const int li = base + lane, l = li + lb;
                 bool ok = li < nl && l != bl;
                 int tc = 0, ic = 0;
                 uint64_t stv = 0;
@@ -211,7 +216,7 @@ greedy_warp_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t*
                     sT = __shfl_sync(0xffffffffu, tc, after);
                     sI = __shfl_sync(0xffffffffu, ic, after);
                     st_b = __shfl_sync(0xffffffffu, stv, after);
-                    b = base + after - k;
+                    b = base + after + lb;
                 }
             }
             // _step (:412-433)
@@ -225,11 +230,11 @@ greedy_warp_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t*
         }
         // run() fix-up (:575-590)
         {
-            const bool in_band = iabs(dl) <= k;
+            const bool in_band = dl >= lb && dl <= ub;
             const int dc = in_band ? lane_destination(m, nn, dl) : -iabs(dl);
             if (cl != dl || cc < dc) {
                 int d = 0;
-                if (in_band) d = pcb<W>(s_lanes + (size_t)(dl + k) * PITCH, 1, cc + sfc(cl, dl), dc);
+                if (in_band) d = pcb<W>(s_lanes + (size_t)(dl - lb) * PITCH, 1, cc + sfc(cl, dl), dc);
                 pen += (GLOBAL ? slp(cl, dl, o, e) : 0) + imax(0, x * d);
                 update_cigar(dl, cl, d);
             }

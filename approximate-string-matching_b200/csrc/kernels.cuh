@@ -76,14 +76,14 @@ __host__ __device__ constexpr int stream_elems(int tile) { return ((stream_chunk
 constexpr int kPool = 32;   // pairs per chunk = per warp pool
 
 template <int W>
-__host__ __device__ constexpr size_t greedy_smem_bytes(int warps, int k) {
-    return (size_t)(2 * k + 1) * (2 * W * 4 + 8) * 32 * warps   // lanes (2W 32-bit words) + state, per thread
+__host__ __device__ constexpr size_t greedy_smem_bytes(int warps, int nl) {   // nl = lane slots per alignment (KParams::nl)
+    return (size_t)nl * (2 * W * 4 + 8) * 32 * warps   // lanes (2W 32-bit words) + state, per thread
            + (size_t)warps * (4 * (size_t)stream_elems<W>(kPool) * 2 + 2 * (kPool + 1) * 4)   // per-warp streams + offsets
            + 64;
 }
 
-template <int W, int WARPS>
-__global__ void __launch_bounds__(32 * WARPS, WARPS == 4 ? 5 : 1)
+template <int W, int WARPS, bool CORR>
+__global__ void __launch_bounds__(32 * WARPS, WARPS == 4 && !CORR ? 5 : 1)
 greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __restrict__ read_off,
               const uint8_t* __restrict__ refs, const uint32_t* __restrict__ ref_off, long long n,
               int32_t* __restrict__ cost, uint16_t* __restrict__ ops_stage, int ops_stride,
@@ -93,7 +93,7 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
     constexpr int T = 32 * WARPS;
     constexpr int SE = stream_elems<W>(kPool);
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int nl = 2 * P.k + 1;
+    const int nl = P.nl;
     uint64_t* s_state = reinterpret_cast<uint64_t*>(smem_raw);
     uint32_t* s_lanes = reinterpret_cast<uint32_t*>(s_state + (size_t)nl * T);
     uint16_t* s_streams = reinterpret_cast<uint16_t*>(s_lanes + (size_t)nl * 2 * W * T);
@@ -202,6 +202,8 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
                 if (!pool_ok) bad |= kStatusTile;
                 if (m > BITS || nn > BITS) bad |= kStatusLength;
                 else if (iabs(nn - m) > kMaxK) bad |= kStatusBand;
+                // widened band: the reference's lane arrays end at MAX_K, ours at the nl slots of this context
+                else if (CORR && (iabs(nn - m) + P.k > kMaxK || 2 * P.k + 1 + iabs(nn - m) > nl)) bad |= kStatusBand;
                 if (bad) {
                     st |= bad;
                     cost[my_p] = INT32_MIN;
@@ -213,7 +215,7 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
                     extract_plane<W>(reinterpret_cast<const uint32_t*>(s_r1), rbit, m, A1);
                     extract_plane<W>(reinterpret_cast<const uint32_t*>(s_f0), fbit, nn, B0);
                     extract_plane<W>(reinterpret_cast<const uint32_t*>(s_f1), fbit, nn, B1);
-                    pair_init<W>(P, A0, A1, B0, B1, m, nn, S, ps);
+                    pair_init<W, CORR>(P, A0, A1, B0, B1, m, nn, S, ps);
                     sink = OpSink{ops_stage ? ops_stage + (size_t)my_p * ops_stride : nullptr, ops_stride, 0};
                     active = true;
                 }
@@ -226,8 +228,8 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
             continue;   // every pair handed out so far was rejected, or the pool just ran empty
         }
         if (active) {
-            if (pair_step<W>(P, S, ps, sink, st)) {
-                pair_finish<W>(P, S, ps, sink);
+            if (pair_step<W, CORR>(P, S, ps, sink, st)) {
+                pair_finish<W, CORR>(P, S, ps, sink);
                 cost[my_p] = ps.cost;
                 if (nops_out) nops_out[my_p] = (uint32_t)sink.n;
                 if (sink.n > ops_stride) st |= kStatusSteps;  // cannot happen: the stride covers the step limit

@@ -40,6 +40,13 @@ public:
         p.x = x; p.o = o; p.e = e; p.k = k;
         if (gasma_create(&p, device, &ctx) != GASMA_OK)
             throw std::runtime_error(std::string("benchmark_gpu: ") + gasma_last_error(nullptr));
+#ifdef CORRECTION   // the reference's compile-time band variant (hurdle_matrix.h:501-512, :634-641)
+#ifndef GASMA_CORRECTION_MAX_DELTA
+#define GASMA_CORRECTION_MAX_DELTA 16
+#endif
+        if (gasma_set_correction(ctx, 1, GASMA_CORRECTION_MAX_DELTA) != GASMA_OK)
+            throw std::runtime_error(std::string("benchmark_gpu: ") + gasma_last_error(ctx));
+#endif
     }
     benchmark_gpu(const benchmark_gpu&) = delete;
     benchmark_gpu& operator=(const benchmark_gpu&) = delete;

@@ -10,7 +10,10 @@
 //   * results are those of the reference in canonical mode (staging tail = 'A'), i.e. they do not
 //     depend on the pairs aligned before;
 //   * |ref_len - read_len| > MAX_K (out-of-bounds in the reference) and CUDA failures throw std::runtime_error;
-//   * MAX_LENGTH is a constructor argument (128 = int_128bit; 192 and 256 are the multi-word extension).
+//   * MAX_LENGTH is a constructor argument (128 = int_128bit; 192 and 256 are the multi-word extension);
+//   * the reference's compile-time band variant `#ifdef CORRECTION` (hurdle_matrix.h:501-512, :634-641) is honoured the
+//     same way: compile the caller with -DCORRECTION and the context runs with the widened band, keeping lane slots for
+//     |ref_len - read_len| <= GASMA_CORRECTION_MAX_DELTA (default 16; shared memory per alignment grows with it).
 #pragma once
 #include <algorithm>
 #include <cstring>
@@ -19,6 +22,10 @@
 #include <vector>
 
 #include "../../include/gasma_b200.h"
+
+#ifndef GASMA_CORRECTION_MAX_DELTA
+#define GASMA_CORRECTION_MAX_DELTA 16
+#endif
 
 #ifndef GASMA_ALIGNMENT_TYPE_T
 #define GASMA_ALIGNMENT_TYPE_T
@@ -42,6 +49,9 @@ public:
         k_ = p.k;
         if (gasma_create(&p, device, &ctx_) != GASMA_OK)
             throw std::runtime_error(std::string("hurdle_matrix_gpu: ") + gasma_last_error(nullptr));
+#ifdef CORRECTION
+        check(gasma_set_correction(ctx_, 1, GASMA_CORRECTION_MAX_DELTA));
+#endif
     }
     // hurdle_matrix(read, ref, error, alignment_type, x, o, e, 0.95, 0.02, 0.03), hurdle_matrix.h:473-484
     hurdle_matrix_gpu(const char* read, const char* ref, int error, alignment_type_t type = GLOBAL, int x = 1, int o = 1,

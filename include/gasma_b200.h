@@ -79,6 +79,13 @@ void gasma_destroy(gasma_ctx* ctx);
 const char* gasma_last_error(const gasma_ctx* ctx);
 /* Change the band between batches: the `error` argument of reset() (hurdle_matrix.h:625). */
 int gasma_set_band(gasma_ctx* ctx, int k);
+/* The reference's compile-time band variant `#ifdef CORRECTION` (hurdle_matrix.h:501-512, :634-641) as a run-time
+ * switch: with enabled != 0 the lanes of a pair are [-k, n-m+k] when m <= n and [n-m-k, k] otherwise (n-m =
+ * ref_len - read_len), so the destination lane is always inside the band.  max_delta is the largest |n-m| the
+ * context keeps lane slots for (2k+1+max_delta lanes per alignment in shared memory); a pair beyond it, or with
+ * |n-m| + k > GASMA_MAX_K (past the reference's lane arrays), fails the batch with GASMA_E_BAND.  Results are
+ * bit-exact to the unmodified reference compiled with -DCORRECTION.  enabled == 0 restores lanes -k..k. */
+int gasma_set_correction(gasma_ctx* ctx, int enabled, int max_delta);
 /* Use the caller's cudaStream_t (e.g. torch's current stream) for all work of this context.  The handle is
  * taken literally: NULL means the legacy default stream.  A fresh context uses a private non-blocking stream. */
 int gasma_set_stream(gasma_ctx* ctx, void* cuda_stream);

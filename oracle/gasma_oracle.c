@@ -124,6 +124,10 @@ int go_greedy(const char* read, int read_len, const char* ref, int ref_len, cons
     /* hurdle_matrix.h:626-627 silent truncation */
     const int m = read_len < BITS ? read_len : BITS, n = ref_len < BITS ? ref_len : BITS;
     if (abs(n - m) > GO_MAX_K) return -2;  /* out-of-bounds in the reference */
+    /* lane range, hurdle_matrix.h:634-644 (#ifdef CORRECTION widens the band towards lane n-m) */
+    int lb = -k, ub = k;
+    if (p->correction) { if (m <= n) ub = n - m + k; else lb = n - m - k; }
+    if (lb < -GO_MAX_K || ub > GO_MAX_K) return -2;  /* past the reference's lane arrays */
     /* hurdle_matrix.h:536-538 */
     const double ms = log(p->match_prob / 0.25), mms = log(p->mismatch_prob / 0.25),
                  ids = log(p->indel_prob / 2 / 0.25);
@@ -140,7 +144,7 @@ int go_greedy(const char* read, int read_len, const char* ref, int ref_len, cons
         nsw[2 * GO_MAX_K + 1], nh[2 * GO_MAX_K + 1], de[2 * GO_MAX_K + 1];
 #define IX(l) ((l) + GO_MAX_K)
     for (int l = -GO_MAX_K; l <= GO_MAX_K; ++l) {
-        if (l < -k || l > k) {
+        if (l < lb || l > ub) {
             bv_zero(&orig[IX(l)]); orig[IX(l)].w[0] = 1;
             flip[IX(l)] = orig[IX(l)];
         }
@@ -149,7 +153,7 @@ int go_greedy(const char* read, int read_len, const char* ref, int ref_len, cons
         sw[IX(l)] = hc[IX(l)] = nsw[IX(l)] = nh[IX(l)] = BITS;
     }
     /* _construct_hurdles, hurdle_matrix.h:441-455 ; highways::reset :106-119 */
-    for (int l = -k; l <= k; ++l) {
+    for (int l = lb; l <= ub; ++l) {
         bv_t s0, s1, v; bv_zero(&v);
         if (l < 0) {
             s0 = bv_down(&A0, -l, W); s1 = bv_down(&A1, -l, W);
@@ -170,7 +174,7 @@ int go_greedy(const char* read, int read_len, const char* ref, int ref_len, cons
     for (;;) {
         /* _update_highway_list loop 1, hurdle_matrix.h:291-322 */
         int reach = 0;
-        for (int l = -k; l <= k; ++l) {
+        for (int l = lb; l <= ub; ++l) {
             int sc = cc + sfc(cl, l);
             if (sp[IX(l)] < sc) {
                 nsw[IX(l)] = abs(l - cl);
@@ -194,7 +198,7 @@ int go_greedy(const char* read, int read_len, const char* ref, int ref_len, cons
         double bestH = -INFINITY;
         int bestLeap = 0; /* -numeric_limits<int>::infinity() == 0, hurdle_matrix.h:287 */
         int bl = 0;
-        for (int l = -k; l <= k; ++l) {
+        for (int l = lb; l <= ub; ++l) {
             int current_cost = -sw[IX(l)] - hc[IX(l)];
             double h = ms * len[IX(l)] + mms * nh[IX(l)] + ids * nsw[IX(l)];
             int lh = -sw[IX(l)];
@@ -209,7 +213,7 @@ int go_greedy(const char* read, int read_len, const char* ref, int ref_len, cons
         if (len[IX(bl)] <= 0) break; /* :358-360 -> _step returns true */
         /* _choose_best_highway, hurdle_matrix.h:368-401 */
         int spb = sp[IX(bl)], sT = hc[IX(bl)] + sw[IX(bl)], sI = sT, b = bl;
-        for (int l = -k; l <= k; ++l) {
+        for (int l = lb; l <= ub; ++l) {
             if (l == bl) continue;
             if (sp[IX(l)] + sfc(l, bl) > spb) continue;
             int end = sp[IX(l)] + len[IX(l)];

@@ -34,6 +34,8 @@ typedef struct {
     int global;          /* 1 = GLOBAL, 0 = SEMI_GLOBAL (utils.h:554) */
     int W;               /* words per bit-vector; MAX_LENGTH = 64*W */
     double match_prob, mismatch_prob, indel_prob; /* hurdle_matrix.h:557-559 */
+    int correction;      /* 1 = the reference built with -DCORRECTION (hurdle_matrix.h:501-512, :634-641):
+                          * lanes [-k, n-m+k] for m <= n, [n-m-k, k] otherwise; 0 = lanes -k..k */
 } go_params;
 
 /* bit_convert.cpp:248 semantics for one string, tail [len, 64W) = 'A' (00) */

@@ -45,12 +45,12 @@ bool stage(const uint8_t* buf, uint32_t base16, uint32_t end, uint32_t total, ui
     return ok;
 }
 
-template <int W>
+template <int W, bool CORR = false>
 int sim_greedy(const KParams& P, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, const uint32_t* foff,
                int64_t n, int T, int32_t* cost, uint16_t* ops_stage, int stride, uint32_t* nops, uint32_t* status_out,
                int64_t* steps_out) {
     constexpr int BITS = 64 * W;
-    const int nl = 2 * P.k + 1;
+    const int nl = CORR ? P.nl : 2 * P.k + 1;
     std::vector<uint32_t> lanes((size_t)nl * 2 * W);
     std::vector<uint64_t> state(nl);
     std::vector<uint16_t> r0(elems<W>(T)), r1(elems<W>(T)), f0(elems<W>(T)), f1(elems<W>(T));
@@ -69,6 +69,7 @@ int sim_greedy(const KParams& P, const uint8_t* reads, const uint32_t* roff, con
             if (!ok) st |= kStatusTile;
             if (m > BITS || nn > BITS) st |= kStatusLength;
             else if (iabs(nn - m) > kMaxK) st |= kStatusBand;
+            else if (CORR && (iabs(nn - m) + P.k > kMaxK || 2 * P.k + 1 + iabs(nn - m) > nl)) st |= kStatusBand;
             int c = INT32_MIN, steps = 0;
             uint32_t my = 0;
             if (!st) {
@@ -80,7 +81,7 @@ int sim_greedy(const KParams& P, const uint8_t* reads, const uint32_t* roff, con
                 extract_plane<W>(reinterpret_cast<const uint32_t*>(f1.data()), fbit, nn, B1);
                 LaneStore S{lanes.data(), state.data(), 1};
                 OpSink sink{ops_stage ? ops_stage + (size_t)(p0 + t) * stride : nullptr, stride, 0};
-                st = greedy_pair<W>(P, A0, A1, B0, B1, m, nn, S, sink, c, steps);
+                st = greedy_pair<W, CORR>(P, A0, A1, B0, B1, m, nn, S, sink, c, steps);
                 my = (uint32_t)sink.n;
             }
             cost[p0 + t] = c;
@@ -386,6 +387,20 @@ int sim_greedy_batch(int W, int T, int k, int x, int o, int e, int global, doubl
         case 2: return sim_greedy<2>(P, reads, roff, refs, foff, n, T, cost, ops_stage, stride, nops, status, steps);
         case 3: return sim_greedy<3>(P, reads, roff, refs, foff, n, T, cost, ops_stage, stride, nops, status, steps);
         case 4: return sim_greedy<4>(P, reads, roff, refs, foff, n, T, cost, ops_stage, stride, nops, status, steps);
+    }
+    return -1;
+}
+
+// the widened band of the reference's -DCORRECTION build (gasma_set_correction); nl = 2k+1+max_delta lane slots
+int sim_greedy_batch_corr(int W, int T, int k, int x, int o, int e, int global, double pm, double pmm, double pid, int max_delta,
+                          const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, const uint32_t* foff, int64_t n,
+                          int32_t* cost, uint16_t* ops_stage, int stride, uint32_t* nops, uint32_t* status, int64_t* steps) {
+    KParams P{k, x, o, e, global, std::log(pm / 0.25), std::log(pmm / 0.25), std::log(pid / 2 / 0.25), 1, 2 * k + 1 + max_delta};
+    switch (W) {
+        case 1: return sim_greedy<1, true>(P, reads, roff, refs, foff, n, T, cost, ops_stage, stride, nops, status, steps);
+        case 2: return sim_greedy<2, true>(P, reads, roff, refs, foff, n, T, cost, ops_stage, stride, nops, status, steps);
+        case 3: return sim_greedy<3, true>(P, reads, roff, refs, foff, n, T, cost, ops_stage, stride, nops, status, steps);
+        case 4: return sim_greedy<4, true>(P, reads, roff, refs, foff, n, T, cost, ops_stage, stride, nops, status, steps);
     }
     return -1;
 }

@@ -28,7 +28,8 @@ def build_oracle(quiet=True):
 class GoParams(C.Structure):
     _fields_ = [("k", C.c_int), ("x", C.c_int), ("o", C.c_int), ("e", C.c_int),
                 ("global_", C.c_int), ("W", C.c_int),
-                ("match_prob", C.c_double), ("mismatch_prob", C.c_double), ("indel_prob", C.c_double)]
+                ("match_prob", C.c_double), ("mismatch_prob", C.c_double), ("indel_prob", C.c_double),
+                ("correction", C.c_int)]
 
 
 class GoGenConfig(C.Structure):
@@ -43,6 +44,7 @@ def _ptr(a):
 
 _oracle = None
 _ref = None
+_ref_corr = None
 
 
 def oracle():
@@ -100,6 +102,23 @@ def ref():
     return _ref
 
 
+def ref_corr_available():
+    return os.path.exists(os.path.join(ORACLE_DIR, "_ref", "libgasma_ref_corr.so"))
+
+
+def ref_corr():
+    """The unmodified reference compiled with -DCORRECTION (hurdle_matrix.h:501-512, :634-641): a library of its
+    own, because the macro changes the one hurdle_matrix<int_128bit> instantiation."""
+    global _ref_corr
+    if _ref_corr is None:
+        L = C.CDLL(os.path.join(ORACLE_DIR, "_ref", "libgasma_ref_corr.so"))
+        L.gasma_ref_greedy_batch.restype = C.c_int
+        L.gasma_ref_greedy_batch.argtypes = ([C.c_void_p] * 4 + [C.c_int64] + [C.c_int] * 4 + [C.c_double] * 3 +
+                                             [C.c_int] * 2 + [C.c_void_p, C.c_void_p, C.c_int])
+        _ref_corr = L
+    return _ref_corr
+
+
 # ----------------------------------------------------------------------------------------------
 # batch containers: concatenated ASCII + CSR offsets (the layout the C ABI uses)
 # ----------------------------------------------------------------------------------------------
@@ -138,8 +157,8 @@ def batch_from_strings(reads, refs):
     return Batch.from_pairs([(r.encode(), f.encode()) for r, f in zip(reads, refs)])
 
 
-def make_params(k=3, x=1, o=1, e=1, W=2, global_=1, probs=DEFAULT_PROBS):
-    return GoParams(k, x, o, e, global_, W, probs[0], probs[1], probs[2])
+def make_params(k=3, x=1, o=1, e=1, W=2, global_=1, probs=DEFAULT_PROBS, correction=0):
+    return GoParams(k, x, o, e, global_, W, probs[0], probs[1], probs[2], correction)
 
 
 def gen_config(seed, length, error_rate, mismatch_rate=0.96, mode=0, profile=None):
@@ -265,8 +284,9 @@ def render_all(ops, op_off):
 # ----------------------------------------------------------------------------------------------
 # unmodified reference calls
 # ----------------------------------------------------------------------------------------------
-def ref_greedy(b, k=3, x=1, o=1, e=1, probs=DEFAULT_PROBS, mode=0, threads=1, want_text=True, stride=1280):
-    L = ref()
+def ref_greedy(b, k=3, x=1, o=1, e=1, probs=DEFAULT_PROBS, mode=0, threads=1, want_text=True, stride=1280,
+               correction=False):
+    L = ref_corr() if correction else ref()
     cost = np.zeros(b.n, np.int32)
     text = np.zeros(b.n * stride, np.uint8) if want_text else None
     need = L.gasma_ref_greedy_batch(_ptr(b.reads), _ptr(b.read_off), _ptr(b.refs), _ptr(b.ref_off), b.n,

@@ -8,8 +8,11 @@ def _p(a):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
 
 
-def sim_greedy(S, ol, b, p, T=128):
+def sim_greedy(S, ol, b, p, T=128, max_delta=None):
+    """max_delta != None: the widened band (KParams::correction) with 2k+1+max_delta lane slots."""
     S.sim_greedy_batch.argtypes = [C.c_int] * 7 + [C.c_double] * 3 + [C.c_void_p] * 4 + [
+        C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+    S.sim_greedy_batch_corr.argtypes = [C.c_int] * 7 + [C.c_double] * 3 + [C.c_int] + [C.c_void_p] * 4 + [
         C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
     stride = 2 * 64 * p.W + 8
     cost = np.zeros(b.n, np.int32)
@@ -17,9 +20,12 @@ def sim_greedy(S, ol, b, p, T=128):
     nops = np.zeros(b.n, np.uint32)
     st = np.zeros(1, np.uint32)
     steps = np.zeros(1, np.int64)
-    rc = S.sim_greedy_batch(p.W, T, p.k, p.x, p.o, p.e, p.global_, p.match_prob, p.mismatch_prob, p.indel_prob,
-                            _p(b.reads), _p(b.read_off), _p(b.refs), _p(b.ref_off), b.n, _p(cost), _p(stage), stride,
-                            _p(nops), _p(st), _p(steps))
+    head = (p.W, T, p.k, p.x, p.o, p.e, p.global_, p.match_prob, p.mismatch_prob, p.indel_prob)
+    tail = (_p(b.reads), _p(b.read_off), _p(b.refs), _p(b.ref_off), b.n, _p(cost), _p(stage), stride, _p(nops), _p(st), _p(steps))
+    if max_delta is None:
+        rc = S.sim_greedy_batch(*head, *tail)
+    else:
+        rc = S.sim_greedy_batch_corr(*head, max_delta, *tail)
     assert rc == 0
     text = [ol.render_ops(stage[i * stride:i * stride + nops[i]]) for i in range(b.n)]
     return cost, text, int(st[0]), int(steps[0])

@@ -245,3 +245,50 @@ def test_gpu_long_reads_warp_per_alignment(pkg, ol, W, k):
     with pytest.raises(pkg.GasmaError):   # the NW verifier stops at 256 characters
         al.nw_batch(b.reads, b.read_off, b.refs, b.ref_off)
     al.close()
+
+
+def test_gpu_widened_band_matches_golden(pkg, ol, golden):
+    """gasma_set_correction against the unmodified reference compiled with -DCORRECTION (golden fixture)."""
+    aligners = {}
+    for s in golden("greedy_ref_correction.json")["sets"]:
+        ps = s["params"]
+        key = (ps["k"], ps["x"], ps["o"], ps["e"], tuple(ps["probs"]))
+        if key not in aligners:
+            aligners[key] = pkg.Aligner(k=ps["k"], x=ps["x"], o=ps["o"], e=ps["e"], match_prob=ps["probs"][0],
+                                        mismatch_prob=ps["probs"][1], indel_prob=ps["probs"][2])
+            aligners[key].set_correction(True, ps["max_delta"])
+        b = _batch(ol, s["pairs"])
+        out, text = _run(pkg, aligners[key], b)
+        assert out["cost"].tolist() == s["cost"], s["name"]
+        assert text == s["cigar"], s["name"]
+
+
+@pytest.mark.parametrize("W", [2, 3, 8, 16])
+def test_gpu_widened_band_matches_oracle(pkg, ol, W):
+    """Thread kernel (W <= 4) and warp kernel (W = 8, 16) with the widened band, against the oracle in that mode;
+    switching it off again restores lanes -k..k; pairs beyond the lane slots fail the batch."""
+    rng = np.random.default_rng(700 + W)
+    n = 4000 if W <= 4 else 600
+    for (k, x, o, e, g, md) in [(3, 1, 1, 1, 1, 12), (7, 2, 3, 1, 1, 20), (3, 1, 1, 1, 0, 9)]:
+        b = ol.random_batch(rng, n, 1, 64 * W, 0.2 if W <= 4 else 0.1, 0.35, md)
+        al = pkg.Aligner(k=k, x=x, o=o, e=e, max_length=64 * W, alignment_type=1 - g)
+        al.set_correction(True, md)
+        out, _ = _run(pkg, al, b)
+        r = ol.oracle_greedy(b, ol.make_params(k, x, o, e, W, g, correction=1), threads=8)
+        assert out["cost"].tolist() == r["cost"].tolist()
+        assert out["op_off"].tolist() == r["op_off"].tolist()
+        assert out["ops"][:out["n_ops"]].tolist() == r["ops"].tolist()
+        al.set_correction(False)
+        out, _ = _run(pkg, al, b)
+        r = ol.oracle_greedy(b, ol.make_params(k, x, o, e, W, g), threads=8)
+        assert out["cost"].tolist() == r["cost"].tolist()
+        assert out["ops"][:out["n_ops"]].tolist() == r["ops"].tolist()
+        al.close()
+    al = pkg.Aligner(max_length=64 * W)
+    al.set_correction(True, 4)
+    b = _batch(ol, [("ACGT" * 5, "ACGT" * 7), ("ACGT", "ACGT")])
+    with pytest.raises(pkg.GasmaError) as ei:
+        al.greedy_batch(b.reads, b.read_off, b.refs, b.ref_off)
+    assert ei.value.code == -3   # GASMA_E_BAND
+    with pytest.raises(pkg.GasmaError):
+        al.set_correction(True, 48)    # max_delta + k > MAX_K

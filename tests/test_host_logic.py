@@ -66,3 +66,33 @@ def test_length_and_band_violations_are_flagged(ol, host_sim):
     b = _batch(ol, [("A" * 10, "A" * 61)])
     _, _, st, _ = sim_lib.sim_greedy(host_sim, ol, b, ol.make_params())
     assert st & 2
+
+
+@pytest.mark.parametrize("W", [2, 3])
+def test_widened_band_logic_matches_oracle(ol, host_sim, W):
+    """KParams::correction (the reference's -DCORRECTION band, hurdle_matrix.h:634-641) vs the oracle in that mode."""
+    rng = np.random.default_rng(300 + W)
+    for (k, x, o, e, g, md) in [(3, 1, 1, 1, 1, 12), (5, 2, 3, 1, 1, 20), (3, 1, 1, 1, 0, 9), (0, 1, 1, 1, 1, 6)]:
+        b = ol.random_batch(rng, 1500, 1, 64 * W, 0.3, 0.35, md)
+        p = ol.make_params(k, x, o, e, W, g, correction=1)
+        r = ol.oracle_greedy(b, p, threads=4, want_text=True)
+        cost, text, st, steps = sim_lib.sim_greedy(host_sim, ol, b, p, max_delta=md)
+        assert st == 0
+        assert cost.tolist() == r["cost"].tolist()
+        assert text == r["text"]
+        assert steps == r["steps"]
+    # a pair beyond the lane slots is flagged, not silently narrowed
+    b = _batch(ol, [("A" * 10, "A" * 20), ("ACGT", "ACGT")])
+    cost, _, st, _ = sim_lib.sim_greedy(host_sim, ol, b, ol.make_params(correction=1), max_delta=8)
+    assert st & 2 and cost[0] == -2**31 and cost[1] == 0
+
+
+def test_widened_band_logic_matches_golden(ol, host_sim, golden):
+    for s in golden("greedy_ref_correction.json")["sets"]:
+        ps = s["params"]
+        p = ol.make_params(ps["k"], ps["x"], ps["o"], ps["e"], 2, 1, tuple(ps["probs"]), correction=1)
+        b = _batch(ol, s["pairs"])
+        cost, text, st, _ = sim_lib.sim_greedy(host_sim, ol, b, p, max_delta=ps["max_delta"])
+        assert st == 0
+        assert cost.tolist() == s["cost"], s["name"]
+        assert text == s["cigar"], s["name"]

@@ -158,3 +158,34 @@ def test_oracle_leap_vs_reference_fresh(ol):
             r0, _ = ol.ref_leap(b, k, x, o, e, mode=0, threads=1)
             r1, _ = ol.ref_leap(b, k, x, o, e, mode=1, threads=4)
             assert a.tolist() == r0.tolist() == r1.tolist()
+
+
+def test_oracle_correction_matches_golden(ol, golden):
+    """The widened band of the reference's -DCORRECTION build (hurdle_matrix.h:501-512, :634-641) against the golden
+    results of the unmodified reference compiled with that macro (tests/golden/make_golden_correction.py)."""
+    total = 0
+    for s in golden("greedy_ref_correction.json")["sets"]:
+        ps = s["params"]
+        p = ol.make_params(ps["k"], ps["x"], ps["o"], ps["e"], 2, 1, tuple(ps["probs"]), correction=1)
+        b = _batch(ol, s["pairs"])
+        r = ol.oracle_greedy(b, p, threads=4, want_text=True)
+        assert r["cost"].tolist() == s["cost"], s["name"]
+        assert r["text"] == s["cigar"], s["name"]
+        total += b.n
+    assert total > 4500
+
+
+def test_oracle_correction_vs_reference_fresh(ol):
+    if not ol.ref_corr_available():
+        pytest.skip("oracle/_ref/libgasma_ref_corr.so not built (needs /root/reference)")
+    rng = np.random.default_rng(4444)
+    differs = 0
+    for (k, x, o, e, md) in [(3, 1, 1, 1, 12), (6, 2, 3, 1, 30), (0, 1, 1, 1, 5)]:
+        b = ol.random_batch(rng, 4000, 1, 128, 0.3, 0.35, md)
+        r = ol.oracle_greedy(b, ol.make_params(k, x, o, e, correction=1), threads=4, want_text=True)
+        f = ol.ref_greedy(b, k, x, o, e, threads=4, correction=True)
+        assert r["cost"].tolist() == f["cost"].tolist()
+        assert r["text"] == f["text"]
+        plain = ol.ref_greedy(b, k, x, o, e, threads=4)
+        differs += sum(a != c for a, c in zip(plain["text"], f["text"]))
+    assert differs > 100   # the macro really changes results (pairs with n != m)
