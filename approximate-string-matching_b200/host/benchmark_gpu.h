@@ -21,6 +21,7 @@
 #include <fstream>
 #include <stdexcept>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/gasma_b200.h"
@@ -31,26 +32,38 @@ public:
     // striped kernel over its scalar one (:239-243); both give the same results, so it is accepted and ignored.
     benchmark_gpu(int _x, int _o, int _e, int _k, int max_test_num, bool _use_SIMD = true, int device = 0,
                   int64_t batch_pairs = 1000000)
+        : benchmark_gpu(_x, _o, _e, _k, max_test_num, _use_SIMD, std::vector<int>{device}, batch_pairs) {}
+    // Several GPUs of one box: the batches of run() are dealt round-robin to one context per device (pairs are
+    // independent; the only cross-GPU quantity is the sum of the counters, benchmark_utils.h:238,253-258).
+    benchmark_gpu(int _x, int _o, int _e, int _k, int max_test_num, bool _use_SIMD, const std::vector<int>& devices,
+                  int64_t batch_pairs = 1000000)
         : x(_x), o(_o), e(_e), k(_k), max_tests(max_test_num), use_SIMD(_use_SIMD), batch(batch_pairs) {
+        if (devices.empty()) throw std::runtime_error("benchmark_gpu: no device given");
         read.resize((size_t)max_tests);
         ref.resize((size_t)max_tests);
         answers.assign((size_t)max_tests, INT32_MIN);
         gasma_params p;
         gasma_default_params(&p);
         p.x = x; p.o = o; p.e = e; p.k = k;
-        if (gasma_create(&p, device, &ctx) != GASMA_OK)
-            throw std::runtime_error(std::string("benchmark_gpu: ") + gasma_last_error(nullptr));
+        for (int device : devices) {
+            gasma_ctx* c = nullptr;
+            if (gasma_create(&p, device, &c) != GASMA_OK) {
+                for (gasma_ctx* made : ctxs) gasma_destroy(made);
+                throw std::runtime_error(std::string("benchmark_gpu: ") + gasma_last_error(nullptr));
+            }
+            ctxs.push_back(c);
 #ifdef CORRECTION   // the reference's compile-time band variant (hurdle_matrix.h:501-512, :634-641)
 #ifndef GASMA_CORRECTION_MAX_DELTA
 #define GASMA_CORRECTION_MAX_DELTA 16
 #endif
-        if (gasma_set_correction(ctx, 1, GASMA_CORRECTION_MAX_DELTA) != GASMA_OK)
-            throw std::runtime_error(std::string("benchmark_gpu: ") + gasma_last_error(ctx));
+            if (gasma_set_correction(c, 1, GASMA_CORRECTION_MAX_DELTA) != GASMA_OK)
+                throw std::runtime_error(std::string("benchmark_gpu: ") + gasma_last_error(c));
 #endif
+        }
     }
     benchmark_gpu(const benchmark_gpu&) = delete;
     benchmark_gpu& operator=(const benchmark_gpu&) = delete;
-    ~benchmark_gpu() { gasma_destroy(ctx); }
+    ~benchmark_gpu() { for (gasma_ctx* c : ctxs) gasma_destroy(c); }
 
     // '>' read '\n' '<' ref '\n' per pair; the first character of every line is skipped (:325-352)
     void read_string_file(const char* string_dir, bool skip_first_char = true) {
@@ -92,47 +105,31 @@ public:
         answers.assign(read.size(), INT32_MIN);
     }
 
-    // :373-385, batched
+    // :373-385, batched.  One host thread per device works through its share of the batches.
     void run() {
-        std::string rbuf, fbuf;
-        std::vector<uint32_t> roff, foff;
-        for (int64_t first = 0; first < max_tests; first += batch) {
-            const int64_t n = std::min<int64_t>(batch, max_tests - first);
-            rbuf.clear(); fbuf.clear();
-            roff.assign(1, 0u); foff.assign(1, 0u);
-            for (int64_t i = first; i < first + n; ++i) {
-                // hurdle_matrix::reset truncates to MAX_LENGTH (hurdle_matrix.h:626-627)
-                rbuf.append(read[(size_t)i], 0, (size_t)kMaxLength);
-                fbuf.append(ref[(size_t)i], 0, (size_t)kMaxLength);
-                roff.push_back((uint32_t)rbuf.size());
-                foff.push_back((uint32_t)fbuf.size());
+        const int64_t n_batches = (max_tests + batch - 1) / batch;
+        const size_t G = ctxs.size();
+        std::vector<tally> part(G);
+        std::vector<std::string> errors(G);
+        auto worker = [&](size_t g) {
+            try {
+                for (int64_t b = (int64_t)g; b < n_batches; b += (int64_t)G) run_batch(ctxs[g], b * batch, part[g]);
+            } catch (const std::exception& ex) {
+                errors[g] = ex.what();
             }
-            uint64_t c[4] = {0, 0, 0, 0};
-            double ms[2] = {0.0, 0.0};
-            nw_pen.resize((size_t)n);
-            leap_pen.resize((size_t)n);
-            int rc = gasma_benchmark_batch(ctx, rbuf.data(), roff.data(), fbuf.data(), foff.data(), n,
-                                           answers.data() + first, c, nullptr, nw_pen.data(), ms);
-            if (rc != GASMA_OK) throw std::runtime_error(std::string("benchmark_gpu::run: ") + gasma_last_error(ctx));
-            total_tests += c[0]; nw_correct += c[1]; greedy_correct += c[2]; greedy_coverage += c[3];
-            greedy_ms += ms[0]; nw_ms += ms[1];
-            // the LEAP column (_run_LEAP, :156-178; LEAP_correct, :254).  LEAP sees the same strings as the aligner,
-            // i.e. cut at MAX_LENGTH; the reference hands it the uncut ones (identical for the benchmark's 100 bp data)
-            rc = gasma_leap_batch(ctx, rbuf.data(), roff.data(), fbuf.data(), foff.data(), n, leap_pen.data());
-            if (rc == GASMA_OK) {
-                for (int64_t i = 0; i < n; ++i) {
-                    const int correct = answers[(size_t)(first + i)] == INT32_MIN ? nw_pen[(size_t)i] : answers[(size_t)(first + i)];
-                    LEAP_correct += leap_pen[(size_t)i] == correct;
-                }
-                int64_t launches = 0;
-                const double lms = gasma_kernel_time_ms(ctx, 2, &launches);
-                if (lms > 0) LEAP_ms += lms;
-            } else if (rc == GASMA_E_UNSUPPORTED) {
-                have_LEAP = false;   // penalties outside the comparator's domain (needs e <= o): the column reads n/a
-            } else {
-                throw std::runtime_error(std::string("benchmark_gpu::run (LEAP): ") + gasma_last_error(ctx));
-            }
-            if (first + n < max_tests) printf("...processed %lld reads.\n", (long long)(first + n));
+        };
+        if (G == 1) {
+            worker(0);
+        } else {
+            std::vector<std::thread> pool;
+            for (size_t g = 0; g < G; ++g) pool.emplace_back(worker, g);
+            for (std::thread& t : pool) t.join();
+        }
+        for (const std::string& err : errors) if (!err.empty()) throw std::runtime_error(err);
+        for (const tally& t : part) {   // the sum over GPUs: 5 integers per device
+            total_tests += t.total; nw_correct += t.nw; greedy_correct += t.greedy; greedy_coverage += t.coverage;
+            LEAP_correct += t.leap; greedy_ms += t.greedy_ms; nw_ms += t.nw_ms; LEAP_ms += t.leap_ms;
+            have_LEAP = have_LEAP && t.have_leap;
         }
         printf("...complete.\n");
     }
@@ -161,12 +158,56 @@ public:
     bool have_LEAP = true;
 
 private:
+    struct tally {
+        uint64_t total = 0, nw = 0, greedy = 0, coverage = 0, leap = 0;
+        double greedy_ms = 0.0, nw_ms = 0.0, leap_ms = 0.0;
+        bool have_leap = true;
+    };
+
+    // one batch of <= `batch` pairs on one context: greedy + NW verifier + counters, then the LEAP column
+    void run_batch(gasma_ctx* ctx, int64_t first, tally& t) {
+        const int64_t n = std::min<int64_t>(batch, max_tests - first);
+        std::string rbuf, fbuf;
+        std::vector<uint32_t> roff(1, 0u), foff(1, 0u);
+        for (int64_t i = first; i < first + n; ++i) {
+            // hurdle_matrix::reset truncates to MAX_LENGTH (hurdle_matrix.h:626-627)
+            rbuf.append(read[(size_t)i], 0, (size_t)kMaxLength);
+            fbuf.append(ref[(size_t)i], 0, (size_t)kMaxLength);
+            roff.push_back((uint32_t)rbuf.size());
+            foff.push_back((uint32_t)fbuf.size());
+        }
+        uint64_t c[4] = {0, 0, 0, 0};
+        double ms[2] = {0.0, 0.0};
+        std::vector<int32_t> nw_pen((size_t)n), leap_pen((size_t)n);
+        int rc = gasma_benchmark_batch(ctx, rbuf.data(), roff.data(), fbuf.data(), foff.data(), n, answers.data() + first, c,
+                                       nullptr, nw_pen.data(), ms);
+        if (rc != GASMA_OK) throw std::runtime_error(std::string("benchmark_gpu::run: ") + gasma_last_error(ctx));
+        t.total += c[0]; t.nw += c[1]; t.greedy += c[2]; t.coverage += c[3];
+        t.greedy_ms += ms[0]; t.nw_ms += ms[1];
+        // the LEAP column (_run_LEAP, :156-178; LEAP_correct, :254).  LEAP sees the same strings as the aligner,
+        // i.e. cut at MAX_LENGTH; the reference hands it the uncut ones (identical for the benchmark's 100 bp data)
+        rc = gasma_leap_batch(ctx, rbuf.data(), roff.data(), fbuf.data(), foff.data(), n, leap_pen.data());
+        if (rc == GASMA_OK) {
+            for (int64_t i = 0; i < n; ++i) {
+                const int correct = answers[(size_t)(first + i)] == INT32_MIN ? nw_pen[(size_t)i] : answers[(size_t)(first + i)];
+                t.leap += leap_pen[(size_t)i] == correct;
+            }
+            int64_t launches = 0;
+            const double lms = gasma_kernel_time_ms(ctx, 2, &launches);
+            if (lms > 0) t.leap_ms += lms;
+        } else if (rc == GASMA_E_UNSUPPORTED) {
+            t.have_leap = false;   // penalties outside the comparator's domain (needs e <= o): the column reads n/a
+        } else {
+            throw std::runtime_error(std::string("benchmark_gpu::run (LEAP): ") + gasma_last_error(ctx));
+        }
+        if (ctxs.size() == 1 && first + n < max_tests) printf("...processed %lld reads.\n", (long long)(first + n));
+    }
+
     static constexpr int kMaxLength = 128;   // MAX_LENGTH, GASMA/utils.h:23-25
     int x, o, e, k, max_tests;
     bool use_SIMD;
     int64_t batch;
     std::vector<std::string> read, ref;
     std::vector<int> answers;
-    std::vector<int32_t> nw_pen, leap_pen;
-    gasma_ctx* ctx = nullptr;
+    std::vector<gasma_ctx*> ctxs;   // one per device
 };

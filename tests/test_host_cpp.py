@@ -89,3 +89,104 @@ def test_benchmark_driver_report_matches_oracle(drivers, ol, tmp_path):
     lacc = re.search(r"\[Accuracy\].*?=> LEAP             \| ([\d.]+) %", txt, re.S)
     assert lacc.group(1) == "%.3f" % (int((leap == on["penalty"]).sum()) / total * 100)
     assert re.search(r"\[Time\].*?=> LEAP             \| \d+\.\d{3} s", txt, re.S)
+
+
+@pytest.mark.gpu
+def test_benchmark_driver_sharded_over_devices(drivers, tmp_path):
+    """Batches dealt to several contexts (one host thread per device entry) give the single-context report: the only
+    cross-device quantity is the counter sum.  Uses two real GPUs when the box has them, else device 0 twice."""
+    import torch
+    exe = os.path.join(drivers, "gasma-benchmark")
+    subprocess.run([exe, "--dataset-only", "--pairs", "20000", "--length", "100"], cwd=tmp_path, check=True, capture_output=True)
+    name = "simulated_20000_100_0.150000_eq.seq"
+
+    def report(*extra):
+        txt = subprocess.run([exe, name, "--pairs", "20000", *extra], cwd=tmp_path, capture_output=True, text=True, check=True).stdout
+        return txt[txt.index("Total number of alignments"):txt.index("[Time]")] + txt[txt.index("[Accuracy]"):]
+
+    one = report()
+    assert report("--batch", "3000", "--devices", "0,0,0") == one
+    if torch.cuda.device_count() >= 2:
+        assert report("--batch", "3000", "--gpus", "2") == one
+
+
+def _mapper_inputs(tmp_path, n_reads=400, seed=11):
+    """A two-contig reference, reads of 100 bp sampled from it with <= 3 edits, as FASTA / FASTQ files."""
+    rng = np.random.default_rng(seed)
+    contigs = ["".join(rng.choice(list("ACGT"), n)) for n in (60000, 25000)]
+    with open(tmp_path / "ref.fa", "w") as f:
+        for i, c in enumerate(contigs):
+            f.write(">chr%d some description\n" % (i + 1))
+            for j in range(0, len(c), 70):
+                f.write(c[j:j + 70] + "\n")
+    truth = []
+    with open(tmp_path / "reads.fq", "w") as f:
+        for r in range(n_reads):
+            cid = int(rng.integers(0, 2))
+            pos = int(rng.integers(1, len(contigs[cid]) - 110))
+            seq = list(contigs[cid][pos:pos + 100])
+            for _ in range(int(rng.integers(0, 4))):
+                kind = rng.random()
+                j = int(rng.integers(0, len(seq)))
+                if kind < 0.7:
+                    seq[j] = "ACGT"[int(rng.integers(0, 4))]
+                elif kind < 0.85:
+                    del seq[j]
+                else:
+                    seq.insert(j, "ACGT"[int(rng.integers(0, 4))])
+            seq = "".join(seq)
+            f.write("@read%d extra\n%s\n+\n%s\n" % (r, seq, "I" * len(seq)))
+            truth.append((cid, pos, seq))
+    return contigs, truth
+
+
+def test_mapper_search_stage(drivers, tmp_path):
+    """gasma-mapper --hits-only (FASTA/FASTQ parsing + seed index; no GPU involved) finds the sampled placements."""
+    contigs, truth = _mapper_inputs(tmp_path)
+    out = subprocess.run([os.path.join(drivers, "gasma-mapper"), "-r", "ref.fa", "-q", "reads.fq", "-e", "3", "--hits-only"],
+                         cwd=tmp_path, check=True, capture_output=True, text=True).stdout.strip().split("\n")
+    assert len(out) == len(truth)
+    good = 0
+    for line, (cid, pos, _) in zip(out, truth):
+        name, rid, begin = line.split()
+        if rid != "-" and int(rid) == cid and abs(int(begin) - pos) <= 3:
+            good += 1
+    assert good >= 0.98 * len(truth)
+    r = subprocess.run([os.path.join(drivers, "gasma-mapper"), "-r", "ref.fa"], cwd=tmp_path, capture_output=True, text=True)
+    assert r.returncode == 255 and "PARSER ERROR" in r.stderr
+
+
+@pytest.mark.gpu
+def test_mapper_sam_matches_oracle(drivers, ol, tmp_path):
+    """gasma-mapper end to end: every SAM record's MAPQ is 60 + the greedy cost of (read, window) as the reference's
+    mapper computes it (mapper/main.cpp:75-91), checked against the oracle; the CIGAR is the oracle's, SAM-merged;
+    two chunks give the same file as one."""
+    contigs, truth = _mapper_inputs(tmp_path, n_reads=600, seed=12)
+    exe = os.path.join(drivers, "gasma-mapper")
+    subprocess.run([exe, "-r", "ref.fa", "-q", "reads.fq", "-e", "3", "-o", "a.sam"], cwd=tmp_path, check=True)
+    subprocess.run([exe, "-r", "ref.fa", "-q", "reads.fq", "-e", "3", "-o", "b.sam", "--chunk", "250"], cwd=tmp_path, check=True)
+    a = open(tmp_path / "a.sam").read()
+    assert a == open(tmp_path / "b.sam").read()
+    lines = a.split("\n")
+    assert lines[0].startswith("@HD") and lines[1] == "@SQ\tSN:chr1\tLN:60000" and lines[2] == "@SQ\tSN:chr2\tLN:25000"
+    recs = [l.split("\t") for l in lines if l and not l.startswith("@")]
+    assert len(recs) >= 0.98 * len(truth)
+    pairs = []
+    for rec in recs:
+        cid = int(rec[2][3:]) - 1
+        start = int(rec[3]) - 3                      # POS = start + 2, written 1-based
+        pairs.append((rec[9], contigs[cid][start:start + len(rec[9]) + 1]))
+    b = ol.batch_from_strings([p[0] for p in pairs], [p[1] for p in pairs])
+    r = ol.oracle_greedy(b, ol.make_params(3, 1, 1, 1), threads=4)
+    for i, rec in enumerate(recs):
+        assert int(rec[4]) == 60 + int(r["cost"][i])
+        merged, run = [], None
+        for op in r["ops"][r["op_off"][i]:r["op_off"][i + 1]]:
+            code, ln = int(op) & 7, int(op) >> 3
+            if run and run[0] == code:
+                run[1] += ln
+            else:
+                run = [code, ln]
+                merged.append(run)
+        assert rec[5] == ("".join("%d%s" % (ln, "MID=X"[c]) for c, ln in merged) or "*")
+        assert rec[0].startswith("read") and rec[10] == "I" * len(rec[9])
