@@ -51,3 +51,50 @@ def max_over_ranks(value, device=None, group=None):
     t = torch.tensor([float(value)], dtype=torch.float64, device=device)
     dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
     return float(t.item())
+
+
+def _parse_cpulist(text):
+    cpus = set()
+    for part in text.strip().split(","):
+        if not part:
+            continue
+        lo, _, hi = part.partition("-")
+        cpus.update(range(int(lo), int(hi or lo) + 1))
+    return cpus
+
+
+def device_numa_node(device_index, sysfs="/sys"):
+    """NUMA node the GPU's PCIe root hangs off (None when the platform does not say)."""
+    try:
+        import torch
+        p = torch.cuda.get_device_properties(device_index)
+        bus = "%04x:%02x:%02x.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
+        with open(os.path.join(sysfs, "bus/pci/devices", bus, "numa_node")) as f:
+            node = int(f.read().strip())
+        return node if node >= 0 else None
+    except Exception:
+        return None
+
+
+def bind_host_to_device(device_index, sysfs="/sys"):
+    """Pin the calling process to the CPUs of the GPU's NUMA node, so that the pinned host buffers it allocates next
+    (first-touch placement) and the thread that feeds the host-pointer C-ABI calls sit next to that GPU's PCIe root.
+    With one process per GPU and every process streaming ~300 MB per batch, buffers on the wrong socket make all the
+    links share one socket's memory controllers and the inter-socket fabric.  Returns (node, n_cpus) or None when the
+    topology is unknown or single-node (nothing is changed then)."""
+    node = device_numa_node(device_index, sysfs)
+    if node is None:
+        return None
+    try:
+        nodes = [d for d in os.listdir(os.path.join(sysfs, "devices/system/node")) if d.startswith("node") and d[4:].isdigit()]
+        if len(nodes) < 2:
+            return None
+        with open(os.path.join(sysfs, "devices/system/node/node%d/cpulist" % node)) as f:
+            cpus = _parse_cpulist(f.read())
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return node, len(cpus)
+    except Exception:
+        return None

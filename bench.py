@@ -263,6 +263,9 @@ def run_b200(a):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     pkg = load_pkg()
+    # host side of the e2e leg: this process and the pinned buffers it allocates go next to its GPU's PCIe root
+    from gasma_b200 import shard
+    numa = None if os.environ.get("GASMA_NO_NUMA_BIND") else shard.bind_host_to_device(local)
     ml = max_length_for(a.length, a.error if a.profile == "simulated" else 0.0)
     al = pkg.Aligner(k=a.k, max_length=ml, device=local)
     stream = torch.cuda.current_stream()
@@ -390,6 +393,7 @@ def run_b200(a):
         "e2e": {"value": world * n * e2e_steps / e2e_s, "unit": "alignments/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "steps": e2e_steps,
                 "h2d_gb_per_s": h2d * e2e_steps / e2e_s / 1e9,
+                "host_numa": ({"node": numa[0], "cpus": numa[1]} if numa else None),
                 "note": "host-pointer C-ABI call, pinned buffers, 8 pipelined slices; bound by the host-to-device link (ASCII in; PCIe 5 x16 measured at 55 GB/s by tools/link_probe.py)"},
         "gpu_launches": int(launches),
         "clocks": clocks,

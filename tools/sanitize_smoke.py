@@ -34,6 +34,18 @@ for ml, k, n in ((128, 3, 3000), (192, 9, 1500), (256, 50, 300), (1024, 24, 200)
     al.generate(cfg, 0, 500)
     al.close()
     print("ok", ml, k, flush=True)
+# the widened band (gasma_set_correction): thread kernel and warp kernel
+for ml, k, md, n in ((128, 3, 12, 2000), (192, 7, 20, 800), (512, 9, 16, 100)):
+    W = ml // 64
+    al = pkg.Aligner(k=k, max_length=ml)
+    al.set_correction(True, md)
+    b = ol.random_batch(rng, n, 0, ml, 0.2, 0.35, md)
+    out = al.greedy_batch(b.reads, b.read_off, b.refs, b.ref_off)
+    r = ol.oracle_greedy(b, ol.make_params(k, 1, 1, 1, W, correction=1), threads=8)
+    assert out["cost"].tolist() == r["cost"].tolist()
+    assert out["ops"][:out["n_ops"]].tolist() == r["ops"].tolist()
+    al.close()
+    print("ok widened band", ml, k, md, flush=True)
 # the pipelined host call
 al = pkg.Aligner()
 b = ol.random_batch(rng, 66000, 0, 128, 0.2, 0.3, 50)
