@@ -381,6 +381,17 @@ def run_b200(a):
         prof = {}
     k_ms = kernel_ms / max(kernel_launches, 1)
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9
+    # the resource that actually binds this integer kernel: warp-instruction issue.  Instructions per launch come from
+    # the ncu capture of this command (deterministic for a given batch), the duration is the live CUDA-event time,
+    # the peak is 4 schedulers x 1 warp-instruction per clock on every SM at the clock sampled under load.
+    issue = None
+    if prof.get("warp_instructions") and clocks and clocks.get("sm_mhz"):
+        sms = torch.cuda.get_device_properties(local).multi_processor_count
+        issue_peak = sms * 4 * clocks["sm_mhz"] * 1e6
+        issue_ach = prof["warp_instructions"] / (k_ms * 1e-3)
+        issue = {"bound": "issue slots (4 schedulers/SM)", "achieved": issue_ach / 1e9, "peak": issue_peak / 1e9,
+                 "unit": "G warp-instr/s", "frac": issue_ach / issue_peak,
+                 "warp_instructions_per_launch": prof["warp_instructions"], "source": prof.get("source")}
     line = {
         "metric": "alignments/sec (greedy + banded NW) at 1/2/4/8 B200 vs AVX2 host cores",
         "value": world * n * a.steps / (ms_total * 1e-3),
@@ -403,7 +414,7 @@ def run_b200(a):
                      "note": "integer bit-vector work: the kernel is bound by instruction issue, not by HBM (see ncu block); "
                              "frac is reported against the HBM roofline as the contract asks", "kernel": ("greedy_kernel<W=%d,WARPS=4>" if ml <= 256 else "greedy_warp_kernel<W=%d,WARPS=4>") % (ml // 64), "kernel_ms": k_ms,
                      "kernel_share_of_step": k_ms / (ms_total / a.steps), "algorithmic_bytes_per_launch": alg_bytes,
-                     "peak_source": peak_src},
+                     "peak_source": peak_src, "issue": issue},
         "counters": {"pairs": int(counters[0]), "penalty_sum": int(counters[1]), "cigar_ops": int(counters[2])},
     }
     if full is not None:
