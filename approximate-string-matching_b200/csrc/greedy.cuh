@@ -170,47 +170,8 @@ GASMA_HD int pcb(const uint32_t* base, int stride, int from, int to) {
     return c;
 }
 
-// v >> s (towards bit 0), zero fill, for a small shift 0 <= s < 64   (shift_left, utils.h:143)
-template <int W>
-GASMA_HD void shift_down_small(const uint64_t v[W], int s, uint64_t out[W]) {
-#pragma unroll
-    for (int j = 0; j < W; ++j) {
-        uint64_t hi = (j + 1 < W) ? v[j + 1] : 0ull;
-        out[j] = s ? (shr64(v[j], s) | shl64(hi, 64 - s)) : v[j];
-    }
-}
-
-// One lane of _construct_hurdles (hurdle_matrix.h:441-455): the original (unflipped) hurdle mask
-template <int W>
-GASMA_HD void build_lane(const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W], const uint64_t B1[W],
-                         int lane, uint64_t orig[W]) {
-    uint64_t s0[W], s1[W];
-    const int a = iabs(lane);
-    if (lane < 0) {
-        shift_down_small<W>(A0, a, s0);
-        shift_down_small<W>(A1, a, s1);
-#pragma unroll
-        for (int j = 0; j < W; ++j) orig[j] = (s0[j] ^ B0[j]) | (s1[j] ^ B1[j]);
-    } else {
-        shift_down_small<W>(B0, a, s0);
-        shift_down_small<W>(B1, a, s1);
-#pragma unroll
-        for (int j = 0; j < W; ++j) orig[j] = (s0[j] ^ A0[j]) | (s1[j] ^ A1[j]);
-    }
-}
-
 template <int W>
 GASMA_HD const uint32_t* lane_base(const LaneStore& S, int li) { return S.lanes + (size_t)(li * 2 * W) * S.stride; }
-
-template <int W>
-GASMA_HD void lane_store(const LaneStore& S, int li, const uint64_t v[W]) {
-    uint32_t* b = S.lanes + (size_t)(li * 2 * W) * S.stride;
-#pragma unroll
-    for (int j = 0; j < W; ++j) {
-        b[(2 * j) * S.stride] = (uint32_t)v[j];
-        b[(2 * j + 1) * S.stride] = (uint32_t)(v[j] >> 32);
-    }
-}
 
 struct OpSink {
     uint16_t* ops;   // this pair's staging row (may be null: costs only)
@@ -246,21 +207,82 @@ GASMA_HD void lane_range(int k, int m, int n, int& lb, int& ub) {
     if (CORR) { if (m <= n) ub = n - m + k; else lb = n - m - k; }
 }
 
-// reset(): highways::reset (:106-119) + _construct_hurdles (:441-455)
+// 32-bit plane words of a string: word j = bits [32j, 32j+32) of the stream window that starts at bit `bit`, bits >= len
+// cleared (the canonical 'A' tail), plus one zero word on top.  The stream must be readable for 2W+1 words from bit>>5.
+template <int W>
+GASMA_HD void extract_plane32(const uint32_t* stream32, int bit, int len, uint32_t out[2 * W + 1]) {
+    constexpr int NW = 2 * W;
+    const int idx = bit >> 5, sh = bit & 31;
+    uint32_t prev = stream32[idx];
+#pragma unroll
+    for (int j = 0; j < NW; ++j) {
+        const uint32_t nxt = stream32[idx + j + 1];
+        const uint32_t v = funnel_r(prev, nxt, sh);
+        const int keep = len - 32 * j;
+        out[j] = keep >= 32 ? v : (keep <= 0 ? 0u : (v & (0xFFFFFFFFu >> (32 - keep))));
+        prev = nxt;
+    }
+    out[NW] = 0u;
+}
+
+// reset(): highways::reset (:106-119) + _construct_hurdles (:441-455), straight from the 2-bit streams.
+// Lane l < 0 compares (read >> |l|) with ref, lane l >= 0 compares (ref >> l) with read (a7).  The four planes are
+// held as 32-bit words, so a shifted word is ONE funnel shift of two neighbours and a lane word is two more logic ops;
+// shifts of 32 and more (bands beyond 31 lanes) re-read the shifted string from the stream instead.
+// r0/r1 (f0/f1) = C|T and G|T plane streams of the read (ref), rbit/fbit = the string's first bit in them; the streams
+// must be readable for 2W+3 words from the string's first word.
 template <int W, bool CORR = false>
-GASMA_HD void pair_init(const KParams& P, const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W],
-                        const uint64_t B1[W], int m, int n, const LaneStore& S, PairState& ps) {
-    constexpr int BITS = 64 * W;
+GASMA_HD void pair_init32(const KParams& P, const uint32_t* r0, const uint32_t* r1, int rbit, int m, const uint32_t* f0,
+                          const uint32_t* f1, int fbit, int n, const LaneStore& S, PairState& ps) {
+    constexpr int BITS = 64 * W, NW = 2 * W;
+    uint32_t A0[NW + 1], A1[NW + 1], B0[NW + 1], B1[NW + 1];
+    extract_plane32<W>(r0, rbit, m, A0);
+    extract_plane32<W>(r1, rbit, m, A1);
+    extract_plane32<W>(f0, fbit, n, B0);
+    extract_plane32<W>(f1, fbit, n, B1);
     int lb, ub;
     lane_range<CORR>(P.k, m, n, lb, ub);
     for (int l = lb; l <= ub; ++l) {
-        uint64_t og[W];
-        build_lane<W>(A0, A1, B0, B1, l, og);
-        lane_store<W>(S, l - lb, og);
+        const int a = iabs(l);
+        uint32_t* b = S.lanes + (size_t)((l - lb) * NW) * S.stride;
+        if (a >= 32) {   // rare: the shifted string comes from the stream again
+            uint32_t T0[NW + 1], T1[NW + 1];
+            extract_plane32<W>(l < 0 ? r0 : f0, (l < 0 ? rbit : fbit) + a, (l < 0 ? m : n) - a, T0);
+            extract_plane32<W>(l < 0 ? r1 : f1, (l < 0 ? rbit : fbit) + a, (l < 0 ? m : n) - a, T1);
+#pragma unroll
+            for (int w = 0; w < NW; ++w)
+                b[w * S.stride] = l < 0 ? ((T0[w] ^ B0[w]) | (T1[w] ^ B1[w])) : ((T0[w] ^ A0[w]) | (T1[w] ^ A1[w]));
+        } else if (l < 0) {
+#pragma unroll
+            for (int w = 0; w < NW; ++w)
+                b[w * S.stride] = (funnel_r(A0[w], A0[w + 1], a) ^ B0[w]) | (funnel_r(A1[w], A1[w + 1], a) ^ B1[w]);
+        } else {
+#pragma unroll
+            for (int w = 0; w < NW; ++w)
+                b[w * S.stride] = (funnel_r(B0[w], B0[w + 1], a) ^ A0[w]) | (funnel_r(B1[w], B1[w + 1], a) ^ A1[w]);
+        }
         S.state[(l - lb) * S.stride] = st_pack(-1, 0, BITS, BITS);
     }
     ps.lb = lb; ps.ub = ub;
     ps.m = m; ps.n = n; ps.cl = 0; ps.cc = 0; ps.cost = 0; ps.steps = 0; ps.first = true;
+}
+
+// The same from already extracted 64-bit planes (host harness, callers that hold planes): the planes are laid out as
+// zero-padded streams that start at bit 0.
+template <int W, bool CORR = false>
+GASMA_HD void pair_init(const KParams& P, const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W],
+                        const uint64_t B1[W], int m, int n, const LaneStore& S, PairState& ps) {
+    constexpr int NW = 2 * W;
+    uint32_t s[4][NW + 4];
+#pragma unroll
+    for (int j = 0; j < NW + 4; ++j) {
+        const int q = j >> 1;
+        s[0][j] = j < NW ? (uint32_t)(A0[q] >> (32 * (j & 1))) : 0u;
+        s[1][j] = j < NW ? (uint32_t)(A1[q] >> (32 * (j & 1))) : 0u;
+        s[2][j] = j < NW ? (uint32_t)(B0[q] >> (32 * (j & 1))) : 0u;
+        s[3][j] = j < NW ? (uint32_t)(B1[q] >> (32 * (j & 1))) : 0u;
+    }
+    pair_init32<W, CORR>(P, s[0], s[1], 0, m, s[2], s[3], 0, n, S, ps);
 }
 
 // One _step() (hurdle_matrix.h:407-434) including its _update_highway_list and _choose_best_highway.

@@ -59,9 +59,9 @@ __device__ __forceinline__ bool stage_tile(const uint8_t* __restrict__ buf, uint
 
 template <int W>
 __host__ __device__ constexpr int stream_chunks(int tile) { return tile * 4 * W + 2; }
-// uint16 elements per stream array incl. padding so that extract_plane may read 2W+1 words past any start
+// uint16 elements per stream array incl. padding so that extract_plane / pair_init32 may read 2W+3 words from any start
 template <int W>
-__host__ __device__ constexpr int stream_elems(int tile) { return ((stream_chunks<W>(tile) + 2 * (2 * W + 2) + 7) / 8) * 8; }
+__host__ __device__ constexpr int stream_elems(int tile) { return ((stream_chunks<W>(tile) + 2 * (2 * W + 4) + 7) / 8) * 8; }
 
 // ---------------------------------------------------------------------------------------------
 // K2+K3: persistent warps, one alignment per thread, finished threads refilled from a per-warp pool.
@@ -209,13 +209,9 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
                     cost[my_p] = INT32_MIN;
                     if (nops_out) nops_out[my_p] = 0u;
                 } else {
-                    uint64_t A0[W], A1[W], B0[W], B1[W];
                     const int rbit = (int)(s_roff[q] - rbase), fbit = (int)(s_foff[q] - fbase);
-                    extract_plane<W>(reinterpret_cast<const uint32_t*>(s_r0), rbit, m, A0);
-                    extract_plane<W>(reinterpret_cast<const uint32_t*>(s_r1), rbit, m, A1);
-                    extract_plane<W>(reinterpret_cast<const uint32_t*>(s_f0), fbit, nn, B0);
-                    extract_plane<W>(reinterpret_cast<const uint32_t*>(s_f1), fbit, nn, B1);
-                    pair_init<W, CORR>(P, A0, A1, B0, B1, m, nn, S, ps);
+                    pair_init32<W, CORR>(P, reinterpret_cast<const uint32_t*>(s_r0), reinterpret_cast<const uint32_t*>(s_r1), rbit, m,
+                                         reinterpret_cast<const uint32_t*>(s_f0), reinterpret_cast<const uint32_t*>(s_f1), fbit, nn, S, ps);
                     sink = OpSink{ops_stage ? ops_stage + (size_t)my_p * ops_stride : nullptr, ops_stride, 0};
                     active = true;
                 }

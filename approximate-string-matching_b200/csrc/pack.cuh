@@ -34,35 +34,51 @@ GASMA_HD void pack_word(uint32_t x, uint32_t& n0, uint32_t& n1) {
     n1 = gather4(g | t);
 }
 
-// 4 characters -> plane nibbles, assuming they are all in {A,C,G,T}; `bad` collects the proof that they are.
-// ASCII A=0x41 C=0x43 G=0x47 T=0x54: bit 2 is the G/T plane and bit1^bit2 the C/T plane.  The character is then
-// rebuilt from its two bits (0x41 + 2*ct + 6*gt + 11*(ct&gt) gives 0x41/0x43/0x47/0x54; bytes never carry) and
-// compared with the input, so any other byte leaves a non-zero mark in `bad`.
-GASMA_HD void pack_word_acgt(uint32_t x, uint32_t& n0, uint32_t& n1, uint32_t& bad) {
-    const uint32_t gt = (x >> 2) & 0x01010101u;
-    const uint32_t ct = ((x >> 1) ^ (x >> 2)) & 0x01010101u;
-    const uint32_t rebuilt = 0x41414141u + 2u * ct + 6u * gt + 11u * (ct & gt);
+// 4 characters -> the top nibbles of two products, assuming they are all in {A,C,G,T}; `bad` collects the proof that
+// they are.  ASCII A=0x41 C=0x43 G=0x47 T=0x54: bit 2 is the G/T plane, bit 1 (C or G) XOR bit 2 the C/T plane.
+// The masked bits stay where they are and ONE multiply per plane moves bit 8j+2 (8j+1) of byte j to bit 28+j:
+// 0x04081020 = 2^26+2^19+2^12+2^5 (0x08102040 = twice that); the 16 partial products land on 16 distinct bits, so no
+// carry reaches bits 28..31.  The caller appends the nibbles with funnel shifts and forms C/T = bit1 ^ bit2 once per
+// chunk.  Validation: the character is rebuilt from its two bits -- 0x41 + (bits 1,2 in place) + 15 where the pattern
+// is "bit 2 without bit 1" (T = 0x41 + 4 + 15) -- and compared with the input: any other byte leaves a mark in `bad`.
+GASMA_HD void pack_word_acgt(uint32_t x, uint32_t& prod_b1, uint32_t& prod_b2, uint32_t& bad) {
+    const uint32_t h = x & 0x02020202u, g = x & 0x04040404u;
+    const uint32_t t = (g >> 2) & ~(h >> 1);                       // 1 per byte that looks like 'T'
+    const uint32_t rebuilt = 0x41414141u + (h | g) + 15u * t;      // bytes never carry: at most 0x41 + 4 + 15
     bad |= rebuilt ^ x;
-    // bit 8j -> bit 28+j: 0x10204080 = 2^28+2^21+2^14+2^7; the cross terms fall below bit 28 on distinct bits or overflow
-    n0 = (ct * 0x10204080u) >> 28;
-    n1 = (gt * 0x10204080u) >> 28;
+    prod_b1 = h * 0x08102040u;
+    prod_b2 = g * 0x04081020u;
+}
+
+// (acc << 4) | top nibble of prod
+GASMA_HD uint32_t append_nibble(uint32_t acc, uint32_t prod) {
+#if defined(__CUDA_ARCH__)
+    return __funnelshift_l(prod, acc, 4);
+#else
+    return (acc << 4) | (prod >> 28);
+#endif
 }
 
 // 16 characters -> 16 + 16 plane bits
 GASMA_HD void pack_chunk(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, uint32_t& p0, uint32_t& p1) {
-    uint32_t a0, a1, b0, b1, c0, c1, d0, d1, bad = 0u;
-    pack_word_acgt(w0, a0, a1, bad);
-    pack_word_acgt(w1, b0, b1, bad);
-    pack_word_acgt(w2, c0, c1, bad);
-    pack_word_acgt(w3, d0, d1, bad);
+    uint32_t a1, a2, b1, b2, c1, c2, d1, d2, bad = 0u;
+    pack_word_acgt(w0, a1, a2, bad);
+    pack_word_acgt(w1, b1, b2, bad);
+    pack_word_acgt(w2, c1, c2, bad);
+    pack_word_acgt(w3, d1, d2, bad);
     if (bad) {   // some byte is not A/C/G/T (N, lower case, NUL ...): exact compares, such bytes pack as 00
+        uint32_t a0, b0, c0, d0;
         pack_word(w0, a0, a1);
         pack_word(w1, b0, b1);
         pack_word(w2, c0, c1);
         pack_word(w3, d0, d1);
+        p0 = a0 | (b0 << 4) | (c0 << 8) | (d0 << 12);
+        p1 = a1 | (b1 << 4) | (c1 << 8) | (d1 << 12);
+        return;
     }
-    p0 = a0 | (b0 << 4) | (c0 << 8) | (d0 << 12);
-    p1 = a1 | (b1 << 4) | (c1 << 8) | (d1 << 12);
+    const uint32_t bit1 = append_nibble(append_nibble(append_nibble(d1 >> 28, c1), b1), a1);   // C or G
+    p1 = append_nibble(append_nibble(append_nibble(d2 >> 28, c2), b2), a2);                     // G or T
+    p0 = bit1 ^ p1;                                                                           // C or T
 }
 
 // Window of W 64-bit words starting at bit `bit` of a 32-bit-word stream, bits >= len cleared
