@@ -38,6 +38,8 @@ struct gasma_ctx {
     int device = 0;
     int sm_count = 148;
     int refill_threshold = 8;   // idle threads in a warp that trigger a refill from the pool (greedy kernel)
+    int greedy_warps = 0;       // warps per CTA of the thread-per-pair greedy kernel: 0 = most resident warps (env GASMA_GREEDY_WARPS: 2, 4, 8)
+    int auto_warps = 0;         // the choice made for the current (W, lanes); reset by derive()
     int correction = 0;         // gasma_set_correction: widened band of the reference's -DCORRECTION build
     int max_delta = 0;          // largest |ref_len - read_len| the widened band has lane slots for
     cudaStream_t stream = nullptr;      // stream all work goes to
@@ -121,6 +123,7 @@ void derive(gasma_ctx* c) {
     c->kp.ms = log(p.match_prob / 0.25);
     c->kp.mms = log(p.mismatch_prob / 0.25);
     c->kp.ids = log(p.indel_prob / 2 / 0.25);
+    c->auto_warps = 0;
     c->kp.correction = c->correction;
     c->kp.nl = 2 * p.k + 1 + (c->correction ? c->max_delta : 0);
 }
@@ -139,7 +142,8 @@ template <int W, int WARPS, bool CORR>
 int launch_greedy_t(gasma_ctx* ctx, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, const uint32_t* foff,
                     int64_t n, int32_t* cost, uint16_t* stage, int stride, uint32_t* nops, uint32_t* chunk_counter,
                     uint32_t* status, unsigned long long* steps) {
-    const size_t smem = greedy_smem_bytes<W>(WARPS, ctx->kp.nl);
+    size_t smem = greedy_smem_bytes<W>(WARPS, ctx->kp.nl);
+    if (const char* env = getenv("GASMA_SMEM_PAD")) smem += (size_t)atoi(env);   // occupancy experiments only
     auto kern = greedy_kernel<W, WARPS, CORR>;
     CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
@@ -161,6 +165,35 @@ template <int W>
 int launch_greedy_w(gasma_ctx* ctx, int warps, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs,
                     const uint32_t* foff, int64_t n, int32_t* cost, uint16_t* stage, int stride, uint32_t* nops,
                     uint32_t* chunk_counter, uint32_t* status, unsigned long long* steps) {
+    if (!ctx->kp.correction && warps == 4) {
+        // CTA shape: per-warp work is independent, so the shape only decides how many warps an SM holds (shared
+        // memory per warp is fixed, the per-CTA reservation and the register file are not).  Pick the most resident warps.
+        int pick = ctx->greedy_warps;
+        if (pick == 0) {
+            if (ctx->auto_warps == 0) {
+                int best = 0;
+                auto consider = [&](int w, auto kern) {
+                    const size_t smem = greedy_smem_bytes<W>(w, ctx->kp.nl);
+                    int per_sm = 0;
+                    if (smem > kMaxSmem) return;
+                    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess ||
+                        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 32 * w, smem) != cudaSuccess) {
+                        cudaGetLastError();
+                        return;
+                    }
+                    if (per_sm * w > best) { best = per_sm * w; ctx->auto_warps = w; }
+                };
+                consider(4, greedy_kernel<W, 4, false>);
+                consider(8, greedy_kernel<W, 8, false>);
+                consider(2, greedy_kernel<W, 2, false>);
+                if (ctx->auto_warps == 0) ctx->auto_warps = 4;
+            }
+            pick = ctx->auto_warps;
+        }
+        if (pick == 2) return launch_greedy_t<W, 2, false>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, chunk_counter, status, steps);
+        if (pick == 8 && greedy_smem_bytes<W>(8, ctx->kp.nl) <= kMaxSmem)
+            return launch_greedy_t<W, 8, false>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, chunk_counter, status, steps);
+    }
     if (ctx->kp.correction) {
         if (warps == 4) return launch_greedy_t<W, 4, true>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, chunk_counter, status, steps);
         return launch_greedy_t<W, 1, true>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, chunk_counter, status, steps);
@@ -253,6 +286,10 @@ int gasma_create(const gasma_params* params, int device, gasma_ctx** out) {
     if (const char* env = getenv("GASMA_REFILL_THRESHOLD")) {   // tuning knob; results do not depend on it
         const int v = atoi(env);
         if (v >= 1 && v <= 32) c->refill_threshold = v;
+    }
+    if (const char* env = getenv("GASMA_GREEDY_WARPS")) {       // CTA shape of the greedy kernel; results do not depend on it
+        const int v = atoi(env);
+        if (v == 2 || v == 4 || v == 8) c->greedy_warps = v;
     }
     c->trace = getenv("GASMA_TRACE") != nullptr;
     if (const char* env = getenv("GASMA_SLICES")) {             // pipeline depth of the host-pointer calls; same results

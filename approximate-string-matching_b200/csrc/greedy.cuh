@@ -20,6 +20,20 @@ namespace gasma {
 GASMA_HD uint64_t st_pack(int sp, int len, int nsw, int nh) {
     return (uint64_t)(uint32_t)((sp + 1) | (len << 16)) | ((uint64_t)(uint32_t)(nsw | (nh << 16)) << 32);
 }
+// The same four fields in ONE 32-bit word, a byte each, for vectors of up to 192 bits (W <= 3): starting_point+1 <=
+// 64W+MAX_K+1 = 243, length and num_hurdles <= 192, num_switches <= 100.  Halves the state's shared memory (more
+// alignments in flight per SM) and the registers / selects of the two arg-max candidates.
+GASMA_HD uint32_t st_pack32(int sp, int len, int nsw, int nh) {
+    return (uint32_t)((sp + 1) | (len << 8) | (nsw << 16) | (nh << 24));
+}
+GASMA_HD int st_sp(uint32_t s) { return (int)(s & 0xFFu) - 1; }
+GASMA_HD int st_len(uint32_t s) { return (int)((s >> 8) & 0xFFu); }
+GASMA_HD int st_nsw(uint32_t s) { return (int)((s >> 16) & 0xFFu); }
+GASMA_HD int st_nh(uint32_t s) { return (int)(s >> 24); }
+template <int W> struct LaneState { using type = uint64_t; static GASMA_HD type pack(int sp, int len, int nsw, int nh) { return st_pack(sp, len, nsw, nh); } };
+template <> struct LaneState<1> { using type = uint32_t; static GASMA_HD type pack(int sp, int len, int nsw, int nh) { return st_pack32(sp, len, nsw, nh); } };
+template <> struct LaneState<2> : LaneState<1> {};
+template <> struct LaneState<3> : LaneState<1> {};
 GASMA_HD int st_sp(uint64_t s) { return (int)((uint32_t)s & 0xFFFFu) - 1; }
 GASMA_HD int st_len(uint64_t s) { return (int)((uint32_t)s >> 16); }
 GASMA_HD int st_nsw(uint64_t s) { return (int)((uint32_t)(s >> 32) & 0xFFFFu); }
@@ -34,9 +48,10 @@ GASMA_HD int st_nh(uint64_t s) { return (int)((uint32_t)(s >> 32) >> 16); }
 // word by word inside the scans (3 ALU ops per word), which halves the shared memory per alignment.
 // `stride` is the number of threads sharing the array (1 in the host harness).
 // ---------------------------------------------------------------------------------------------
+template <int W>
 struct LaneStore {
     uint32_t* lanes;
-    uint64_t* state;  // [li][stride]
+    typename LaneState<W>::type* state;  // [li][stride]
     int stride;
 };
 
@@ -171,7 +186,7 @@ GASMA_HD int pcb(const uint32_t* base, int stride, int from, int to) {
 }
 
 template <int W>
-GASMA_HD const uint32_t* lane_base(const LaneStore& S, int li) { return S.lanes + (size_t)(li * 2 * W) * S.stride; }
+GASMA_HD const uint32_t* lane_base(const LaneStore<W>& S, int li) { return S.lanes + (size_t)(li * 2 * W) * S.stride; }
 
 struct OpSink {
     uint16_t* ops;   // this pair's staging row (may be null: costs only)
@@ -233,7 +248,7 @@ GASMA_HD void extract_plane32(const uint32_t* stream32, int bit, int len, uint32
 // must be readable for 2W+3 words from the string's first word.
 template <int W, bool CORR = false>
 GASMA_HD void pair_init32(const KParams& P, const uint32_t* r0, const uint32_t* r1, int rbit, int m, const uint32_t* f0,
-                          const uint32_t* f1, int fbit, int n, const LaneStore& S, PairState& ps) {
+                          const uint32_t* f1, int fbit, int n, const LaneStore<W>& S, PairState& ps) {
     constexpr int BITS = 64 * W, NW = 2 * W;
     uint32_t A0[NW + 1], A1[NW + 1], B0[NW + 1], B1[NW + 1];
     extract_plane32<W>(r0, rbit, m, A0);
@@ -261,7 +276,7 @@ GASMA_HD void pair_init32(const KParams& P, const uint32_t* r0, const uint32_t* 
             for (int w = 0; w < NW; ++w)
                 b[w * S.stride] = (funnel_r(B0[w], B0[w + 1], a) ^ A0[w]) | (funnel_r(B1[w], B1[w + 1], a) ^ A1[w]);
         }
-        S.state[(l - lb) * S.stride] = st_pack(-1, 0, BITS, BITS);
+        S.state[(l - lb) * S.stride] = LaneState<W>::pack(-1, 0, BITS, BITS);
     }
     ps.lb = lb; ps.ub = ub;
     ps.m = m; ps.n = n; ps.cl = 0; ps.cc = 0; ps.cost = 0; ps.steps = 0; ps.first = true;
@@ -271,7 +286,7 @@ GASMA_HD void pair_init32(const KParams& P, const uint32_t* r0, const uint32_t* 
 // zero-padded streams that start at bit 0.
 template <int W, bool CORR = false>
 GASMA_HD void pair_init(const KParams& P, const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W],
-                        const uint64_t B1[W], int m, int n, const LaneStore& S, PairState& ps) {
+                        const uint64_t B1[W], int m, int n, const LaneStore<W>& S, PairState& ps) {
     constexpr int NW = 2 * W;
     uint32_t s[4][NW + 4];
 #pragma unroll
@@ -288,7 +303,7 @@ GASMA_HD void pair_init(const KParams& P, const uint64_t A0[W], const uint64_t A
 // One _step() (hurdle_matrix.h:407-434) including its _update_highway_list and _choose_best_highway.
 // Returns true when the traversal is over (the caller then runs pair_finish).
 template <int W, bool CORR = false>
-GASMA_HD bool pair_step(const KParams& P, const LaneStore& S, PairState& ps, OpSink& sink, uint32_t& status) {
+GASMA_HD bool pair_step(const KParams& P, const LaneStore<W>& S, PairState& ps, OpSink& sink, uint32_t& status) {
     constexpr int BITS = 64 * W;
     const int x = P.x, o = P.o, e = P.e;
     const int lb = CORR ? ps.lb : -P.k, ub = CORR ? ps.ub : P.k;
@@ -301,13 +316,14 @@ GASMA_HD bool pair_step(const KParams& P, const LaneStore& S, PairState& ps, OpS
     // ---- _update_highway_list, loops 1 and 2 fused: both arg-max candidates are tracked, the one that
     // applies is picked once `reach` is known (hurdle_matrix.h:291-352) ----
     bool reach = false;
-    double bestH_s = 0.0; int bestLeap_s = 0, bl_s = 0; uint64_t st_s = 0; bool have_s = false;
-    int bestH_r = 0, bestLeap_r = 0, bl_r = 0; uint64_t st_r = 0; bool have_r = false;
+    using ST = typename LaneState<W>::type;
+    double bestH_s = 0.0; int bestLeap_s = 0, bl_s = 0; ST st_s = 0; bool have_s = false;
+    int bestH_r = 0, bestLeap_r = 0, bl_r = 0; ST st_r = 0; bool have_r = false;
     for (int l = lb; l <= ub; ++l) {
         const int li = l - lb;
         const int sc = cc + sfc(cl, l);
         const int de = lane_destination(m, n, l);
-        uint64_t st = S.state[li * S.stride];
+        ST st = S.state[li * S.stride];
         int sp = st_sp(st), len = st_len(st), nsw = st_nsw(st);
         if (sp < sc) {  // cache miss: look up the closest highway of this lane (:293-310)
             nsw = iabs(l - cl);
@@ -317,7 +333,7 @@ GASMA_HD bool pair_step(const KParams& P, const LaneStore& S, PairState& ps, OpS
         const int sw = leap_cost ? slp(cl, l, o, e) : 0;
         const int nh = pcb<W>(lane_base<W>(S, li), S.stride, sc, sp + len);
         const int hc = x * nh;
-        st = st_pack(sp, len, nsw, nh);
+        st = LaneState<W>::pack(sp, len, nsw, nh);
         S.state[li * S.stride] = st;
         // significance heuristic (:328-332): ((ms*len) + (mms*nh)) + (ids*nsw), each op rounded
         const double h = dadd(dadd(dmul(P.ms, (double)len), dmul(P.mms, (double)nh)), dmul(P.ids, (double)nsw));
@@ -334,18 +350,18 @@ GASMA_HD bool pair_step(const KParams& P, const LaneStore& S, PairState& ps, OpS
         }
     }
     const int bl = reach ? bl_r : bl_s;
-    const uint64_t st_bl = reach ? st_r : st_s;
+    const ST st_bl = reach ? st_r : st_s;
     if (st_len(st_bl) <= 0) return true;  // no usable highway (:358-360, :570)
 
     // ---- _choose_best_highway (:368-401) ----
     const int spb = st_sp(st_bl);
     const int swb = leap_cost ? slp(cl, bl, o, e) : 0;
     int sT = x * st_nh(st_bl) + swb, sI = sT, b = bl;
-    uint64_t st_b = st_bl;
+    ST st_b = st_bl;
     const uint32_t* ob = lane_base<W>(S, bl - lb);
     for (int l = lb; l <= ub; ++l) {
         if (l == bl) continue;
-        const uint64_t st = S.state[(l - lb) * S.stride];
+        const ST st = S.state[(l - lb) * S.stride];
         const int sp = st_sp(st), s_l = sfc(l, bl);
         if (sp + s_l > spb) continue;
         const int end = sp + st_len(st);
@@ -369,7 +385,7 @@ GASMA_HD bool pair_step(const KParams& P, const LaneStore& S, PairState& ps, OpS
 // run() fix-up (hurdle_matrix.h:575-590).  A destination lane outside the band keeps the state of a fresh
 // object: lane value 1 (utils.h:57-59) and destination -|lane| (hurdle_matrix.h:79-92 with m=n=0).
 template <int W, bool CORR = false>
-GASMA_HD void pair_finish(const KParams& P, const LaneStore& S, PairState& ps, OpSink& sink) {
+GASMA_HD void pair_finish(const KParams& P, const LaneStore<W>& S, PairState& ps, OpSink& sink) {
     const int x = P.x;
     const int lb = CORR ? ps.lb : -P.k, ub = CORR ? ps.ub : P.k;
     const int dl = ps.n - ps.m, cl = ps.cl, cc = ps.cc;
@@ -387,7 +403,7 @@ GASMA_HD void pair_finish(const KParams& P, const LaneStore& S, PairState& ps, O
 // The whole alignment of one pair (host harness, and kernels that do not interleave pairs).  Returns status bits.
 template <int W, bool CORR = false>
 GASMA_HD uint32_t greedy_pair(const KParams& P, const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W],
-                              const uint64_t B1[W], int m, int n, const LaneStore& S, OpSink& sink, int& cost_out,
+                              const uint64_t B1[W], int m, int n, const LaneStore<W>& S, OpSink& sink, int& cost_out,
                               int& steps_out) {
     PairState ps;
     uint32_t status = 0;

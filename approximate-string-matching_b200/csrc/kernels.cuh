@@ -77,13 +77,13 @@ constexpr int kPool = 32;   // pairs per chunk = per warp pool
 
 template <int W>
 __host__ __device__ constexpr size_t greedy_smem_bytes(int warps, int nl) {   // nl = lane slots per alignment (KParams::nl)
-    return (size_t)nl * (2 * W * 4 + 8) * 32 * warps   // lanes (2W 32-bit words) + state, per thread
-           + (size_t)warps * (4 * (size_t)stream_elems<W>(kPool) * 2 + 2 * (kPool + 1) * 4)   // per-warp streams + offsets
+    return (size_t)nl * (2 * W * 4 + sizeof(typename LaneState<W>::type)) * 32 * warps   // lanes (2W 32-bit words) + state, per thread
+           + (size_t)warps * (4 * (size_t)stream_elems<W>(kPool) * 2)   // per-warp 2-bit streams (the pool's offsets live in registers)
            + 64;
 }
 
 template <int W, int WARPS, bool CORR>
-__global__ void __launch_bounds__(32 * WARPS, WARPS == 4 && !CORR ? 5 : 1)
+__global__ void __launch_bounds__(32 * WARPS, CORR ? 1 : (WARPS == 8 ? 3 : (WARPS == 4 ? 5 : (WARPS == 2 ? 11 : 1))))
 greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __restrict__ read_off,
               const uint8_t* __restrict__ refs, const uint32_t* __restrict__ ref_off, long long n,
               int32_t* __restrict__ cost, uint16_t* __restrict__ ops_stage, int ops_stride,
@@ -94,24 +94,22 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
     constexpr int SE = stream_elems<W>(kPool);
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int nl = P.nl;
-    uint64_t* s_state = reinterpret_cast<uint64_t*>(smem_raw);
+    using ST = typename LaneState<W>::type;
+    ST* s_state = reinterpret_cast<ST*>(smem_raw);
     uint32_t* s_lanes = reinterpret_cast<uint32_t*>(s_state + (size_t)nl * T);
     uint16_t* s_streams = reinterpret_cast<uint16_t*>(s_lanes + (size_t)nl * 2 * W * T);
-    uint32_t* s_offs = reinterpret_cast<uint32_t*>(s_streams + (size_t)WARPS * 4 * SE);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     uint16_t* s_r0 = s_streams + (size_t)warp * 4 * SE;
     uint16_t* s_r1 = s_r0 + SE;
     uint16_t* s_f0 = s_r1 + SE;
     uint16_t* s_f1 = s_f0 + SE;
-    uint32_t* s_roff = s_offs + warp * 2 * (kPool + 1);
-    uint32_t* s_foff = s_roff + (kPool + 1);
     // zero the stream padding once so every later read is of initialised memory (stale bits past a string's
     // length are masked by extract_plane)
     for (int i = lane; i < SE; i += 32) { s_r0[i] = 0; s_r1[i] = 0; s_f0[i] = 0; s_f1[i] = 0; }
     __syncwarp();
 
-    const LaneStore S{s_lanes + tid, s_state + tid, T};
+    const LaneStore<W> S{s_lanes + tid, s_state + tid, T};
     const uint32_t nchunks = (uint32_t)((n + kPool - 1) / kPool);
     const uint32_t rtotal = read_off[n], ftotal = ref_off[n];
 
@@ -120,6 +118,9 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
     int pool_next = 0, pool_count = 0;
     bool pool_ok = true;
     uint32_t rbase = 0, fbase = 0;
+    // offsets of the pool's pairs: lane i holds off[p0 + min(i, count)], the end offsets are warp-uniform; a thread
+    // that takes pair q reads them with shuffles (the hand-out runs with the warp converged)
+    uint32_t pl_ro = 0, pl_fo = 0, pl_re = 0, pl_fe = 0;
     // The NEXT chunk is claimed and brought towards the SM while the current pool is being worked on, one
     // stage per loop iteration so that no stage waits for the previous one's memory round trip:
     //   kClaimed   lane 0 has issued the atomicAdd, its result is not consumed yet
@@ -176,11 +177,9 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
                     pool_count = nx_count;
                     pool_next = 0;
                     __syncwarp();
-                    if (lane < pool_count) { s_roff[lane] = nx_ro; s_foff[lane] = nx_fo; }
-                    if (lane == 0) { s_roff[pool_count] = nx_re; s_foff[pool_count] = nx_fe; }
-                    __syncwarp();
-                    rbase = s_roff[0] & ~15u;
-                    fbase = s_foff[0] & ~15u;
+                    pl_ro = nx_ro; pl_fo = nx_fo; pl_re = nx_re; pl_fe = nx_fe;
+                    rbase = __shfl_sync(0xffffffffu, pl_ro, 0) & ~15u;
+                    fbase = __shfl_sync(0xffffffffu, pl_fo, 0) & ~15u;
                     pool_ok = true;
 #pragma unroll 1
                     for (int side = 0; side < 2; ++side)   // one instance of the pack code for both sides
@@ -194,10 +193,14 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
             }
             // ---- hand the pool's next pairs to the idle threads ----
             const int q = pool_next + __popc(idle & ((1u << lane) - 1u));
+            const int q0 = imin(q, 31), q1 = imin(q + 1, 31);
+            const uint32_t ro_q = __shfl_sync(0xffffffffu, pl_ro, q0), fo_q = __shfl_sync(0xffffffffu, pl_fo, q0);
+            uint32_t ro_q1 = __shfl_sync(0xffffffffu, pl_ro, q1), fo_q1 = __shfl_sync(0xffffffffu, pl_fo, q1);
+            if (q + 1 > 31) { ro_q1 = pl_re; fo_q1 = pl_fe; }
             if (!active && q < pool_count) {
                 my_p = pool_p0 + q;
-                const int m = (int)(s_roff[q + 1] - s_roff[q]);
-                const int nn = (int)(s_foff[q + 1] - s_foff[q]);
+                const int m = (int)(ro_q1 - ro_q);
+                const int nn = (int)(fo_q1 - fo_q);
                 uint32_t bad = 0;
                 if (!pool_ok) bad |= kStatusTile;
                 if (m > BITS || nn > BITS) bad |= kStatusLength;
@@ -209,7 +212,7 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
                     cost[my_p] = INT32_MIN;
                     if (nops_out) nops_out[my_p] = 0u;
                 } else {
-                    const int rbit = (int)(s_roff[q] - rbase), fbit = (int)(s_foff[q] - fbase);
+                    const int rbit = (int)(ro_q - rbase), fbit = (int)(fo_q - fbase);
                     pair_init32<W, CORR>(P, reinterpret_cast<const uint32_t*>(s_r0), reinterpret_cast<const uint32_t*>(s_r1), rbit, m,
                                          reinterpret_cast<const uint32_t*>(s_f0), reinterpret_cast<const uint32_t*>(s_f1), fbit, nn, S, ps);
                     sink = OpSink{ops_stage ? ops_stage + (size_t)my_p * ops_stride : nullptr, ops_stride, 0};

@@ -52,7 +52,7 @@ int sim_greedy(const KParams& P, const uint8_t* reads, const uint32_t* roff, con
     constexpr int BITS = 64 * W;
     const int nl = CORR ? P.nl : 2 * P.k + 1;
     std::vector<uint32_t> lanes((size_t)nl * 2 * W);
-    std::vector<uint64_t> state(nl);
+    std::vector<typename LaneState<W>::type> state(nl);
     std::vector<uint16_t> r0(elems<W>(T)), r1(elems<W>(T)), f0(elems<W>(T)), f1(elems<W>(T));
     uint32_t status = 0;
     int64_t steps_total = 0;
@@ -79,7 +79,7 @@ int sim_greedy(const KParams& P, const uint8_t* reads, const uint32_t* roff, con
                 extract_plane<W>(reinterpret_cast<const uint32_t*>(r1.data()), rbit, m, A1);
                 extract_plane<W>(reinterpret_cast<const uint32_t*>(f0.data()), fbit, nn, B0);
                 extract_plane<W>(reinterpret_cast<const uint32_t*>(f1.data()), fbit, nn, B1);
-                LaneStore S{lanes.data(), state.data(), 1};
+                LaneStore<W> S{lanes.data(), state.data(), 1};
                 OpSink sink{ops_stage ? ops_stage + (size_t)(p0 + t) * stride : nullptr, stride, 0};
                 st = greedy_pair<W, CORR>(P, A0, A1, B0, B1, m, nn, S, sink, c, steps);
                 my = (uint32_t)sink.n;
