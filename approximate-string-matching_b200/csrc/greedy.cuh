@@ -124,6 +124,28 @@ GASMA_HD void scan_highway_loop(const uint32_t* base, int stride, int sc, int& s
     }
 }
 
+// Continuation of a search whose highway start sp is known and whose flipped lane holds no hurdle in [sp, q):
+// len = (first hurdle at/after bit q) - sp, BITS if none follows.  Words that start beyond the destination column de
+// are not visited: a highway that long is clamped to the destination by the caller whatever its exact end.
+template <int W>
+GASMA_HD int scan_highway_tail(const uint32_t* base, int stride, int q, int de, int sp) {
+    constexpr int NW = 2 * W, BITS = 64 * W;
+    int w = q >> 5;
+    if (w >= NW) return BITS;
+    uint32_t prev = w > 0 ? base[(w - 1) * stride] : 0u;
+    uint32_t cur = base[w * stride];
+    uint32_t mask = 0xFFFFFFFFu << (q & 31);
+    for (;;) {
+        const uint32_t next = w + 1 < NW ? base[(w + 1) * stride] : 0u;
+        const uint32_t t = flip_word(prev, cur, next) & mask;
+        if (t) return 32 * w + ctz32(t) - sp;
+        if (++w >= NW || 32 * w > de) return BITS;
+        prev = cur;
+        cur = next;
+        mask = 0xFFFFFFFFu;
+    }
+}
+
 GASMA_HD uint32_t funnel_r(uint32_t lo, uint32_t hi, int s) {  // low word of (hi:lo) >> s, 0 <= s < 32
 #if defined(__CUDA_ARCH__)
     return __funnelshift_r(lo, hi, s);
@@ -159,13 +181,13 @@ GASMA_HD void scan_highway(const uint32_t* base, int stride, int sc, int de, int
             sp = sc + fz;
             len = (tlo ? ctz32(tlo) : 32 + ctz32(thi)) - fz;
             resolved = true;
-        } else if (sc + 64 >= BITS || sc + 64 > de) {   // no hurdle up to the end of the vector / past the destination
+        } else {   // the highway leaves the window: no hurdle up to the end of the vector / past the destination, or go on
             sp = sc + fz;
-            len = BITS;
+            len = (sc + 64 >= BITS || sc + 64 > de) ? BITS : scan_highway_tail<W>(base, stride, sc + 64, de, sp);
             resolved = true;
         }
     }
-    if (!resolved) scan_highway_loop<W>(base, stride, sc, sp, len);
+    if (!resolved) scan_highway_loop<W>(base, stride, sc, sp, len);   // 64 hurdles in a row
 }
 
 // pop_count_between(from,to), utils.h:263-270 = shift_left(from).shift_right(from+BITS-to).pop_count():
