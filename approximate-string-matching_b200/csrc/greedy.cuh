@@ -244,6 +244,15 @@ GASMA_HD void lane_range(int k, int m, int n, int& lb, int& ub) {
     if (CORR) { if (m <= n) ub = n - m + k; else lb = n - m - k; }
 }
 
+// mask of the low n bits; n <= 0 gives 0, n >= 32 all ones
+GASMA_HD uint32_t low_bits(int n) {
+#if defined(__CUDA_ARCH__)
+    return __funnelshift_lc(0xFFFFFFFFu, 0u, (uint32_t)imax(n, 0));   // clamps the shift at 32
+#else
+    return n <= 0 ? 0u : (n >= 32 ? 0xFFFFFFFFu : (0xFFFFFFFFu >> (32 - n)));
+#endif
+}
+
 // 32-bit plane words of a string: word j = bits [32j, 32j+32) of the stream window that starts at bit `bit`, bits >= len
 // cleared (the canonical 'A' tail), plus one zero word on top.  The stream must be readable for 2W+1 words from bit>>5.
 template <int W>
@@ -255,8 +264,7 @@ GASMA_HD void extract_plane32(const uint32_t* stream32, int bit, int len, uint32
     for (int j = 0; j < NW; ++j) {
         const uint32_t nxt = stream32[idx + j + 1];
         const uint32_t v = funnel_r(prev, nxt, sh);
-        const int keep = len - 32 * j;
-        out[j] = keep >= 32 ? v : (keep <= 0 ? 0u : (v & (0xFFFFFFFFu >> (32 - keep))));
+        out[j] = v & low_bits(len - 32 * j);
         prev = nxt;
     }
     out[NW] = 0u;
@@ -339,8 +347,9 @@ GASMA_HD bool pair_step(const KParams& P, const LaneStore<W>& S, PairState& ps, 
     // applies is picked once `reach` is known (hurdle_matrix.h:291-352) ----
     bool reach = false;
     using ST = typename LaneState<W>::type;
-    double bestH_s = 0.0; int bestLeap_s = 0, bl_s = 0; ST st_s = 0; bool have_s = false;
-    int bestH_r = 0, bestLeap_r = 0, bl_r = 0; ST st_r = 0; bool have_r = false;
+    // both maxima start below every candidate (the heuristics are finite), so the first lane is always taken
+    double bestH_s = -1.0e300; int bestLeap_s = 0, bl_s = 0; ST st_s = 0;
+    int bestH_r = INT32_MIN, bestLeap_r = 0, bl_r = 0; ST st_r = 0;
     for (int l = lb; l <= ub; ++l) {
         const int li = l - lb;
         const int sc = cc + sfc(cl, l);
@@ -360,15 +369,15 @@ GASMA_HD bool pair_step(const KParams& P, const LaneStore<W>& S, PairState& ps, 
         // significance heuristic (:328-332): ((ms*len) + (mms*nh)) + (ids*nsw), each op rounded
         const double h = dadd(dadd(dmul(P.ms, (double)len), dmul(P.mms, (double)nh)), dmul(P.ids, (double)nsw));
         const int lh = -sw;
-        if (!have_s || h > bestH_s || (h == bestH_s && lh > bestLeap_s)) {
-            have_s = true; bestH_s = h; bestLeap_s = lh; bl_s = l; st_s = st;
+        if (h > bestH_s || (h == bestH_s && lh > bestLeap_s)) {
+            bestH_s = h; bestLeap_s = lh; bl_s = l; st_s = st;
         }
         // destination heuristic (:334-342), integer valued
         const int fsw = GLOBAL ? slp(l, dl, o, e) : 0;
         const int hr = -sw - hc - fsw - x * (de - sp - len);
         const int lhr = -sw - fsw;
-        if (!have_r || hr > bestH_r || (hr == bestH_r && lhr > bestLeap_r)) {
-            have_r = true; bestH_r = hr; bestLeap_r = lhr; bl_r = l; st_r = st;
+        if (hr > bestH_r || (hr == bestH_r && lhr > bestLeap_r)) {
+            bestH_r = hr; bestLeap_r = lhr; bl_r = l; st_r = st;
         }
     }
     const int bl = reach ? bl_r : bl_s;
