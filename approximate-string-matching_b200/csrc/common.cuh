@@ -84,11 +84,17 @@ GASMA_HD uint64_t ones_from(int s, int j) { return shl64(~0ull, imax(s - 64 * j,
 
 // ---- lane geometry -------------------------------------------------------------------------
 // switch_lane_penalty, utils.h:576-579
-GASMA_HD int slp(int l1, int l2, int o, int e) { return l1 == l2 ? 0 : o + e * (iabs(l1 - l2) - 1); }
+// = min(d,1)*(o-e) + e*d with d = |l1-l2|: branch-free, two multiply-adds
+GASMA_HD int slp(int l1, int l2, int o, int e) {
+    const int d = iabs(l1 - l2);
+    return imin(d, 1) * (o - e) + e * d;
+}
 // switch_forward_column, utils.h:587-593
+// Lanes on opposite sides of lane 0 (sign bits differ, neither is 0) cost |l1|, otherwise max(|l1|-|l2|, 0).  When
+// one of them is 0 both forms agree, so the sign test alone decides: max(|l1| - (opposite ? 0 : |l2|), 0).
 GASMA_HD int sfc(int l1, int l2) {
-    int a1 = iabs(l1), a2 = iabs(l2);
-    return (l1 * l2 >= 0) ? imax(a1 - a2, 0) : a1;
+    const int a2 = ((l1 ^ l2) < 0) ? 0 : iabs(l2);
+    return imax(iabs(l1) - a2, 0);
 }
 // highways::_calculate_destination, hurdle_matrix.h:58-68, closed form: min(m+min(l,0), n-max(l,0))
 GASMA_HD int lane_destination(int m, int n, int l) { return imin(m + imin(l, 0), n - imax(l, 0)); }
