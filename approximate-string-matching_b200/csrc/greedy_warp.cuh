@@ -124,11 +124,13 @@ greedy_warp_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t*
             const uint32_t* Y0 = s_plane + (l < 0 ? 2 : 0) * L::PLANE;
             const uint32_t* Y1 = Y0 + L::PLANE;
             uint32_t* row = s_lanes + (size_t)li * PITCH;
+            // |l| <= MAX_K = 50, so aw <= 1 and the last word read is PLANE-1 (the planes carry two zero words on top);
+            // each plane word is loaded once and slides from "upper" to "lower" half of the funnel shift
+            uint32_t x0a = X0[aw], x1a = X1[aw];
             for (int w = 0; w < NW; ++w) {
-                const int j = w + aw;
-                const uint32_t x0a = j < L::PLANE ? X0[j] : 0u, x0b = j + 1 < L::PLANE ? X0[j + 1] : 0u;
-                const uint32_t x1a = j < L::PLANE ? X1[j] : 0u, x1b = j + 1 < L::PLANE ? X1[j + 1] : 0u;
+                const uint32_t x0b = X0[w + aw + 1], x1b = X1[w + aw + 1];
                 row[w] = (__funnelshift_r(x0a, x0b, ab) ^ Y0[w]) | (__funnelshift_r(x1a, x1b, ab) ^ Y1[w]);
+                x0a = x0b; x1a = x1b;
             }
             s_state[li] = st_pack(-1, 0, BITS, BITS);
         }
@@ -178,13 +180,27 @@ greedy_warp_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t*
                 if (cand_better(d, cr)) cr = d;
             }
             const bool reach = __ballot_sync(0xffffffffu, reach_local) != 0u;
-            WarpCand best = reach ? cr : cs;
-#pragma unroll
-            for (int d = 16; d; d >>= 1) {
-                const WarpCand other = cand_shfl_xor(best, d);
-                if (cand_better(other, best)) best = other;
+            const WarpCand mine = reach ? cr : cs;
+            // Warp arg-max of (heuristic, leap, -lane) in three integer max-reductions (REDUX) instead of five
+            // rounds of 7-register shuffles: the double is mapped to an unsigned key of the same order (sign bit
+            // flipped, negative values complemented; -0 folded into +0 first), its high and low words are reduced
+            // one after the other, then (leap, -lane) among the lanes that tie.  leap = -(switch costs) lies in
+            // (-2^22, 0] for penalties <= 1000, 63 - lane in [13, 113].
+            unsigned long long hk = 0ull;
+            if (mine.valid) {
+                const long long bits = __double_as_longlong(dadd(mine.h, 0.0));
+                hk = (unsigned long long)bits ^ ((unsigned long long)(bits >> 63) | 0x8000000000000000ull);
             }
-            __syncwarp();   // every lane's refreshed state is visible before _choose_best_highway reads it
+            const uint32_t hk_hi = (uint32_t)(hk >> 32), hk_lo = (uint32_t)hk;
+            const uint32_t m_hi = __reduce_max_sync(0xffffffffu, hk_hi);
+            const uint32_t m_lo = __reduce_max_sync(0xffffffffu, hk_hi == m_hi ? hk_lo : 0u);
+            const bool tie = mine.valid && hk_hi == m_hi && hk_lo == m_lo;
+            const uint32_t k2 = tie ? (((uint32_t)(mine.leap + (1 << 22)) << 8) | (uint32_t)(63 - mine.l)) : 0u;
+            const uint32_t m2 = __reduce_max_sync(0xffffffffu, k2);
+            __syncwarp();   // every lane's refreshed state is visible before it is read back / _choose_best_highway reads it
+            WarpCand best;
+            best.l = 63 - (int)(m2 & 0xFFu);
+            best.st = s_state[best.l - lb];
             const int bl = best.l;
             if (st_len(best.st) <= 0) break;   // no usable highway (:358-360)
 
@@ -215,10 +231,10 @@ greedy_warp_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t*
                     after = __ffs((int)take) - 1;
                     sT = __shfl_sync(0xffffffffu, tc, after);
                     sI = __shfl_sync(0xffffffffu, ic, after);
-                    st_b = __shfl_sync(0xffffffffu, stv, after);
                     b = base + after + lb;
                 }
             }
+            if (b != bl) st_b = s_state[b - lb];   // the taken lane's highway (its state was refreshed above)
             // _step (:412-433)
             pen += (leap_cost ? slp(cl, b, o, e) : 0) + x * st_nh(st_b);
             const int endb = st_sp(st_b) + st_len(st_b);
