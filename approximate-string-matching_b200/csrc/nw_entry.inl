@@ -103,7 +103,7 @@ int launch_nw_counters_w(gasma_ctx* ctx, const uint8_t* reads, const uint32_t* r
     CU(cudaEventRecord(mev[0], ctx->stream));
     CU(cudaMemsetAsync(dcount, 0, 8, ctx->stream));   // deferred count + hard count (misc[4], misc[5])
     auto tk = nw_band_kernel<W, TT, kNwCounters>;
-    const size_t tsmem = myers_trace_smem_bytes<W>(TT);
+    const size_t tsmem = myers_trace_smem_bytes<W>(TT) + kTileGops * sizeof(uint16_t);   // + the tile's greedy ops
     CU(cudaFuncSetAttribute(tk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsmem));
     tk<<<(unsigned)((n + TT - 1) / TT), TT, tsmem, ctx->stream>>>(reads, roff, refs, foff, (long long)n, gcost, penalty, nullptr, stride,
                                                                 nullptr, (uint32_t*)ctx->nw_deferred.p, dcount, misc, ca);

@@ -202,6 +202,10 @@ nw_myers_kernel(const uint8_t* __restrict__ reads, const uint32_t* __restrict__ 
 //           A deferred pair is not counted here: nw_wide_kernel writes its CIGAR and
 //           nw_deferred_counters_kernel counts it from there.
 constexpr int kNwPenalty = 0, kNwOps = 1, kNwCounters = 2;
+// MODE 2 keeps the greedy CIGAR ops of the tile's pairs (one contiguous CSR range) in shared memory, copied with
+// coalesced loads next to the tile staging: the per-pair loop over them then runs on shared-memory latency instead
+// of one dependent L2 round trip per op at a handful of active threads.  A tile with more ops reads them from global.
+constexpr int kTileGops = 512;
 
 struct NwCounterArgs {
     const uint16_t* g_ops;        // greedy CIGAR (CSR)
@@ -230,10 +234,20 @@ nw_band_kernel(const uint8_t* __restrict__ reads, const uint32_t* __restrict__ r
     uint16_t* s_f1 = s_f0 + stream_elems<W>(T);
     uint32_t* s_roff = reinterpret_cast<uint32_t*>(s_f1 + stream_elems<W>(T));
     uint32_t* s_foff = s_roff + (T + 1);
+    uint16_t* s_gops = reinterpret_cast<uint16_t*>(s_foff + (T + 1));   // MODE 2 only (kTileGops entries)
 
     const int tid = threadIdx.x;
     const long long p0 = (long long)blockIdx.x * T;
     const int np = (int)((n - p0) < (long long)T ? (n - p0) : (long long)T);
+    uint32_t g_lo = 0u;
+    bool gops_staged = false;
+    if (MODE == kNwCounters) {
+        g_lo = ca.g_off[p0];
+        const uint32_t g_cnt = ca.g_off[p0 + np] - g_lo;
+        gops_staged = g_cnt <= (uint32_t)kTileGops;
+        if (gops_staged)
+            for (uint32_t i = tid; i < g_cnt; i += T) s_gops[i] = ca.g_ops[g_lo + i];
+    }
     for (int i = tid; i <= np; i += T) { s_roff[i] = read_off[p0 + i]; s_foff[i] = ref_off[p0 + i]; }
     for (int i = tid; i < stream_elems<W>(T); i += T) { s_r0[i] = 0; s_r1[i] = 0; s_f0[i] = 0; s_f1[i] = 0; }
     __syncthreads();
@@ -278,7 +292,9 @@ nw_band_kernel(const uint8_t* __restrict__ reads, const uint32_t* __restrict__ r
                 uint32_t P1[2 * W], P2[2 * W], a0[2 * W], a1[2 * W];
                 runs3_positions<2 * W>(t.E, t.B, P2);                    // LCM2: read positions under '=' runs >= 3
                 const uint32_t g0 = ca.g_off[p];
-                lcm_toggles<2 * W>(ca.g_ops + g0, (int)(ca.g_off[p + 1] - g0), 1, P1);
+                const int gn = (int)(ca.g_off[p + 1] - g0);
+                if (gops_staged) lcm_toggles<2 * W>(s_gops + (g0 - g_lo), gn, 1, P1);
+                else lcm_toggles<2 * W>(ca.g_ops + g0, gn, 1, P1);
                 prefix_xor_fill<2 * W>(P1);                              // LCM1: read positions under greedy M runs
 #pragma unroll
                 for (int w = 0; w < W; ++w) {
