@@ -96,3 +96,32 @@ def test_widened_band_logic_matches_golden(ol, host_sim, golden):
         assert st == 0
         assert cost.tolist() == s["cost"], s["name"]
         assert text == s["cigar"], s["name"]
+
+
+def test_numa_binding_helper(pkg, tmp_path, monkeypatch):
+    """shard.bind_host_to_device on a fake sysfs tree: picks the GPU's node, intersects with the current affinity,
+    and leaves single-node boxes alone."""
+    import os
+    import types
+    from gasma_b200 import shard
+    import torch
+    props = types.SimpleNamespace(pci_domain_id=0, pci_bus_id=0x1b, pci_device_id=0)
+    monkeypatch.setattr(torch.cuda, "get_device_properties", lambda d: props)
+    sysfs = tmp_path / "sys"
+    (sysfs / "bus/pci/devices/0000:1b:00.0").mkdir(parents=True)
+    (sysfs / "bus/pci/devices/0000:1b:00.0/numa_node").write_text("1\n")
+    for node, cpus in ((0, "0-1"), (1, "%s" % ",".join(str(c) for c in sorted(os.sched_getaffinity(0))[:1]))):
+        (sysfs / ("devices/system/node/node%d" % node)).mkdir(parents=True)
+        (sysfs / ("devices/system/node/node%d/cpulist" % node)).write_text(cpus + "\n")
+    assert shard.device_numa_node(0, str(sysfs)) == 1
+    before = os.sched_getaffinity(0)
+    try:
+        got = shard.bind_host_to_device(0, str(sysfs))
+        assert got == (1, 1) and len(os.sched_getaffinity(0)) == 1
+    finally:
+        os.sched_setaffinity(0, before)
+    # one node only: nothing to bind to
+    import shutil
+    shutil.rmtree(sysfs / "devices/system/node/node0")
+    assert shard.bind_host_to_device(0, str(sysfs)) is None
+    assert shard._parse_cpulist("0-3,8,10-11") == {0, 1, 2, 3, 8, 10, 11}
