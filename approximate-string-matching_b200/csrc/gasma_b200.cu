@@ -39,6 +39,7 @@ struct gasma_ctx {
     int sm_count = 148;
     int refill_threshold = 8;   // idle threads in a warp that trigger a refill from the pool (greedy kernel)
     int greedy_warps = 0;       // warps per CTA of the thread-per-pair greedy kernel: 0 = most resident warps (env GASMA_GREEDY_WARPS: 2, 4, 8)
+    bool counter_clean = false;  // the greedy kernel's chunk counter is 0 (left so by scan_tiles_kernel of the previous batch)
     int auto_warps = 0;         // the choice made for the current (W, lanes); reset by derive()
     int correction = 0;         // gasma_set_correction: widened band of the reference's -DCORRECTION build
     int max_delta = 0;          // largest |ref_len - read_len| the widened band has lane slots for
@@ -55,6 +56,7 @@ struct gasma_ctx {
     int64_t launches = 0;
     std::string err;
     // device scratch
+    DevBuf g_tile_sums;          // per-tile op counts of the greedy path: accumulated by the greedy kernel, zeroed again by the scan
     DevBuf ops_stage, nops, tile_sums, tile_bases, misc;  // misc: [0] status u32, [1] total ops u32, [2..3] step counter u64
     // device mirrors for the host-pointer entry points
     DevBuf d_reads, d_refs, d_read_off, d_ref_off, d_cost, d_ops, d_op_off, d_p0, d_p1;
@@ -141,7 +143,7 @@ int greedy_warps_for(int nl) {
 template <int W, int WARPS, bool CORR>
 int launch_greedy_t(gasma_ctx* ctx, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, const uint32_t* foff,
                     int64_t n, int32_t* cost, uint16_t* stage, int stride, uint32_t* nops, uint32_t* chunk_counter,
-                    uint32_t* status, unsigned long long* steps) {
+                    uint32_t* status, unsigned long long* steps, uint32_t* tsums) {
     size_t smem = greedy_smem_bytes<W>(WARPS, ctx->kp.nl);
     if (const char* env = getenv("GASMA_SMEM_PAD")) smem += (size_t)atoi(env);   // occupancy experiments only
     auto kern = greedy_kernel<W, WARPS, CORR>;
@@ -153,9 +155,9 @@ int launch_greedy_t(gasma_ctx* ctx, const uint8_t* reads, const uint32_t* roff, 
     const int64_t chunks = (n + kPool - 1) / kPool;
     int64_t grid = (int64_t)ctx->sm_count * per_sm;
     if (grid * WARPS > chunks) grid = (chunks + WARPS - 1) / WARPS;
-    CU(cudaMemsetAsync(chunk_counter, 0, 4, ctx->stream));
+    if (!ctx->counter_clean) CU(cudaMemsetAsync(chunk_counter, 0, 4, ctx->stream));
     kern<<<(unsigned)grid, 32 * WARPS, smem, ctx->stream>>>(ctx->kp, reads, roff, refs, foff, (long long)n, cost, stage, stride,
-                                                          nops, chunk_counter, ctx->refill_threshold, status, steps);
+                                                          nops, chunk_counter, ctx->refill_threshold, status, steps, tsums);
     CU(cudaGetLastError());
     ctx->launches++;
     return GASMA_OK;
@@ -164,7 +166,7 @@ int launch_greedy_t(gasma_ctx* ctx, const uint8_t* reads, const uint32_t* roff, 
 template <int W>
 int launch_greedy_w(gasma_ctx* ctx, int warps, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs,
                     const uint32_t* foff, int64_t n, int32_t* cost, uint16_t* stage, int stride, uint32_t* nops,
-                    uint32_t* chunk_counter, uint32_t* status, unsigned long long* steps) {
+                    uint32_t* chunk_counter, uint32_t* status, unsigned long long* steps, uint32_t* tsums) {
     if (!ctx->kp.correction && warps == 4) {
         // CTA shape: per-warp work is independent, so the shape only decides how many warps an SM holds (shared
         // memory per warp is fixed, the per-CTA reservation and the register file are not).  Pick the most resident warps.
@@ -190,16 +192,16 @@ int launch_greedy_w(gasma_ctx* ctx, int warps, const uint8_t* reads, const uint3
             }
             pick = ctx->auto_warps;
         }
-        if (pick == 2) return launch_greedy_t<W, 2, false>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, chunk_counter, status, steps);
+        if (pick == 2) return launch_greedy_t<W, 2, false>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, chunk_counter, status, steps, tsums);
         if (pick == 8 && greedy_smem_bytes<W>(8, ctx->kp.nl) <= kMaxSmem)
-            return launch_greedy_t<W, 8, false>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, chunk_counter, status, steps);
+            return launch_greedy_t<W, 8, false>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, chunk_counter, status, steps, tsums);
     }
     if (ctx->kp.correction) {
-        if (warps == 4) return launch_greedy_t<W, 4, true>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, chunk_counter, status, steps);
-        return launch_greedy_t<W, 1, true>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, chunk_counter, status, steps);
+        if (warps == 4) return launch_greedy_t<W, 4, true>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, chunk_counter, status, steps, tsums);
+        return launch_greedy_t<W, 1, true>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, chunk_counter, status, steps, tsums);
     }
-    if (warps == 4) return launch_greedy_t<W, 4, false>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, chunk_counter, status, steps);
-    return launch_greedy_t<W, 1, false>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, chunk_counter, status, steps);
+    if (warps == 4) return launch_greedy_t<W, 4, false>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, chunk_counter, status, steps, tsums);
+    return launch_greedy_t<W, 1, false>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, chunk_counter, status, steps, tsums);
 }
 
 int greedy_tile_threads(const gasma_ctx* c) {   // 0 = configuration does not fit
@@ -217,7 +219,7 @@ int greedy_tile_threads(const gasma_ctx* c) {   // 0 = configuration does not fi
 template <int W>
 int launch_greedy_warp(gasma_ctx* ctx, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, const uint32_t* foff,
                        int64_t n, int32_t* cost, uint16_t* stage, int stride, uint32_t* nops, uint32_t* pair_counter,
-                       uint32_t* status, unsigned long long* steps) {
+                       uint32_t* status, unsigned long long* steps, uint32_t* tsums) {
     constexpr int WARPS = 4;
     const size_t smem = WARPS * ((WarpLayout<W>::bytes_per_warp(ctx->kp.nl) + 15) / 16 * 16);
     auto kern = greedy_warp_kernel<W, WARPS>;
@@ -227,9 +229,9 @@ int launch_greedy_warp(gasma_ctx* ctx, const uint8_t* reads, const uint32_t* rof
     if (per_sm < 1) return fail(ctx, GASMA_E_CUDA, "warp-per-alignment kernel does not fit an SM");
     int64_t grid = (int64_t)ctx->sm_count * per_sm;
     if (grid * WARPS > n) grid = (n + WARPS - 1) / WARPS;
-    CU(cudaMemsetAsync(pair_counter, 0, 4, ctx->stream));
+    if (!ctx->counter_clean) CU(cudaMemsetAsync(pair_counter, 0, 4, ctx->stream));
     kern<<<(unsigned)grid, 32 * WARPS, smem, ctx->stream>>>(ctx->kp, reads, roff, refs, foff, (long long)n, cost, stage, stride, nops,
-                                                          pair_counter, status, steps);
+                                                          pair_counter, status, steps, tsums);
     CU(cudaGetLastError());
     ctx->launches++;
     return GASMA_OK;
@@ -330,7 +332,7 @@ void gasma_destroy(gasma_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
-    DevBuf* bufs[] = {&c->ops_stage, &c->nops, &c->tile_sums, &c->tile_bases, &c->misc, &c->d_reads, &c->d_refs,
+    DevBuf* bufs[] = {&c->g_tile_sums, &c->ops_stage, &c->nops, &c->tile_sums, &c->tile_bases, &c->misc, &c->d_reads, &c->d_refs,
                       &c->d_read_off, &c->d_ref_off, &c->d_cost, &c->d_ops, &c->d_op_off, &c->d_p0, &c->d_p1, &c->gen_len, &c->d_bound, &c->nw_deferred, &c->nw_tb, &c->nw_pool_hi, &c->nw_pool_tb,
                       &c->bm_hard, &c->bm_gops, &c->bm_goff, &c->bm_nops, &c->bm_noff, &c->bm_gcost, &c->bm_nwpen, &c->bm_counters, &c->bm_answers};
     for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
@@ -485,9 +487,12 @@ int greedy_dev_impl(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_read_
     if (want_ops) {
         if ((rc = reserve(ctx, ctx->ops_stage, (size_t)n * stride * sizeof(uint16_t)))) return rc;
         if ((rc = reserve(ctx, ctx->nops, (size_t)n * 4))) return rc;
-        if ((rc = reserve(ctx, ctx->tile_sums, (size_t)ntiles * 4))) return rc;
+        const void* before = ctx->g_tile_sums.p;
+        if ((rc = reserve(ctx, ctx->g_tile_sums, (size_t)ntiles * 4))) return rc;
+        if (ctx->g_tile_sums.p != before) CU(cudaMemsetAsync(ctx->g_tile_sums.p, 0, ctx->g_tile_sums.cap, ctx->stream));
         if ((rc = reserve(ctx, ctx->tile_bases, (size_t)ntiles * 4))) return rc;
     }
+    uint32_t* tsums = want_ops ? (uint32_t*)ctx->g_tile_sums.p : nullptr;
     uint16_t* stage = want_ops ? (uint16_t*)ctx->ops_stage.p : nullptr;
     uint32_t* nops = want_ops ? (uint32_t*)ctx->nops.p : nullptr;
     const uint8_t* r = (const uint8_t*)d_reads;
@@ -497,25 +502,27 @@ int greedy_dev_impl(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_read_
     cudaEvent_t* evp = ctx->ev[0][ctx->ev_count[0] % gasma_ctx::kRing];
     CU(cudaEventRecord(evp[0], ctx->stream));
     switch (ctx->W) {
-        case 1: rc = launch_greedy_w<1>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, chunk_counter, misc, steps); break;
-        case 2: rc = launch_greedy_w<2>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, chunk_counter, misc, steps); break;
-        case 3: rc = launch_greedy_w<3>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, chunk_counter, misc, steps); break;
-        case 4: rc = launch_greedy_w<4>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, chunk_counter, misc, steps); break;
-        case 8: rc = launch_greedy_warp<8>(ctx, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, chunk_counter, misc, steps); break;
-        default: rc = launch_greedy_warp<16>(ctx, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, chunk_counter, misc, steps); break;
+        case 1: rc = launch_greedy_w<1>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, chunk_counter, misc, steps, tsums); break;
+        case 2: rc = launch_greedy_w<2>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, chunk_counter, misc, steps, tsums); break;
+        case 3: rc = launch_greedy_w<3>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, chunk_counter, misc, steps, tsums); break;
+        case 4: rc = launch_greedy_w<4>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, chunk_counter, misc, steps, tsums); break;
+        case 8: rc = launch_greedy_warp<8>(ctx, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, chunk_counter, misc, steps, tsums); break;
+        default: rc = launch_greedy_warp<16>(ctx, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, chunk_counter, misc, steps, tsums); break;
     }
     if (rc) return rc;
     CU(cudaEventRecord(evp[1], ctx->stream));
     ctx->ev_count[0]++;
+    ctx->counter_clean = false;   // the kernel leaves its chunk counter past the end
     if (want_ops) {
-        tile_sums_kernel<T><<<(unsigned)ntiles, T, 0, ctx->stream>>>(nops, (long long)n, (uint32_t*)ctx->tile_sums.p);
+        // the per-tile op counts were accumulated by the greedy kernel; the scan zeroes them again and resets the chunk counter
+        scan_tiles_kernel<<<1, 1024, 0, ctx->stream>>>(tsums, (uint32_t*)ctx->tile_bases.p, (int)ntiles, misc + 1, carry_ops ? misc + 1 : nullptr,
+                                                       true, chunk_counter);
         CU(cudaGetLastError());
-        scan_tiles_kernel<<<1, 1024, 0, ctx->stream>>>((uint32_t*)ctx->tile_sums.p, (uint32_t*)ctx->tile_bases.p, (int)ntiles, misc + 1, carry_ops ? misc + 1 : nullptr);
-        CU(cudaGetLastError());
+        ctx->counter_clean = true;
         compact_ops_kernel<T, false><<<(unsigned)ntiles, T, 0, ctx->stream>>>(stage, stride, nops, (uint32_t*)ctx->tile_bases.p,
                                                                      (long long)n, d_ops, (long long)ops_cap, d_op_off, 0);
         CU(cudaGetLastError());
-        ctx->launches += 3;
+        ctx->launches += 2;
     }
     return GASMA_OK;
 }

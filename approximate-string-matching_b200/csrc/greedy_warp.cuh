@@ -63,7 +63,8 @@ greedy_warp_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t*
                    const uint8_t* __restrict__ refs, const uint32_t* __restrict__ ref_off, long long n,
                    int32_t* __restrict__ cost, uint16_t* __restrict__ ops_stage, int ops_stride,
                    uint32_t* __restrict__ nops_out, uint32_t* __restrict__ pair_counter,
-                   uint32_t* __restrict__ status, unsigned long long* __restrict__ step_counter) {
+                   uint32_t* __restrict__ status, unsigned long long* __restrict__ step_counter,
+                   uint32_t* __restrict__ tile_sums) {
     using L = WarpLayout<W>;
     constexpr int BITS = 64 * W, NW = L::NW, PITCH = L::PITCH;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -258,6 +259,7 @@ greedy_warp_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t*
         if (lane == 0) {
             cost[p] = pen;
             if (nops_out) nops_out[p] = (uint32_t)n_ops;
+            if (tile_sums && n_ops) atomicAdd(tile_sums + (p >> 7), (uint32_t)n_ops);
             if (n_ops > ops_stride) st_bits |= kStatusSteps;
             steps_total += (unsigned long long)steps;
         }

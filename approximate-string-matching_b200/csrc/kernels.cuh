@@ -88,7 +88,8 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
               const uint8_t* __restrict__ refs, const uint32_t* __restrict__ ref_off, long long n,
               int32_t* __restrict__ cost, uint16_t* __restrict__ ops_stage, int ops_stride,
               uint32_t* __restrict__ nops_out, uint32_t* __restrict__ chunk_counter, int refill_threshold,
-              uint32_t* __restrict__ status, unsigned long long* __restrict__ step_counter) {
+              uint32_t* __restrict__ status, unsigned long long* __restrict__ step_counter,
+              uint32_t* __restrict__ tile_sums) {   // optional: op count per 128-pair tile, accumulated here (input of scan_tiles_kernel)
     constexpr int BITS = 64 * W;
     constexpr int T = 32 * WARPS;
     constexpr int SE = stream_elems<W>(kPool);
@@ -231,6 +232,7 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
                 pair_finish<W, CORR>(P, S, ps, sink);
                 cost[my_p] = ps.cost;
                 if (nops_out) nops_out[my_p] = (uint32_t)sink.n;
+                if (tile_sums && sink.n) atomicAdd(tile_sums + (my_p >> 7), (uint32_t)sink.n);
                 if (sink.n > ops_stride) st |= kStatusSteps;  // cannot happen: the stride covers the step limit
                 steps_done += (uint32_t)ps.steps;
                 active = false;
@@ -250,8 +252,11 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
 // Exclusive scan of per-tile counts (single CTA; a 1 M-pair batch has 7813 tiles).
 // base_in (optional, device) is added to every output so several launches can share one CSR array.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(1024) scan_tiles_kernel(const uint32_t* __restrict__ sums, uint32_t* __restrict__ bases,
-                                                          int ntiles, uint32_t* total_out, const uint32_t* base_in) {
+// clear_sums: the sums are zeroed once read (they are accumulated with atomics by the next greedy launch);
+// reset_word (optional) is set to 0 at the end (the greedy kernel's chunk counter) -- both save a memset per batch.
+__global__ void __launch_bounds__(1024) scan_tiles_kernel(uint32_t* __restrict__ sums, uint32_t* __restrict__ bases,
+                                                          int ntiles, uint32_t* total_out, const uint32_t* base_in,
+                                                          bool clear_sums = false, uint32_t* reset_word = nullptr) {
     __shared__ uint32_t s_warp[32];
     __shared__ uint32_t s_carry;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -260,6 +265,7 @@ __global__ void __launch_bounds__(1024) scan_tiles_kernel(const uint32_t* __rest
     for (int start = 0; start < ntiles; start += 1024) {
         const int i = start + tid;
         const uint32_t v = i < ntiles ? sums[i] : 0u;
+        if (clear_sums && i < ntiles) sums[i] = 0u;
         uint32_t inc = v;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
@@ -286,6 +292,7 @@ __global__ void __launch_bounds__(1024) scan_tiles_kernel(const uint32_t* __rest
         __syncthreads();
     }
     if (tid == 0 && total_out) *total_out = s_carry;
+    if (tid == 0 && reset_word) *reset_word = 0u;
 }
 
 // ---------------------------------------------------------------------------------------------
