@@ -538,7 +538,18 @@ int greedy_batch_pipelined(gasma_ctx* ctx, const char* reads, const uint32_t* re
     const int S = ctx->slices;
     const size_t ob = (size_t)(n + 1) * 4;
     int64_t edge[gasma_ctx::kSlices + 1];
-    for (int i = 0; i <= S; ++i) edge[i] = i == S ? n : ((n * i / S) / 128) * 128;
+    // The call ends one slice's kernels + result copies after the last input byte has arrived, so the last two slices
+    // are short (weights 1, ..., 1, 1/2, 1/5): the tail shrinks with them while the link stays saturated.
+    {
+        double w[gasma_ctx::kSlices], total = 0.0, acc = 0.0;
+        for (int i = 0; i < S; ++i) { w[i] = S >= 4 && i == S - 1 ? 0.2 : (S >= 4 && i == S - 2 ? 0.5 : 1.0); total += w[i]; }
+        edge[0] = 0;
+        for (int i = 1; i <= S; ++i) {
+            acc += w[i - 1];
+            edge[i] = i == S ? n : ((int64_t)((double)n * acc / total) / 128) * 128;
+            if (edge[i] < edge[i - 1]) edge[i] = edge[i - 1];
+        }
+    }
     char* d_reads = (char*)ctx->d_reads.p;
     char* d_refs = (char*)ctx->d_refs.p;
     uint32_t* d_roff = (uint32_t*)ctx->d_read_off.p;
