@@ -45,6 +45,7 @@ EXPORTS = [
     "gasma_nw_batch", "gasma_nw_batch_dev", "gasma_metrics_dev",
     "gasma_generate_ref_capacity", "gasma_generate_dev", "gasma_generate", "gasma_render_cigar",
     "gasma_benchmark_batch", "gasma_benchmark_batch_dev", "gasma_leap_batch", "gasma_leap_batch_dev",
+    "gasma_greedy_batch_dev_noalloc",
 ]
 
 _lib = None
@@ -79,7 +80,7 @@ def lib():
     L.gasma_last_step_count.restype = i64
     for name in ("gasma_pack2bit_batch", "gasma_pack2bit_batch_dev"):
         getattr(L, name).argtypes = [vp, vp, vp, i64, vp, vp]
-    for name in ("gasma_greedy_batch", "gasma_greedy_batch_dev"):
+    for name in ("gasma_greedy_batch", "gasma_greedy_batch_dev", "gasma_greedy_batch_dev_noalloc"):
         getattr(L, name).argtypes = [vp, vp, vp, vp, vp, i64, vp, vp, i64, vp]
     for name in ("gasma_nw_batch", "gasma_nw_batch_dev"):
         getattr(L, name).argtypes = [vp, vp, vp, vp, vp, i64, vp, vp, vp, i64, vp]
@@ -242,6 +243,13 @@ class Aligner:
         self._check(self._L.gasma_greedy_batch_dev(self._ctx, _dev_ptr(d_reads), _dev_ptr(d_read_off), _dev_ptr(d_refs),
                                                    _dev_ptr(d_ref_off), n, _dev_ptr(d_cost), _dev_ptr(d_ops),
                                                    0 if d_ops is None else d_ops.numel(), _dev_ptr(d_op_off)))
+
+    def greedy_batch_dev_noalloc(self, d_reads, d_read_off, d_refs, d_ref_off, n, d_cost, d_ops=None, d_op_off=None):
+        """The greedy step with its scratch in the library's static __device__ array: allocates nothing
+        (n <= 8192 pairs, max_length <= 256; calls that overlap on one GPU race on the array)."""
+        self._check(self._L.gasma_greedy_batch_dev_noalloc(self._ctx, _dev_ptr(d_reads), _dev_ptr(d_read_off), _dev_ptr(d_refs),
+                                                           _dev_ptr(d_ref_off), n, _dev_ptr(d_cost), _dev_ptr(d_ops),
+                                                           0 if d_ops is None else d_ops.numel(), _dev_ptr(d_op_off)))
 
     def nw_batch_dev(self, d_reads, d_read_off, d_refs, d_ref_off, n, d_bound, d_penalty, d_ops=None, d_op_off=None):
         self._check(self._L.gasma_nw_batch_dev(self._ctx, _dev_ptr(d_reads), _dev_ptr(d_read_off), _dev_ptr(d_refs),

@@ -789,3 +789,4 @@ int gasma_generate_dev(gasma_ctx* ctx, const gasma_gen_config* cfg, uint64_t fir
 #include "nw_entry.inl"
 #include "leap_entry.inl"
 #include "bench_entry.inl"
+#include "noalloc_entry.inl"

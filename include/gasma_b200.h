@@ -127,6 +127,22 @@ int gasma_greedy_batch_dev(gasma_ctx* ctx,
                            const char* d_refs, const uint32_t* d_ref_off, int64_t n_pairs,
                            int32_t* d_cost, gasma_cigar_op* d_ops, int64_t ops_cap, uint32_t* d_op_off);
 
+/* -- the greedy step without any allocation ------------------------------------------------------- */
+/* No counterpart in the reference; added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same inputs, outputs
+ * and results as gasma_greedy_batch_dev, but the call allocates NOTHING: its scratch (per-pair CIGAR staging rows,
+ * op counts, per-tile sums, chunk counter) is a file-scope __device__ array of the library, 8.6 MB that every GPU
+ * which loads the library holds until the process exits.  Limits: n_pairs <= GASMA_NOALLOC_MAX_PAIRS and the
+ * context's max_length <= GASMA_NOALLOC_MAX_LENGTH; anything larger is rejected with GASMA_E_UNSUPPORTED.
+ * All calls on one device share the array: calls that overlap on the GPU (different streams or contexts) race on
+ * it, so serialise them.  The array keeps the previous call's contents; the call clears what must start at zero. */
+#define GASMA_NOALLOC_MAX_PAIRS 8192
+#define GASMA_NOALLOC_MAX_LENGTH 256
+int gasma_greedy_batch_dev_noalloc(gasma_ctx* ctx,
+                                   const char* d_reads, const uint32_t* d_read_off,
+                                   const char* d_refs, const uint32_t* d_ref_off, int64_t n_pairs,
+                                   int32_t* d_cost, gasma_cigar_op* d_ops, int64_t ops_cap, uint32_t* d_op_off);
+
 /* -- LEAP comparator ----------------------------------------------------------- */
 /* Replaces benchmark::_run_LEAP (GASMA/benchmark/benchmark_utils.h:156-178): class LV of
  * GASMA/benchmark/LEAP_SIMD/LV_BAG.cpp set up as init(k, 200, ED_GLOBAL, x, o, e) (:289); k, x, o, e are the
