@@ -78,6 +78,42 @@ def oracle():
     return _oracle
 
 
+_fast = None
+
+
+def fast():
+    """oracle/libgasma_fast.so: the fast CPU arm (W fixed at compile time), bench.py's CPU baseline beyond 128 characters."""
+    global _fast
+    if _fast is None:
+        path = os.path.join(ORACLE_DIR, "libgasma_fast.so")
+        if not os.path.exists(path):
+            build_oracle()
+        L = C.CDLL(path)
+        L.gf_greedy_batch.restype = C.c_int
+        L.gf_greedy_batch.argtypes = ([C.c_void_p] * 4 + [C.c_int64] + [C.c_int] * 6 + [C.c_double] * 3 + [C.c_int] +
+                                      [C.c_void_p] * 3 + [C.c_int64, C.c_void_p])
+        _fast = L
+    return _fast
+
+
+def fast_greedy(b, k=3, x=1, o=1, e=1, W=2, global_=1, probs=DEFAULT_PROBS, threads=1, want_ops=True, ops_cap=None):
+    """cost + CIGAR CSR from the fast CPU arm (one pass; want_ops=False still builds every CIGAR, like get_CIGAR())."""
+    cost = np.zeros(b.n, np.int32)
+    op_off = np.zeros(b.n + 1, np.uint32)
+    cap = ops_cap if ops_cap is not None else max(16, 24 * b.n)
+    ops = np.zeros(cap, np.uint16) if want_ops else None
+    steps = C.c_int64(0)
+    rc = fast().gf_greedy_batch(_ptr(b.reads), _ptr(b.read_off), _ptr(b.refs), _ptr(b.ref_off), b.n, k, x, o, e, global_, W,
+                                probs[0], probs[1], probs[2], threads, _ptr(cost), _ptr(ops), _ptr(op_off), cap, C.byref(steps))
+    if rc == -4 and ops_cap is None:
+        return fast_greedy(b, k, x, o, e, W, global_, probs, threads, True, int(op_off[-1]))
+    assert rc == 0, rc
+    out = {"cost": cost, "op_off": op_off, "steps": steps.value}
+    if want_ops:
+        out["ops"] = ops[:int(op_off[-1])]
+    return out
+
+
 def ref_available():
     return os.path.exists(os.path.join(ORACLE_DIR, "_ref", "libgasma_ref.so"))
 

@@ -189,3 +189,91 @@ def test_oracle_correction_vs_reference_fresh(ol):
         plain = ol.ref_greedy(b, k, x, o, e, threads=4)
         differs += sum(a != c for a, c in zip(plain["text"], f["text"]))
     assert differs > 100   # the macro really changes results (pairs with n != m)
+
+
+# ---- the fast CPU arm (oracle/gasma_fast.cpp): bench.py's CPU baseline beyond the reference's 128 characters ----
+def test_fast_cpu_arm_matches_port_all_widths(ol):
+    rng = np.random.default_rng(777)
+    for W in (1, 2, 3, 4):
+        for (k, x, o, e, g) in [(3, 1, 1, 1, 1), (3, 1, 1, 1, 0), (9, 2, 3, 1, 1), (25, 1, 2, 1, 1), (50, 4, 6, 2, 1)]:
+            b = ol.random_batch(rng, 1500, 1, 64 * W, 0.3, 0.3, 50)
+            r = ol.oracle_greedy(b, ol.make_params(k, x, o, e, W, g), threads=4)
+            f = ol.fast_greedy(b, k, x, o, e, W, g, threads=3)
+            assert np.array_equal(r["cost"], f["cost"]), (W, k)
+            assert np.array_equal(r["op_off"], f["op_off"]), (W, k)
+            assert np.array_equal(r["ops"], f["ops"]), (W, k)
+            assert r["steps"] == f["steps"]
+    # non-ACGT bytes pack as 'A' (bit_convert.cpp:248), rejected pairs are flagged, empty strings work
+    b = ol.Batch.from_pairs([(b"ACGTNNacgtACGT", b"ACGTAAAAAAACGT"), (b"", b""), (b"A" * 130, b"A" * 130), (b"ACGT", b"AGT")])
+    r = ol.oracle_greedy(ol.Batch.from_pairs([b.pair(0), b.pair(1), b.pair(3)]), ol.make_params())
+    f = ol.fast_greedy(b, W=2)
+    assert f["cost"].tolist() == [r["cost"][0], r["cost"][1], -2**31, r["cost"][2]]
+    assert ol.render_all(f["ops"], f["op_off"]) == ol.render_all(r["ops"], r["op_off"])[:2] + ["", "1M1I2M"]
+
+
+def test_fast_cpu_arm_matches_reference_and_golden(ol, golden):
+    for s in golden("greedy_ref.json")["sets"]:
+        ps = s["params"]
+        b = _batch(ol, s["pairs"])
+        f = ol.fast_greedy(b, ps["k"], ps["x"], ps["o"], ps["e"], 2, 1, tuple(ps["probs"]), threads=2)
+        assert f["cost"].tolist() == s["cost"], s["name"]
+        assert ol.render_all(f["ops"], f["op_off"]) == s["cigar"], s["name"]
+    if not ol.ref_available():
+        pytest.skip("oracle/_ref not built (needs /root/reference)")
+    rng = np.random.default_rng(778)
+    b = ol.random_batch(rng, 6000, 1, 128, 0.3, 0.3, 50)
+    f = ol.fast_greedy(b, 5, 2, 3, 1, 2, threads=4)
+    r = ol.ref_greedy(b, 5, 2, 3, 1, threads=4)
+    assert f["cost"].tolist() == r["cost"].tolist()
+    assert ol.render_all(f["ops"], f["op_off"]) == r["text"]
+
+
+# ---- coverage metric: the port against the unmodified benchmark_coverage.h on fresh random inputs ----
+def test_coverage_port_vs_reference_fuzz(ol):
+    """go_lcm / go_covers (oracle/gasma_oracle.c) against long_consecutive_matching_substring / covers
+    (GASMA/benchmark/benchmark_coverage.h:26-91, unmodified, through oracle/_ref) on 100 k random CIGAR / string pairs."""
+    if not ol.ref_available():
+        pytest.skip("oracle/_ref not built (needs /root/reference)")
+    import ctypes as C
+    rng = np.random.default_rng(31337)
+    letters = "MID=X"
+    L, R = ol.oracle(), ol.ref()
+    out_o = np.zeros(512, np.uint8)
+    out_r = C.create_string_buffer(512)
+    n_lcm = n_cov = 0
+    for it in range(50000):
+        m = int(rng.integers(0, 200))
+        s1 = bytes(rng.choice(np.frombuffer(b"ACGT", np.uint8), m).tolist())
+        # a CIGAR that consumes exactly the m read characters; runs of every code, lengths 1..12
+        ops, left = [], m
+        while left > 0 or rng.random() < 0.15:
+            code = int(rng.integers(0, 5))
+            ln = int(rng.integers(1, 13))
+            if code != 2:
+                if left == 0:
+                    break
+                ln = min(ln, left)
+                left -= ln
+            ops.append((ln << 3) | code)
+        ops_np = np.array(ops if ops else [0], np.uint16)[:len(ops)]
+        text = "".join("%d%s" % (o >> 3, letters[o & 7]) for o in ops).encode()
+        thr = int(rng.integers(1, 5))
+        n1 = L.go_lcm(ol._ptr(np.frombuffer(s1 + b"\0", np.uint8)), m, ol._ptr(ops_np) if len(ops) else None, len(ops), thr,
+                      ol._ptr(out_o), 512)
+        n2 = R.gasma_ref_lcm(s1, b"", text, thr, out_r, 512)
+        assert n1 == n2 and out_o[:n1].tobytes() == out_r.raw[:n2], (s1, text, thr)
+        n_lcm += 1
+        # covers(a, b): b a subsequence of a; draw b as a noisy subsequence so that both outcomes occur
+        a = out_o[:n1].tobytes()
+        keep = rng.random(len(a)) < 0.6
+        bb = bytearray(np.frombuffer(a, np.uint8)[keep].tolist())
+        if len(bb) and rng.random() < 0.5:
+            bb[int(rng.integers(0, len(bb)))] = b"ACGT"[int(rng.integers(0, 4))]
+        if rng.random() < 0.1:
+            bb.append(b"ACGT"[int(rng.integers(0, 4))])
+        bb = bytes(bb)
+        c1 = L.go_covers(ol._ptr(np.frombuffer(a + b"\0", np.uint8)), len(a), ol._ptr(np.frombuffer(bb + b"\0", np.uint8)), len(bb))
+        c2 = R.gasma_ref_covers(a, bb)
+        assert c1 == c2, (a, bb)
+        n_cov += 1
+    assert n_lcm + n_cov >= 100000
