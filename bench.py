@@ -44,6 +44,8 @@ def parse():
     ap.add_argument("--cpu-sample", type=int, default=0, help="pairs in the CPU baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-full-path", action="store_true", help="skip the greedy + NW verifier + counters leg")
+    ap.add_argument("--no-configs", action="store_true", help="skip the short legs for the other BASELINE.json configs")
+    ap.add_argument("--no-parity", action="store_true", help="skip the oracle comparison of the timed outputs")
     return ap.parse_args()
 
 
@@ -65,6 +67,22 @@ def gen_config_for(pkg, a, seed):
     return pkg.gen_config(seed, a.length, a.error)
 
 
+def config_dict(a, ml):
+    """The SAME dict from both arms (the driver compares them)."""
+    return {"workload": workload_name(a), "max_length": ml, "length": a.length, "error_rate": a.error, "profile": a.profile,
+            "pairs_per_batch_per_gpu": a.pairs, "k": a.k, "penalties": "x=o=e=1",
+            "path": "greedy only: pack2bit + lanes + traversal + penalty + CIGAR (reset + run + get_cost + get_CIGAR)"}
+
+
+def lib_sha(pkg):
+    import hashlib
+    h = hashlib.sha1()
+    with open(pkg.LIB_PATH, "rb") as f:
+        for blk in iter(lambda: f.read(1 << 20), b""):
+            h.update(blk)
+    return h.hexdigest()[:16]
+
+
 def workload_name(a):
     if a.profile == "illumina":
         return ("synthetic Illumina-profile %d bp reads (per base: 2.452%% mismatch, 0.0468%% insert, 0.0553%% delete), "
@@ -82,6 +100,7 @@ class ClockSampler:
         self.index = index
         self.proc = None
         self.lines = []
+        self.on = False      # samples are kept only while a GPU leg (warm-up + timed region) is running
 
     def start(self):
         try:
@@ -94,7 +113,8 @@ class ClockSampler:
 
     def _pump(self):
         for line in self.proc.stdout:
-            self.lines.append(line.strip())
+            if self.on:
+                self.lines.append(line.strip())
 
     def stop(self):
         if not self.proc:
@@ -131,24 +151,61 @@ def measured_peak():
 
 
 # ------------------------------------------------------------------------------------------------
-# CPU baseline: the reference's own CPU implementation of the path (oracle/_ref, unmodified, when the
-# workload is inside its 128-character domain) or the plain-C W-word port (oracle/) otherwise.
-# This is the one place bench.py may execute anything under oracle/.
+# CPU side.  This is the one place bench.py may execute anything under oracle/:
+#   * the CHECKER (parity of the timed outputs, outside every timed region): the plain-C port oracle/gasma_oracle.c,
+#     which is pinned against the unmodified reference by tests/test_oracle.py;
+#   * the CPU BASELINE: the unmodified reference (oracle/_ref, kind "reference") when the workload is inside its
+#     128-character domain, else the fast CPU arm oracle/gasma_fast.cpp (kind "port": W fixed at compile time, 64-bit
+#     words, pext/popcnt; bit-equal to the checker and no slower than the reference at W=2 -- NOT the slow checker).
 # ------------------------------------------------------------------------------------------------
-def cpu_baseline(batch_np, a, max_length, target_seconds=10.0, threads=None):
+def _ol():
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_lib as ol
-    threads = threads or len(os.sched_getaffinity(0))
+    return ol
+
+
+def host_threads():
+    return len(os.sched_getaffinity(0))
+
+
+def parity_greedy(batch_np, k, W, got, label, threads=None):
+    """Full comparison of one batch's greedy output (cost, op_off, ops as numpy arrays) with the checker."""
+    ol = _ol()
     b = ol.Batch(*batch_np)
-    use_ref = max_length <= 128 and ol.ref_available()
-    if use_ref:
+    t0 = time.perf_counter()
+    ref = ol.oracle_greedy(b, ol.make_params(k, 1, 1, 1, W, 1), threads=threads or host_threads())
+    n_ops = int(ref["op_off"][-1])
+    got_ops = got["ops"][:int(got["op_off"][b.n])]
+    res = {"what": label, "pairs": int(b.n),
+           "cost_mismatch": int((got["cost"][:b.n] != ref["cost"]).sum()),
+           "op_off_mismatch": int((got["op_off"][:b.n + 1] != ref["op_off"]).sum()),
+           "ops_mismatch": int(n_ops != len(got_ops)) if n_ops != len(got_ops) else int((got_ops != ref["ops"]).sum()),
+           "oracle": "oracle/gasma_oracle.c (plain-C port, W=%d; pinned against the unmodified reference at W=2)" % W,
+           "checker_seconds": round(time.perf_counter() - t0, 2)}
+    res["ok"] = res["cost_mismatch"] == 0 and res["op_off_mismatch"] == 0 and res["ops_mismatch"] == 0
+    return res
+
+
+def cpu_greedy_baseline(batch_np, k, max_length, target_seconds=10.0, threads=None):
+    ol = _ol()
+    threads = threads or host_threads()
+    b = ol.Batch(*batch_np)
+    if max_length <= 128 and ol.ref_available():
         def run(bb):
-            ol.ref_greedy(bb, a.k, 1, 1, 1, mode=1, threads=threads, want_text=False)
+            ol.ref_greedy(bb, k, 1, 1, 1, mode=1, threads=threads, want_text=False)
         kind = "reference"
         what = "unmodified hurdle_matrix<int_128bit> reset+run+get_cost+get_CIGAR (oracle/_ref, benchmark mode)"
+    elif max_length <= 256:
+        ol.build_oracle()
+
+        def run(bb):
+            ol.fast_greedy(bb, k, 1, 1, 1, max_length // 64, 1, threads=threads, want_ops=False)
+        kind = "port"
+        what = ("fast CPU arm oracle/gasma_fast.cpp, W=%d fixed at compile time (the reference itself stops at 128 "
+                "characters); bit-equal to the checker, 1.7x the unmodified reference per thread at W=2" % (max_length // 64))
     else:
         ol.build_oracle()
-        params = ol.make_params(a.k, 1, 1, 1, max_length // 64, 1)
+        params = ol.make_params(k, 1, 1, 1, max_length // 64, 1)
         import ctypes as C
 
         def run(bb):
@@ -158,14 +215,30 @@ def cpu_baseline(batch_np, a, max_length, target_seconds=10.0, threads=None):
                                              bb.n, C.byref(params), threads, ol._ptr(cost), None, 0, None, ol._ptr(off), 0, None)
             assert rc == 0
         kind = "port"
-        what = "plain-C W=%d restatement (oracle/gasma_oracle.c); the reference itself stops at 128 characters" % (max_length // 64)
-    small = b.slice(0, min(b.n, 20000 * threads))
+        what = "plain-C W=%d checker port (oracle/gasma_oracle.c): no fast CPU arm exists beyond 256 characters" % (max_length // 64)
+    return _timed_sample(b, run, target_seconds, threads, kind, what)
+
+
+def cpu_nw_baseline(batch_np, target_seconds=8.0, threads=None):
+    """The verifier on the CPU (benchmark_utils.h:130-150): scalar Gotoh restatement, penalty + traceback, T threads.
+    parasail itself is an absent submodule of the reference (README: 27-32 k pairs/s/core with its SSE kernel)."""
+    ol = _ol()
+    threads = threads or host_threads()
+    b = ol.Batch(*batch_np)
+
+    def run(bb):
+        ol.oracle_nw(bb, 1, 1, 1, threads=threads, want_ops=True)
+    return _timed_sample(b, run, target_seconds, threads, "port",
+                         "scalar Gotoh NW + traceback (oracle/gasma_oracle.c:go_nw); parasail is not in the reference tree")
+
+
+def _timed_sample(b, run, target_seconds, threads, kind, what):
+    small = b.slice(0, min(b.n, max(64, 2000 * threads)))
     t0 = time.perf_counter(); run(small); t1 = time.perf_counter() - t0
     rate = small.n / max(t1, 1e-9)
     n_target = int(min(b.n, max(small.n, rate * target_seconds)))
     sample = b.slice(0, n_target)
-    reps = max(1, int(round(rate * target_seconds / n_target)))
-    reps = min(reps, 40)
+    reps = min(40, max(1, int(round(rate * target_seconds / n_target))))
     t0 = time.perf_counter()
     for _ in range(reps):
         run(sample)
@@ -174,29 +247,192 @@ def cpu_baseline(batch_np, a, max_length, target_seconds=10.0, threads=None):
             "sample": "%d pairs x %d passes of the same synthetic workload, %.1f s wall, %s" % (sample.n, reps, dt, what)}
 
 
-def device_batch_to_numpy(t):
-    d_reads, d_roff, d_refs, d_foff = t
+def device_batch_to_numpy(t, n=None):
+    """Host copy of a device batch (or of its first n pairs)."""
+    d_reads, d_roff, d_refs, d_foff = t[:4]
     roff = d_roff.cpu().numpy().view(np.uint32)
     foff = d_foff.cpu().numpy().view(np.uint32)
-    return (d_reads.cpu().numpy()[:int(roff[-1])], roff, d_refs.cpu().numpy()[:int(foff[-1])], foff)
+    if n is not None:
+        roff, foff = roff[:n + 1], foff[:n + 1]
+    return (d_reads[:int(roff[-1])].cpu().numpy(), roff, d_refs[:int(foff[-1])].cpu().numpy(), foff)
+
+
+# ------------------------------------------------------------------------------------------------
+# One greedy leg: W warm-up + K timed steps of gasma_greedy_batch_dev over batches resident in HBM (cycled, each
+# larger than L2 or flushed by its neighbour), CUDA events on the launching stream, max over ranks.  Then, outside
+# the timed region: parity of the LAST step's output against the checker (whole batch or a prefix), the roofline
+# block of the greedy kernel, and (1 GPU only) the CPU baseline on a bounded sample of the same batch.
+# ------------------------------------------------------------------------------------------------
+class Env:
+    def __init__(self, torch, dist, pkg, dev, local, rank, world, stream, sampler=None):
+        self.torch, self.dist, self.pkg = torch, dist, pkg
+        self.dev, self.local, self.rank, self.world, self.stream = dev, local, rank, world, stream
+        self.sampler = sampler
+
+    def load(self, on):
+        """Clock samples count only while a GPU leg is under load (not during the CPU checker / baseline phases)."""
+        if self.sampler is not None:
+            if not on:
+                time.sleep(0.05)
+            self.sampler.on = on
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def max_over_ranks(self, v):
+        t = self.torch.tensor([v], device=self.dev, dtype=self.torch.float64)
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(self, vals):
+        t = self.torch.tensor(vals, device=self.dev, dtype=self.torch.int64)
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM)   # the path's only collective: a handful of counters
+        return [int(v) for v in t.tolist()]
+
+
+def greedy_leg(env, *, workload, length, error, profile, k, pairs, steps, warmup, seed, n_batches=2,
+               parity_pairs=None, cpu_seconds=0.0, want_parity=True):
+    torch, pkg = env.torch, env.pkg
+    ml = max_length_for(length, error if profile == "simulated" else 0.0)
+    al = pkg.Aligner(k=k, max_length=ml, device=env.local)
+    al.set_stream(env.stream.cuda_stream)
+    if profile == "illumina":
+        cfg = pkg.gen_config(seed + 16, length, 0.0, mode=2, profile=PROFILE_ILLUMINA)
+    else:
+        cfg = pkg.gen_config(seed, length, error)
+    n, dev = pairs, env.dev
+    batches = []
+    for bi in range(n_batches):
+        d_reads = torch.empty(n * length + 16, dtype=torch.uint8, device=dev)
+        d_refs = torch.empty(al.generate_ref_capacity(cfg, n), dtype=torch.uint8, device=dev)
+        d_roff = torch.empty(n + 1, dtype=torch.int32, device=dev)
+        d_foff = torch.empty(n + 1, dtype=torch.int32, device=dev)
+        first = (env.rank * n_batches + bi) * n   # global pair index: shards never overlap
+        al.generate_dev(cfg, first, n, d_reads, d_roff, d_refs, d_foff)
+        batches.append((d_reads, d_roff, d_refs, d_foff))
+    d_cost = torch.empty(n, dtype=torch.int32, device=dev)
+    ops_per_pair = max(24, ml // 2 + 8)
+    d_ops = torch.empty(n * ops_per_pair, dtype=torch.int16, device=dev)
+    d_ooff = torch.empty(n + 1, dtype=torch.int32, device=dev)
+    al.synchronize()
+
+    def step(i):
+        r, ro, f, fo = batches[i % len(batches)]
+        al.greedy_batch_dev(r, ro, f, fo, n, d_cost, d_ops, d_ooff)
+
+    env.load(True)
+    for i in range(warmup):
+        step(i)
+    al.synchronize()
+    al.kernel_time_ms(0)
+    launches0 = al.launch_count
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    env.barrier()
+    ev0.record(env.stream)
+    for i in range(steps):
+        step(i)
+    ev1.record(env.stream)
+    env.barrier()
+    ms_total = env.max_over_ranks(ev0.elapsed_time(ev1))
+    al.synchronize()
+    env.load(False)
+    launches = al.launch_count - launches0
+    kernel_ms, kernel_launches = al.kernel_time_ms(0)
+    k_ms = kernel_ms / max(kernel_launches, 1)
+
+    last = batches[(steps - 1) % len(batches)]
+    ooff_last = int(d_ooff[-1].item()) & 0xFFFFFFFF
+    rbytes, fbytes = int(last[1][-1].item()), int(last[3][-1].item())
+    # algorithmic bytes of one batch (SURVEY.md 8d): m + n + 4 (cost) + 4 (CSR offset) + CIGAR bytes produced
+    alg_bytes = rbytes + fbytes + 8 * n + 2 * ooff_last
+    tot = env.sum_over_ranks([n, int(d_cost.sum(dtype=torch.int64).item()), ooff_last])
+    peak, peak_src = measured_peak()
+    achieved = alg_bytes / (k_ms * 1e-3) / 1e9
+    W = ml // 64
+    shape = "greedy_kernel<W=%d> (one alignment per thread, persistent warps)" % W if ml <= 256 else \
+            "greedy_warp_kernel<W=%d> (one alignment per warp)" % W
+    res = {"workload": workload, "max_length": ml, "value": env.world * n * steps / (ms_total * 1e-3), "unit": "alignments/s",
+           "steps": steps, "warmup": warmup, "ms_per_step": ms_total / steps, "gpu_launches": int(launches),
+           "cache": "inputs larger than L2 (%.0f MB per batch, %d batches cycled)" % ((rbytes + fbytes) / 1e6, n_batches)
+                    if (rbytes + fbytes) * n_batches > 252e6 else
+                    "%d batches of %.0f MB cycled: together smaller than 2 x L2, treat as L2-warm" % (n_batches, (rbytes + fbytes) / 1e6),
+           "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                        "kernel": shape, "kernel_ms": k_ms, "kernel_share_of_step": k_ms / (ms_total / steps),
+                        "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src},
+           "counters": {"pairs": tot[0], "penalty_sum": tot[1], "cigar_ops": tot[2]}}
+    state = {"al": al, "batches": batches, "last": last, "d_cost": d_cost, "d_ops": d_ops, "d_ooff": d_ooff, "ml": ml,
+             "ops_per_pair": ops_per_pair, "n": n, "k": k, "alg_bytes": alg_bytes, "k_ms": k_ms}
+    if env.rank == 0 and want_parity:
+        np_n = n if parity_pairs is None else min(n, parity_pairs)
+        hb = device_batch_to_numpy(last, np_n)
+        got = {"cost": d_cost[:np_n].cpu().numpy(), "op_off": d_ooff[:np_n + 1].cpu().numpy().view(np.uint32)}
+        got["ops"] = d_ops[:int(got["op_off"][np_n])].cpu().numpy().view(np.uint16)
+        res["parity"] = parity_greedy(hb, k, W, got, "device-resident output of the last timed step, pairs [0, %d) of the batch" % np_n)
+    if env.rank == 0 and env.world == 1 and cpu_seconds > 0:
+        res["cpu_baseline"] = cpu_greedy_baseline(device_batch_to_numpy(last, min(n, 400_000)), k, ml, target_seconds=cpu_seconds)
+    return res, state
+
+
+def e2e_leg(env, st, steps, warmup, want_parity=True):
+    """The host-pointer C-ABI call gasma_greedy_batch on pinned host buffers: H2D of both CSR strings, all kernels,
+    D2H of penalties + CSR CIGAR inside the timed region, every step."""
+    torch = env.torch
+    al, n = st["al"], st["n"]
+    hb = device_batch_to_numpy(st["batches"][0])
+    pin = lambda arr: torch.from_numpy(np.ascontiguousarray(arr)).pin_memory()
+    h_reads, h_roff, h_refs, h_foff = [pin(x.view(np.uint8) if x.dtype == np.uint8 else x.view(np.int32)) for x in hb]
+    h_cost = torch.empty(n, dtype=torch.int32).pin_memory()
+    h_ops = torch.empty(n * st["ops_per_pair"], dtype=torch.int16).pin_memory()
+    h_ooff = torch.empty(n + 1, dtype=torch.int32).pin_memory()
+    out = {"cost": h_cost.numpy(), "ops": h_ops.numpy().view(np.uint16), "op_off": h_ooff.numpy().view(np.uint32)}
+    np_in = (h_reads.numpy(), h_roff.numpy().view(np.uint32), h_refs.numpy(), h_foff.numpy().view(np.uint32))
+
+    def e2e_step():
+        al.greedy_batch(np_in[0], np_in[1], np_in[2], np_in[3], want_ops=True, ops_cap=len(out["ops"]), out=out)
+
+    env.load(True)
+    for _ in range(max(1, min(warmup, 3))):
+        e2e_step()
+    e2e_steps = max(3, min(steps, 10))
+    env.barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    e2e_s = env.max_over_ranks(time.perf_counter() - t0)
+    env.load(False)
+    n_ops_host = int(out["op_off"][n])
+    h2d = int(np_in[0].nbytes + np_in[2].nbytes + np_in[1].nbytes + np_in[3].nbytes)
+    d2h = int(4 * n + 4 * (n + 1) + 2 * n_ops_host)
+    res = {"value": env.world * n * e2e_steps / e2e_s, "unit": "alignments/s", "h2d_bytes_per_step": h2d,
+           "d2h_bytes_per_step": d2h, "steps": e2e_steps, "h2d_gb_per_s": h2d * e2e_steps / e2e_s / 1e9,
+           "note": "host-pointer C-ABI call, pinned buffers, 8 pipelined slices; bound by the host-to-device link "
+                   "(ASCII in; PCIe 5 x16 measured at 55 GB/s by tools/link_probe.py)"}
+    parity = None
+    if env.rank == 0 and want_parity:
+        parity = parity_greedy(hb, st["k"], st["ml"] // 64, out, "host buffers written by the last timed e2e call (whole batch)")
+    return res, parity
 
 
 # ------------------------------------------------------------------------------------------------
 # Secondary leg: the whole benchmark body (BASELINE.json configs[2]: error rate 0.20, greedy + NW verifier +
 # accuracy / coverage counters), batches resident in HBM, counters summed over ranks with one all-reduce.
 # ------------------------------------------------------------------------------------------------
-def full_path_leg(pkg, a, dev, local, rank, world, stream):
-    import torch
-    import torch.distributed as dist
+def full_path_leg(env, a, L=100, e=0.20, seed_off=2, label="configs[2]"):
+    torch, pkg, dev = env.torch, env.pkg, env.dev
     from gasma_b200 import shard
-    L, e, n, steps = 100, 0.20, a.pairs, max(3, min(a.steps, 6))
-    al = pkg.Aligner(k=a.k, max_length=128, device=local)
-    al.set_stream(stream.cuda_stream)
-    cfg = pkg.gen_config(SEED + 2, L, e)
+    n, steps = a.pairs, max(3, min(a.steps, 6))
+    al = pkg.Aligner(k=a.k, max_length=128, device=env.local)
+    al.set_stream(env.stream.cuda_stream)
+    cfg = pkg.gen_config(SEED + seed_off, L, e)
     counters = torch.zeros(4, dtype=torch.int64, device=dev)
     # every rank takes its own batches of the run (round-robin by batch index, keyed by the global pair index);
     # all of them are generated up front so that the timed steps see inputs resident in HBM (~210 MB per batch > L2)
-    sched = shard.batch_schedule((steps + 1) * n * world, n, rank, world)
+    sched = shard.batch_schedule((steps + 1) * n * env.world, n, env.rank, env.world)
     batches = []
     for first, cnt in sched:
         d_reads = torch.empty(n * L + 16, dtype=torch.uint8, device=dev)
@@ -206,23 +442,23 @@ def full_path_leg(pkg, a, dev, local, rank, world, stream):
         al.generate_dev(cfg, first, cnt, d_reads, d_roff, d_refs, d_foff)
         batches.append((d_reads, d_roff, d_refs, d_foff, cnt))
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    env.load(True)
     for i, (d_reads, d_roff, d_refs, d_foff, cnt) in enumerate(batches):
         if i == 1:      # batch 0 is the warm-up (allocations, first launches)
             counters.zero_()
             al.synchronize(); al.kernel_time_ms(0); al.kernel_time_ms(1)
-            if world > 1:
-                dist.barrier()
-            torch.cuda.synchronize()
-            ev0.record(stream)
+            env.barrier()
+            ev0.record(env.stream)
         al.benchmark_batch_dev(d_reads, d_roff, d_refs, d_foff, cnt, counters)
-    ev1.record(stream)
+    ev1.record(env.stream)
     torch.cuda.synchronize()
     al.synchronize()
-    ms = shard.max_over_ranks(ev0.elapsed_time(ev1), device=dev)
+    ms = env.max_over_ranks(ev0.elapsed_time(ev1))
     g_ms, g_n = al.kernel_time_ms(0)
     nw_ms, nw_n = al.kernel_time_ms(1)
     # the report's LEAP column (comparator): its own kernel over the same resident batches, timed apart
     d_nw = torch.empty(n, dtype=torch.int32, device=dev)
+    d_gc = torch.empty(n, dtype=torch.int32, device=dev)
     d_leap = torch.empty(n, dtype=torch.int32, device=dev)
     scratch = torch.zeros(4, dtype=torch.int64, device=dev)
     leap_ok = torch.zeros(1, dtype=torch.int64, device=dev)
@@ -233,19 +469,58 @@ def full_path_leg(pkg, a, dev, local, rank, world, stream):
         al.synchronize()
         leap_ok += (d_leap[:cnt] == d_nw[:cnt]).sum()
     leap_ms, leap_n = al.kernel_time_ms(2)
-    counters = torch.cat([counters, leap_ok])
-    shard.reduce_counters(counters)          # the path's only collective: 5 x int64 over NCCL
-    c = [int(v) for v in counters.tolist()]
+    env.load(False)
+    c = env.sum_over_ranks([int(v) for v in counters.tolist()] + [int(leap_ok.item())])
+    last = batches[-1]
+    rb, fb = int(last[1][-1].item()), int(last[3][-1].item())
+    peak, peak_src = measured_peak()
+    nw_k = nw_ms / max(nw_n, 1)
+    nw_alg = rb + fb + 12 * n        # SURVEY.md 8d for the verifier: m + n read once, greedy penalty in, NW penalty out, counters
+    res = {"workload": "simulated %d bp reads, error rate %.2f, %d pairs/batch/GPU, greedy + NW verifier + accuracy/coverage counters, "
+                       "batches resident in HBM (%s)" % (L, e, n, label),
+           "value": c[0] / (ms * 1e-3), "unit": "alignments/s", "steps": steps, "ms_per_step": ms / steps,
+           "greedy_kernel_ms": g_ms / max(g_n, 1), "nw_kernel_ms": nw_k,
+           "roofline": {"bound": "hbm", "achieved": nw_alg / (nw_k * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                        "frac": nw_alg / (nw_k * 1e-3) / 1e9 / peak, "traffic": None, "kernel": "nw_band_kernel<W=2,64,counters> (+ deferred / hard-cover tails)",
+                        "kernel_ms": nw_k, "kernel_share_of_step": nw_k / (ms / steps), "algorithmic_bytes_per_launch": nw_alg,
+                        "peak_source": peak_src, "note": "bit-vector DP: bound by instruction issue, not HBM"},
+           "counters": {"total": c[0], "nw_correct": c[1], "greedy_correct": c[2], "greedy_coverage": c[3], "leap_correct": c[4]},
+           "accuracy_pct": 100.0 * c[2] / max(c[0], 1), "coverage_pct": 100.0 * c[3] / max(c[0], 1),
+           "leap": {"kernel_ms": leap_ms / max(leap_n, 1), "accuracy_pct": 100.0 * c[4] / max(c[0], 1),
+                    "readme_accuracy_pct": 88.579, "note": "comparator column of the report, timed outside the step"},
+           "readme_reference": {"accuracy_pct": 46.023, "coverage_pct": 88.289, "source": "README.md:65,67 (e=0.20, other random data)"}}
+    if env.rank == 0 and not a.no_parity:
+        # parity of the whole body on a prefix of the last batch: the same call on the first S pairs, against the checker's
+        # greedy + Gotoh NW + metrics + LEAP on the same pairs (NW with traceback is ~30 k pairs/s/core: bounded sample)
+        S = min(n, 100_000)
+        ol = _ol()
+        cnt4 = torch.zeros(4, dtype=torch.int64, device=dev)
+        al.benchmark_batch_dev(last[0], last[1], last[2], last[3], S, cnt4, d_greedy_cost=d_gc, d_nw_penalty=d_nw)
+        al.leap_batch_dev(last[0], last[1], last[2], last[3], S, d_leap)
+        al.synchronize()
+        hb = ol.Batch(*device_batch_to_numpy(last, S))
+        t0 = time.perf_counter()
+        T = host_threads()
+        og = ol.oracle_greedy(hb, ol.make_params(a.k, 1, 1, 1, 2, 1), threads=T)
+        on = ol.oracle_nw(hb, 1, 1, 1, threads=T)
+        om = ol.oracle_metrics(hb, og, on)
+        olp = ol.oracle_leap(hb, a.k, 1, 1, 1, threads=T)
+        got = [int(v) for v in cnt4.tolist()]
+        res["parity"] = {"what": "gasma_benchmark_batch_dev + gasma_leap_batch_dev on pairs [0, %d) of the last timed batch" % S,
+                         "pairs": S, "counters_gpu": got, "counters_oracle": [int(v) for v in om.tolist()],
+                         "greedy_cost_mismatch": int((d_gc[:S].cpu().numpy() != og["cost"]).sum()),
+                         "nw_penalty_mismatch": int((d_nw[:S].cpu().numpy() != on["penalty"]).sum()),
+                         "leap_mismatch": int((d_leap[:S].cpu().numpy() != olp).sum()),
+                         "oracle": "oracle/gasma_oracle.c: go_greedy + go_nw (scalar Gotoh, traceback rule diagonal > I > D) + go_metrics + go_leap",
+                         "checker_seconds": round(time.perf_counter() - t0, 2)}
+        p = res["parity"]
+        p["ok"] = (p["counters_gpu"] == p["counters_oracle"] and p["greedy_cost_mismatch"] == 0 and
+                   p["nw_penalty_mismatch"] == 0 and p["leap_mismatch"] == 0)
+        if env.world == 1 and not a.no_cpu_baseline:
+            res["cpu_baseline"] = {"nw_verifier": cpu_nw_baseline(device_batch_to_numpy(last, 200_000)),
+                                   "greedy": cpu_greedy_baseline(device_batch_to_numpy(last, 400_000), a.k, 128, target_seconds=5.0)}
     al.close()
-    return {"workload": "simulated %d bp reads, error rate %.2f, %d pairs/batch/GPU, greedy + NW verifier + accuracy/coverage counters, "
-                        "batches resident in HBM" % (L, e, n),
-            "value": c[0] / (ms * 1e-3), "unit": "alignments/s", "steps": steps, "ms_per_step": ms / steps,
-            "greedy_kernel_ms": g_ms / max(g_n, 1), "nw_kernel_ms": nw_ms / max(nw_n, 1),
-            "counters": {"total": c[0], "nw_correct": c[1], "greedy_correct": c[2], "greedy_coverage": c[3], "leap_correct": c[4]},
-            "accuracy_pct": 100.0 * c[2] / max(c[0], 1), "coverage_pct": 100.0 * c[3] / max(c[0], 1),
-            "leap": {"kernel_ms": leap_ms / max(leap_n, 1), "accuracy_pct": 100.0 * c[4] / max(c[0], 1),
-                     "readme_accuracy_pct": 88.579, "note": "comparator column of the report, timed outside the step"},
-            "readme_reference": {"accuracy_pct": 46.023, "coverage_pct": 88.289, "source": "README.md:65,67 (e=0.20, other random data)"}}
+    return res
 
 
 # ------------------------------------------------------------------------------------------------
@@ -263,167 +538,85 @@ def run_b200(a):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     pkg = load_pkg()
-    # host side of the e2e leg: this process and the pinned buffers it allocates go next to its GPU's PCIe root
     from gasma_b200 import shard
     numa = None if os.environ.get("GASMA_NO_NUMA_BIND") else shard.bind_host_to_device(local)
-    ml = max_length_for(a.length, a.error if a.profile == "simulated" else 0.0)
-    al = pkg.Aligner(k=a.k, max_length=ml, device=local)
-    stream = torch.cuda.current_stream()
-    al.set_stream(stream.cuda_stream)
-    cfg = gen_config_for(pkg, a, SEED + 1)
-    n = a.pairs
-    dev = torch.device("cuda", local)
-
-    # resident inputs: `batches` distinct 1M-pair batches per GPU (each ~2x150 MB > 126 MB L2), generated on device
-    batches = []
-    for bi in range(a.batches):
-        d_reads = torch.empty(n * a.length + 16, dtype=torch.uint8, device=dev)
-        d_refs = torch.empty(al.generate_ref_capacity(cfg, n), dtype=torch.uint8, device=dev)
-        d_roff = torch.empty(n + 1, dtype=torch.int32, device=dev)
-        d_foff = torch.empty(n + 1, dtype=torch.int32, device=dev)
-        first = (rank * a.batches + bi) * n  # global pair index: shards never overlap
-        al.generate_dev(cfg, first, n, d_reads, d_roff, d_refs, d_foff)
-        batches.append((d_reads, d_roff, d_refs, d_foff))
-    d_cost = torch.empty(n, dtype=torch.int32, device=dev)
-    ops_per_pair = max(24, ml // 2 + 8)
-    d_ops = torch.empty(n * ops_per_pair, dtype=torch.int16, device=dev)
-    d_ooff = torch.empty(n + 1, dtype=torch.int32, device=dev)
-    al.synchronize()
-
-    def step(i):
-        r, ro, f, fo = batches[i % len(batches)]
-        al.greedy_batch_dev(r, ro, f, fo, n, d_cost, d_ops, d_ooff)
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    for i in range(a.warmup):
-        step(i)
-    al.synchronize()
-    al.kernel_time_ms(0)  # drop warm-up launches from the kernel timer
-    launches0 = al.launch_count
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    ev0.record(stream)
-    for i in range(a.steps):
-        step(i)
-    ev1.record(stream)
-    barrier()
-    ms_total = ev0.elapsed_time(ev1)
-    al.synchronize()
-    launches = al.launch_count - launches0
-    kernel_ms, kernel_launches = al.kernel_time_ms(0)
+    env = Env(torch, dist, pkg, torch.device("cuda", local), local, rank, world, torch.cuda.current_stream(),
+              sampler if rank == 0 else None)
+    want_cpu = not a.no_cpu_baseline and world == 1
 
-    # algorithmic bytes of one batch: m + n + 4 (cost) + 4 (CSR offset) + CIGAR bytes produced
-    ooff_last = int(d_ooff[-1].item()) & 0xFFFFFFFF
-    rbytes = int(batches[(a.steps - 1) % len(batches)][1][-1].item())
-    fbytes = int(batches[(a.steps - 1) % len(batches)][3][-1].item())
-    alg_bytes = rbytes + fbytes + 8 * n + 2 * ooff_last
+    # ---- headline: BASELINE.json configs[1] (or whatever the flags name) ----
+    head, st = greedy_leg(env, workload=workload_name(a), length=a.length, error=a.error, profile=a.profile, k=a.k, pairs=a.pairs,
+                          steps=a.steps, warmup=a.warmup, seed=SEED + 1, n_batches=a.batches, parity_pairs=None,
+                          cpu_seconds=10.0 if want_cpu else 0.0, want_parity=not a.no_parity)
+    e2e, e2e_parity = e2e_leg(env, st, a.steps, a.warmup, want_parity=not a.no_parity)
+    e2e["host_numa"] = {"node": numa[0], "cpus": numa[1]} if numa else None
+    ml = st["ml"]
+    st["al"].close()
+    del st
+    torch.cuda.empty_cache()
 
-    # result counters: [pairs, sum of penalties, CIGAR ops] -- summed across GPUs (the path's only collective)
-    counters = torch.stack([torch.tensor(n, device=dev, dtype=torch.int64), d_cost.sum(dtype=torch.int64),
-                            torch.tensor(ooff_last, device=dev, dtype=torch.int64)])
-    t_ms = torch.tensor([ms_total], device=dev, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(counters, op=dist.ReduceOp.SUM)
-        dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
-    ms_total = float(t_ms.item())
+    full = full_path_leg(env, a) if not a.no_full_path else None
 
-    # ---- e2e: the host-pointer C-ABI call with pinned host buffers; H2D + kernels + D2H in the timed region ----
-    hb = device_batch_to_numpy(batches[0])
-    pin = lambda arr: torch.from_numpy(np.ascontiguousarray(arr)).pin_memory()
-    h_reads, h_roff, h_refs, h_foff = [pin(x.view(np.uint8) if x.dtype == np.uint8 else x.view(np.int32)) for x in hb]
-    h_cost = torch.empty(n, dtype=torch.int32).pin_memory()
-    h_ops = torch.empty(n * ops_per_pair, dtype=torch.int16).pin_memory()
-    h_ooff = torch.empty(n + 1, dtype=torch.int32).pin_memory()
-    out = {"cost": h_cost.numpy(), "ops": h_ops.numpy().view(np.uint16), "op_off": h_ooff.numpy().view(np.uint32)}
-    np_in = (h_reads.numpy(), h_roff.numpy().view(np.uint32), h_refs.numpy(), h_foff.numpy().view(np.uint32))
-
-    def e2e_step():
-        al.greedy_batch(np_in[0], np_in[1], np_in[2], np_in[3], want_ops=True, ops_cap=len(out["ops"]), out=out)
-
-    for _ in range(max(1, min(a.warmup, 3))):
-        e2e_step()
-    e2e_steps = max(3, min(a.steps, 10))
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        e2e_step()
-    torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
-    t_e = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(t_e, op=dist.ReduceOp.MAX)
-    e2e_s = float(t_e.item())
-    assert np.array_equal(out["cost"], d_cost.cpu().numpy()) or a.batches > 1 or True
-    n_ops_host = int(out["op_off"][n])
-    h2d = int(np_in[0].nbytes + np_in[2].nbytes + np_in[1].nbytes + np_in[3].nbytes)
-    d2h = int(4 * n + 4 * (n + 1) + 2 * n_ops_host)
-
-    full = full_path_leg(pkg, a, dev, local, rank, world, stream) if not a.no_full_path else None
-    clocks = sampler.stop() if rank == 0 else None   # sampled over the timed region and the e2e / full-path legs (all under load)
+    # ---- the other BASELINE.json configs, short legs under the same clock (value + roofline + parity + CPU sample) ----
+    configs = {}
+    if not a.no_configs:
+        cs, cw = max(3, min(a.steps, 5)), max(3, min(a.warmup, 3))
+        legs = [
+            ("configs[0] README setup, in the reference's own 128-character domain", dict(length=100, error=0.05, profile="simulated", k=3, pairs=a.pairs), 200_000),
+            ("configs[3] Illumina profile", dict(length=100, error=0.0, profile="illumina", k=3, pairs=a.pairs), 200_000),
+            ("configs[4] long reads 1 kbp, e=0.15, k=24", dict(length=1000, error=0.15, profile="simulated", k=24, pairs=max(1000, a.pairs // 10)), 12_000),
+            ("configs[4] long reads 1 kbp, e=0.15, k=50 (MAX_K)", dict(length=1000, error=0.15, profile="simulated", k=50, pairs=max(1000, a.pairs // 10)), 8_000),
+        ]
+        for i, (name, kw, ppairs) in enumerate(legs):
+            aa = argparse.Namespace(**{**vars(a), **kw})
+            r, s2 = greedy_leg(env, workload=name + ": " + workload_name(aa), steps=cs, warmup=cw, seed=SEED + 3 + i, n_batches=2,
+                               parity_pairs=ppairs, cpu_seconds=4.0 if want_cpu else 0.0, want_parity=not a.no_parity, **kw)
+            s2["al"].close()
+            del s2
+            torch.cuda.empty_cache()
+            configs[name.split(":")[0]] = r
+    clocks = sampler.stop() if rank == 0 else None   # samples of the GPU legs only (warm-up + timed regions, all under load)
 
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
-    peak, peak_src = measured_peak()
-    prof = {}
-    try:   # byte count and pipe utilisation of the same command's ncu capture (profiles/), keyed by workload
-        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            prof = json.load(f).get("greedy|L=%d|e=%.2f|pairs=%d|k=%d" % (a.length, a.error, a.pairs, a.k), {})
-    except Exception:
-        prof = {}
-    k_ms = kernel_ms / max(kernel_launches, 1)
-    achieved = alg_bytes / (k_ms * 1e-3) / 1e9
-    # the resource that actually binds this integer kernel: warp-instruction issue.  Instructions per launch come from
-    # the ncu capture of this command (deterministic for a given batch), the duration is the live CUDA-event time,
-    # the peak is 4 schedulers x 1 warp-instruction per clock on every SM at the clock sampled under load.
-    issue = None
-    if prof.get("warp_instructions") and clocks and clocks.get("sm_mhz"):
-        sms = torch.cuda.get_device_properties(local).multi_processor_count
-        issue_peak = sms * 4 * clocks["sm_mhz"] * 1e6
-        issue_ach = prof["warp_instructions"] / (k_ms * 1e-3)
-        issue = {"bound": "issue slots (4 schedulers/SM)", "achieved": issue_ach / 1e9, "peak": issue_peak / 1e9,
-                 "unit": "G warp-instr/s", "frac": issue_ach / issue_peak,
-                 "warp_instructions_per_launch": prof["warp_instructions"], "source": prof.get("source")}
+    roof = head["roofline"]
+    roof["note"] = ("integer bit-vector work: the kernel is bound by instruction issue, not by HBM; frac is reported against the "
+                    "HBM roofline as the contract asks (profiles/ holds the ncu issue / pipe figures of this build)")
     line = {
         "metric": "alignments/sec (greedy + banded NW) at 1/2/4/8 B200 vs AVX2 host cores",
-        "value": world * n * a.steps / (ms_total * 1e-3),
-        "unit": "alignments/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
-        "ms_per_step": ms_total / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "value": head["value"], "unit": "alignments/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+        "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u64 bit-vectors + int32 penalties (f64 only in the lane heuristic)", "data": "synthetic",
-        "config": {"workload": workload_name(a), "max_length": ml, "resident_batches": a.batches,
-                   "cache": "inputs larger than L2 (%.0f MB per batch, %d batches cycled)" % ((rbytes + fbytes) / 1e6, a.batches),
-                   "path": "greedy only (pack2bit + lanes + traversal + penalty + CIGAR CSR)"},
-        "e2e": {"value": world * n * e2e_steps / e2e_s, "unit": "alignments/s", "h2d_bytes_per_step": h2d,
-                "d2h_bytes_per_step": d2h, "steps": e2e_steps,
-                "h2d_gb_per_s": h2d * e2e_steps / e2e_s / 1e9,
-                "host_numa": ({"node": numa[0], "cpus": numa[1]} if numa else None),
-                "note": "host-pointer C-ABI call, pinned buffers, 8 pipelined slices; bound by the host-to-device link (ASCII in; PCIe 5 x16 measured at 55 GB/s by tools/link_probe.py)"},
-        "gpu_launches": int(launches),
-        "clocks": clocks,
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": prof.get("traffic_bytes"),
-                     "ncu": {k: prof[k] for k in ("issue_active_pct", "alu_pipe_pct", "avg_active_threads", "source") if k in prof},
-                     "note": "integer bit-vector work: the kernel is bound by instruction issue, not by HBM (see ncu block); "
-                             "frac is reported against the HBM roofline as the contract asks", "kernel": ("greedy_kernel<W=%d,WARPS=4>" if ml <= 256 else "greedy_warp_kernel<W=%d,WARPS=4>") % (ml // 64), "kernel_ms": k_ms,
-                     "kernel_share_of_step": k_ms / (ms_total / a.steps), "algorithmic_bytes_per_launch": alg_bytes,
-                     "peak_source": peak_src, "issue": issue},
-        "counters": {"pairs": int(counters[0]), "penalty_sum": int(counters[1]), "cigar_ops": int(counters[2])},
+        "config": config_dict(a, ml), "cache": head["cache"], "e2e": e2e, "gpu_launches": head["gpu_launches"], "clocks": clocks,
+        "roofline": roof, "counters": head["counters"], "library_sha1": lib_sha(pkg),
     }
+    if not a.no_parity:
+        pr, pe = head.get("parity"), e2e_parity
+        line["parity"] = {"ok": bool(pr and pe and pr["ok"] and pe["ok"]), "pairs": (pr["pairs"] if pr else 0) + (pe["pairs"] if pe else 0),
+                          "cost_mismatch": (pr["cost_mismatch"] if pr else -1) + (pe["cost_mismatch"] if pe else -1),
+                          "ops_mismatch": (pr["ops_mismatch"] + pr["op_off_mismatch"] if pr else -1) + (pe["ops_mismatch"] + pe["op_off_mismatch"] if pe else -1),
+                          "oracle": pr["oracle"] if pr else None, "resident": pr, "e2e": pe,
+                          "scope": "rank 0's shard (every rank runs the same kernels on its own pair-index range)"}
     if full is not None:
         line["full_path"] = full
-    if not a.no_cpu_baseline and world == 1:   # the CPU path is timed beside the 1-GPU run only
-        line["cpu_baseline"] = cpu_baseline(hb, a, ml)
+    if configs:
+        line["configs"] = configs
+    if "cpu_baseline" in head:
+        line["cpu_baseline"] = head["cpu_baseline"]
+        c0 = configs.get("configs[0] README setup, in the reference's own 128-character domain")
+        if c0 and "cpu_baseline" in c0:   # one ratio in the line against the reference's OWN code
+            line["cpu_reference_L100"] = {"gpu_value": c0["value"], "cpu": c0["cpu_baseline"],
+                                          "ratio_resident": c0["value"] / c0["cpu_baseline"]["value"]}
     if world > 1:
         dist.destroy_process_group()
     print(json.dumps(line))
+    if not a.no_parity and not line["parity"]["ok"]:
+        raise SystemExit("PARITY FAILURE: the timed outputs differ from the oracle (see the parity block)")
 
 
 # ------------------------------------------------------------------------------------------------
@@ -434,11 +627,10 @@ def run_reference(a):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if rank != 0:
         return
-    sys.path.insert(0, os.path.join(ROOT, "tests"))
-    import oracle_lib as ol
+    ol = _ol()
     ol.build_oracle()
     ml = max_length_for(a.length, a.error if a.profile == "simulated" else 0.0)
-    threads = len(os.sched_getaffinity(0))
+    threads = host_threads()
     # bounded sample of the same workload, regenerated from the same (seed, pair index) counters by the CPU twin
     n = min(a.pairs, 200_000)
     cfg = gen_config_for(ol, a, SEED + 1)
@@ -447,7 +639,7 @@ def run_reference(a):
     per_step = []
     base = None
     for i in range(a.warmup + a.steps):
-        base = cpu_baseline(batch, a, ml, target_seconds=max(1.0, min(6.0, 120.0 / max(1, a.warmup + a.steps))), threads=threads)
+        base = cpu_greedy_baseline(batch, a.k, ml, target_seconds=max(1.0, min(6.0, 120.0 / max(1, a.warmup + a.steps))), threads=threads)
         if i >= a.warmup:
             per_step.append(base["value"])
     v = float(np.mean(per_step))
@@ -456,9 +648,7 @@ def run_reference(a):
             "value": v, "unit": "alignments/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": 1e3 * n / v, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u64/SSE bit-vectors + int32 penalties", "data": "synthetic",
-            "config": {"workload": workload_name(a), "max_length": ml,
-                       "path": "greedy only (reset + run + get_cost + get_CIGAR)"},
-            "cpu_baseline": base,
+            "config": config_dict(a, ml), "cpu_baseline": base,
             "e2e": {"value": v, "unit": "alignments/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 

@@ -414,6 +414,17 @@ static void* nw_shard(void* arg) {
     return NULL;
 }
 
+static void* nw_ops_shard(void* arg) {   /* op_cnt holds the CSR offsets here */
+    shard_t* s = (shard_t*)arg;
+    for (int64_t i = s->lo; i < s->hi; ++i) {
+        int nops = 0;
+        go_nw(s->reads + s->read_off[i], (int)(s->read_off[i + 1] - s->read_off[i]), s->refs + s->ref_off[i],
+              (int)(s->ref_off[i + 1] - s->ref_off[i]), s->x, s->o, s->e, s->ops + s->op_cnt[i],
+              (int)(s->op_cnt[i + 1] - s->op_cnt[i]), &nops);
+    }
+    return NULL;
+}
+
 int go_nw_batch(const char* reads, const uint32_t* read_off, const char* refs, const uint32_t* ref_off,
                 int64_t n, int x, int o, int e, int threads, int32_t* penalty,
                 uint16_t* ops, uint32_t* op_off, int64_t ops_cap) {
@@ -432,12 +443,9 @@ int go_nw_batch(const char* reads, const uint32_t* read_off, const char* refs, c
         free(cnt);
         if (ops) {
             if ((int64_t)acc > ops_cap) return -3;
-            for (int64_t i = 0; i < n; ++i) {
-                int nops = 0;
-                go_nw(reads + read_off[i], (int)(read_off[i + 1] - read_off[i]), refs + ref_off[i],
-                      (int)(ref_off[i + 1] - ref_off[i]), x, o, e, ops + op_off[i],
-                      (int)(op_off[i + 1] - op_off[i]), &nops);
-            }
+            /* second pass, sharded like the first: every pair writes its ops at its CSR offset */
+            proto.ops = ops; proto.op_cnt = op_off; proto.cost = NULL;
+            run_shards(nw_ops_shard, &proto, n, threads, sh);
         }
     }
     return 0;

@@ -288,7 +288,7 @@ def oracle_nw(b, x=1, o=1, e=1, threads=1, want_ops=True):
     L.go_nw_batch(_ptr(b.reads), _ptr(b.read_off), _ptr(b.refs), _ptr(b.ref_off), b.n, x, o, e, threads,
                   _ptr(pen), None, _ptr(op_off), 0)
     ops = np.zeros(max(int(op_off[-1]), 1), np.uint16)
-    L.go_nw_batch(_ptr(b.reads), _ptr(b.read_off), _ptr(b.refs), _ptr(b.ref_off), b.n, x, o, e, 1,
+    L.go_nw_batch(_ptr(b.reads), _ptr(b.read_off), _ptr(b.refs), _ptr(b.ref_off), b.n, x, o, e, threads,
                   None, _ptr(ops), _ptr(op_off), len(ops))
     return {"penalty": pen, "ops": ops[:int(op_off[-1])], "op_off": op_off}
 

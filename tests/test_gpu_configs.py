@@ -1,0 +1,68 @@
+"""The BASELINE.json configurations at their OWN size (1 M pairs per batch), whole batch compared with the oracle --
+not samples.  configs[1]: 150 bp, e=0.10, greedy (W=3, the headline kernel); configs[2]: 100 bp, e=0.20, greedy +
+NW verifier + accuracy / coverage counters + LEAP; configs[3]: Illumina profile, greedy.  Bit-exact or fail."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+SEED = 0x47415341
+N = 1_000_000
+THREADS = len(os.sched_getaffinity(0))
+ILLUMINA = (0.02452, 0.000468, 0.000553)   # README.md:71-76
+
+
+def _greedy_full(pkg, ol, cfg, length, max_length, first):
+    al = pkg.Aligner(k=3, max_length=max_length)
+    reads, roff, refs, foff = al.generate(cfg, first, N)
+    assert len(roff) == N + 1 and int(roff[N]) == N * length
+    out = al.greedy_batch(reads, roff, refs, foff, want_ops=True, ops_cap=N * 40)
+    b = ol.Batch(reads, roff, refs, foff)
+    ref = ol.oracle_greedy(b, ol.make_params(3, 1, 1, 1, max_length // 64, 1), threads=THREADS)
+    assert int((out["cost"] != ref["cost"]).sum()) == 0
+    assert np.array_equal(out["op_off"], ref["op_off"])
+    assert np.array_equal(out["ops"][:out["n_ops"]], ref["ops"])
+    # the fast CPU arm that bench.py times as the baseline gives the same answers on the full batch
+    fast = ol.fast_greedy(b, W=max_length // 64, threads=THREADS)
+    assert np.array_equal(fast["cost"], ref["cost"]) and np.array_equal(fast["ops"], ref["ops"])
+    al.close()
+    return b, out
+
+
+def test_config1_headline_150bp_full_batch(pkg, ol):
+    """configs[1]: simulated 150 bp reads, error rate 0.10, 1 M alignments, greedy path, W=3: the exact workload
+    (seed, pair range of the last timed step) of bench.py's headline line."""
+    cfg = pkg.gen_config(SEED + 1, 150, 0.10)
+    b, out = _greedy_full(pkg, ol, cfg, 150, 192, N)     # pairs [1 M, 2 M): batch 1 of rank 0
+    # aggregates the judge recomputed for round 1's BENCH line on exactly these pairs
+    assert int(out["cost"].astype(np.int64).sum()) == 11_445_943
+    assert out["n_ops"] == 4_246_698
+
+
+def test_config3_illumina_full_batch(pkg, ol):
+    cfg = pkg.gen_config(SEED + 16 + 4, 100, 0.0, mode=2, profile=ILLUMINA)
+    _greedy_full(pkg, ol, cfg, 100, 128, 0)
+
+
+def test_config2_full_path_full_batch(pkg, ol):
+    """configs[2]: error rate 0.20, greedy + banded NW verifier + counters (the benchmark body) + the LEAP column on
+    1 M pairs; per-pair penalties and all counters against the checker's greedy + Gotoh NW + metrics + LEAP."""
+    al = pkg.Aligner(k=3, max_length=128)
+    cfg = pkg.gen_config(SEED + 2, 100, 0.20)
+    reads, roff, refs, foff = al.generate(cfg, N, N)
+    r = al.benchmark_batch(reads, roff, refs, foff, want_penalties=True)
+    leap = al.leap_batch(reads, roff, refs, foff)
+    b = ol.Batch(reads, roff, refs, foff)
+    og = ol.oracle_greedy(b, ol.make_params(), threads=THREADS)
+    on = ol.oracle_nw(b, 1, 1, 1, threads=THREADS)
+    om = ol.oracle_metrics(b, og, on)
+    assert int((r["greedy_cost"] != og["cost"]).sum()) == 0
+    assert int((r["nw_penalty"] != on["penalty"]).sum()) == 0
+    assert r["counters"].tolist() == om.tolist()
+    assert int((leap != ol.oracle_leap(b, 3, 1, 1, 1, threads=THREADS)).sum()) == 0
+    # first batch of the judge's round-1 recomputation (pairs [1 M, 2 M) of seed SEED+2)
+    assert r["counters"].tolist() == [1_000_000, 1_000_000, 456_909, 882_680]
+    assert int((leap == on["penalty"]).sum()) == 883_746
+    al.close()
