@@ -92,7 +92,7 @@ def workload_name(a):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+    """nvidia-smi clocks / throttle reasons sampled every 100 ms while the GPU legs run."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
@@ -105,7 +105,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._pump, daemon=True).start()
         except OSError:
@@ -233,16 +233,19 @@ def cpu_nw_baseline(batch_np, target_seconds=8.0, threads=None):
 
 
 def _timed_sample(b, run, target_seconds, threads, kind, what):
+    """Whole passes over a bounded sample of the batch until `target_seconds` of CPU work are done."""
     small = b.slice(0, min(b.n, max(64, 2000 * threads)))
+    run(small)                                   # warm-up: thread start, page faults, library load
     t0 = time.perf_counter(); run(small); t1 = time.perf_counter() - t0
     rate = small.n / max(t1, 1e-9)
-    n_target = int(min(b.n, max(small.n, rate * target_seconds)))
-    sample = b.slice(0, n_target)
-    reps = min(40, max(1, int(round(rate * target_seconds / n_target))))
-    t0 = time.perf_counter()
-    for _ in range(reps):
+    sample = b.slice(0, int(min(b.n, max(small.n, rate * target_seconds / 4))))
+    reps, t0 = 0, time.perf_counter()
+    while True:
         run(sample)
-    dt = time.perf_counter() - t0
+        reps += 1
+        dt = time.perf_counter() - t0
+        if dt >= target_seconds or reps >= 1000:
+            break
     return {"value": sample.n * reps / dt, "unit": "alignments/s", "cores": threads, "kind": kind,
             "sample": "%d pairs x %d passes of the same synthetic workload, %.1f s wall, %s" % (sample.n, reps, dt, what)}
 
@@ -305,6 +308,7 @@ def greedy_leg(env, *, workload, length, error, profile, k, pairs, steps, warmup
     else:
         cfg = pkg.gen_config(seed, length, error)
     n, dev = pairs, env.dev
+    env.load(True)      # generation, warm-up and the timed region all keep the GPU busy
     batches = []
     for bi in range(n_batches):
         d_reads = torch.empty(n * length + 16, dtype=torch.uint8, device=dev)
@@ -324,7 +328,6 @@ def greedy_leg(env, *, workload, length, error, profile, k, pairs, steps, warmup
         r, ro, f, fo = batches[i % len(batches)]
         al.greedy_batch_dev(r, ro, f, fo, n, d_cost, d_ops, d_ooff)
 
-    env.load(True)
     for i in range(warmup):
         step(i)
     al.synchronize()
