@@ -56,8 +56,14 @@ struct gasma_ctx {
     int64_t launches = 0;
     std::string err;
     // device scratch
-    DevBuf g_tile_sums;          // per-tile op counts of the greedy path: accumulated by the greedy kernel, zeroed again by the scan
-    DevBuf ops_stage, nops, tile_sums, tile_bases, misc;  // misc: [0] status u32, [1] total ops u32, [2..3] step counter u64
+    // per-tile op counts of the greedy path, two arrays used alternately: the greedy kernel of batch i accumulates into
+    // g_sums[i & 1], compact_rows_kernel of batch i reads it and zeroes the other one for batch i+1
+    DevBuf g_sums[2];
+    int g_dirty[2] = {0, 0};     // tiles of g_sums[q] that may be non-zero
+    int g_parity = 0;            // array the NEXT greedy launch uses
+    int base_parity = 0;         // misc[8 + base_parity] holds the running op total the next carry_ops step starts from
+    DevBuf ops_rows;             // greedy CIGAR staging: 32-byte primary row per pair (greedy.cuh:OpSink)
+    DevBuf ops_stage, nops, tile_sums, tile_bases, misc;  // misc: [0] status u32, [1] total ops u32, [2..3] step counter u64, [8..9] running op base (alternating)
     // device mirrors for the host-pointer entry points
     DevBuf d_reads, d_refs, d_read_off, d_ref_off, d_cost, d_ops, d_op_off, d_p0, d_p1;
     DevBuf gen_len, d_bound, nw_deferred, nw_tb, nw_pool_hi, nw_pool_tb;
@@ -142,7 +148,7 @@ int greedy_warps_for(int nl) {
 
 template <int W, int WARPS, bool CORR>
 int launch_greedy_t(gasma_ctx* ctx, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, const uint32_t* foff,
-                    int64_t n, int32_t* cost, uint16_t* stage, int stride, uint32_t* nops, uint32_t* chunk_counter,
+                    int64_t n, int32_t* cost, uint16_t* rows, uint16_t* stage, int stride, uint32_t* nops, uint32_t* chunk_counter,
                     uint32_t* status, unsigned long long* steps, uint32_t* tsums) {
     size_t smem = greedy_smem_bytes<W>(WARPS, ctx->kp.nl);
     if (const char* env = getenv("GASMA_SMEM_PAD")) smem += (size_t)atoi(env);   // occupancy experiments only
@@ -156,7 +162,7 @@ int launch_greedy_t(gasma_ctx* ctx, const uint8_t* reads, const uint32_t* roff, 
     int64_t grid = (int64_t)ctx->sm_count * per_sm;
     if (grid * WARPS > chunks) grid = (chunks + WARPS - 1) / WARPS;
     if (!ctx->counter_clean) CU(cudaMemsetAsync(chunk_counter, 0, 4, ctx->stream));
-    kern<<<(unsigned)grid, 32 * WARPS, smem, ctx->stream>>>(ctx->kp, reads, roff, refs, foff, (long long)n, cost, stage, stride,
+    kern<<<(unsigned)grid, 32 * WARPS, smem, ctx->stream>>>(ctx->kp, reads, roff, refs, foff, (long long)n, cost, rows, stage, stride,
                                                           nops, chunk_counter, ctx->refill_threshold, status, steps, tsums);
     CU(cudaGetLastError());
     ctx->launches++;
@@ -165,7 +171,7 @@ int launch_greedy_t(gasma_ctx* ctx, const uint8_t* reads, const uint32_t* roff, 
 
 template <int W>
 int launch_greedy_w(gasma_ctx* ctx, int warps, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs,
-                    const uint32_t* foff, int64_t n, int32_t* cost, uint16_t* stage, int stride, uint32_t* nops,
+                    const uint32_t* foff, int64_t n, int32_t* cost, uint16_t* rows, uint16_t* stage, int stride, uint32_t* nops,
                     uint32_t* chunk_counter, uint32_t* status, unsigned long long* steps, uint32_t* tsums) {
     if (!ctx->kp.correction && warps == 4) {
         // CTA shape: per-warp work is independent, so the shape only decides how many warps an SM holds (shared
@@ -192,16 +198,16 @@ int launch_greedy_w(gasma_ctx* ctx, int warps, const uint8_t* reads, const uint3
             }
             pick = ctx->auto_warps;
         }
-        if (pick == 2) return launch_greedy_t<W, 2, false>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, chunk_counter, status, steps, tsums);
+        if (pick == 2) return launch_greedy_t<W, 2, false>(ctx, reads, roff, refs, foff, n, cost, rows, stage, stride, nops, chunk_counter, status, steps, tsums);
         if (pick == 8 && greedy_smem_bytes<W>(8, ctx->kp.nl) <= kMaxSmem)
-            return launch_greedy_t<W, 8, false>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, chunk_counter, status, steps, tsums);
+            return launch_greedy_t<W, 8, false>(ctx, reads, roff, refs, foff, n, cost, rows, stage, stride, nops, chunk_counter, status, steps, tsums);
     }
     if (ctx->kp.correction) {
-        if (warps == 4) return launch_greedy_t<W, 4, true>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, chunk_counter, status, steps, tsums);
-        return launch_greedy_t<W, 1, true>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, chunk_counter, status, steps, tsums);
+        if (warps == 4) return launch_greedy_t<W, 4, true>(ctx, reads, roff, refs, foff, n, cost, rows, stage, stride, nops, chunk_counter, status, steps, tsums);
+        return launch_greedy_t<W, 1, true>(ctx, reads, roff, refs, foff, n, cost, rows, stage, stride, nops, chunk_counter, status, steps, tsums);
     }
-    if (warps == 4) return launch_greedy_t<W, 4, false>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, chunk_counter, status, steps, tsums);
-    return launch_greedy_t<W, 1, false>(ctx, reads, roff, refs, foff, n, cost, stage, stride, nops, chunk_counter, status, steps, tsums);
+    if (warps == 4) return launch_greedy_t<W, 4, false>(ctx, reads, roff, refs, foff, n, cost, rows, stage, stride, nops, chunk_counter, status, steps, tsums);
+    return launch_greedy_t<W, 1, false>(ctx, reads, roff, refs, foff, n, cost, rows, stage, stride, nops, chunk_counter, status, steps, tsums);
 }
 
 int greedy_tile_threads(const gasma_ctx* c) {   // 0 = configuration does not fit
@@ -218,7 +224,7 @@ int greedy_tile_threads(const gasma_ctx* c) {   // 0 = configuration does not fi
 // one alignment per warp (max_length 512 / 1024)
 template <int W>
 int launch_greedy_warp(gasma_ctx* ctx, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, const uint32_t* foff,
-                       int64_t n, int32_t* cost, uint16_t* stage, int stride, uint32_t* nops, uint32_t* pair_counter,
+                       int64_t n, int32_t* cost, uint16_t* rows, uint16_t* stage, int stride, uint32_t* nops, uint32_t* pair_counter,
                        uint32_t* status, unsigned long long* steps, uint32_t* tsums) {
     constexpr int WARPS = 4;
     const size_t smem = WARPS * ((WarpLayout<W>::bytes_per_warp(ctx->kp.nl) + 15) / 16 * 16);
@@ -230,7 +236,7 @@ int launch_greedy_warp(gasma_ctx* ctx, const uint8_t* reads, const uint32_t* rof
     int64_t grid = (int64_t)ctx->sm_count * per_sm;
     if (grid * WARPS > n) grid = (n + WARPS - 1) / WARPS;
     if (!ctx->counter_clean) CU(cudaMemsetAsync(pair_counter, 0, 4, ctx->stream));
-    kern<<<(unsigned)grid, 32 * WARPS, smem, ctx->stream>>>(ctx->kp, reads, roff, refs, foff, (long long)n, cost, stage, stride, nops,
+    kern<<<(unsigned)grid, 32 * WARPS, smem, ctx->stream>>>(ctx->kp, reads, roff, refs, foff, (long long)n, cost, rows, stage, stride, nops,
                                                           pair_counter, status, steps, tsums);
     CU(cudaGetLastError());
     ctx->launches++;
@@ -332,7 +338,7 @@ void gasma_destroy(gasma_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
-    DevBuf* bufs[] = {&c->g_tile_sums, &c->ops_stage, &c->nops, &c->tile_sums, &c->tile_bases, &c->misc, &c->d_reads, &c->d_refs,
+    DevBuf* bufs[] = {&c->g_sums[0], &c->g_sums[1], &c->ops_rows, &c->ops_stage, &c->nops, &c->tile_sums, &c->tile_bases, &c->misc, &c->d_reads, &c->d_refs,
                       &c->d_read_off, &c->d_ref_off, &c->d_cost, &c->d_ops, &c->d_op_off, &c->d_p0, &c->d_p1, &c->gen_len, &c->d_bound, &c->nw_deferred, &c->nw_tb, &c->nw_pool_hi, &c->nw_pool_tb,
                       &c->bm_hard, &c->bm_gops, &c->bm_goff, &c->bm_nops, &c->bm_noff, &c->bm_gcost, &c->bm_nwpen, &c->bm_counters, &c->bm_answers};
     for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
@@ -462,11 +468,17 @@ int launch_pack_w(gasma_ctx* ctx, const uint8_t* seqs, const uint32_t* off, int6
     return GASMA_OK;
 }
 
+// How the CIGAR ops leave a greedy step:
+//   d_ops == nullptr, rows_only == false   costs only
+//   d_ops != nullptr                       CSR: compact_rows_kernel writes d_ops / d_op_off
+//   rows_only                              left in the staging rows + ctx->nops (the benchmark body's verifier reads them there)
 // carry_ops: op_off continues from the running total left by the previous call (slices of one batch share one
 // CSR array); otherwise it starts at 0.
+constexpr int64_t kMaxCsrPairs = (int64_t)4096 * kCsrTile;   // pairs per compact_rows_kernel launch (a CTA adds up <= 4096 tile counts)
+
 int greedy_dev_impl(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_read_off, const char* d_refs,
                     const uint32_t* d_ref_off, int64_t n, int32_t* d_cost, gasma_cigar_op* d_ops, int64_t ops_cap,
-                    uint32_t* d_op_off, bool carry_ops = false) {
+                    uint32_t* d_op_off, bool carry_ops = false, bool rows_only = false) {
     if (!ctx) return GASMA_E_ARG;
     if (n < 0 || n > (int64_t)1 << 31) return fail(ctx, GASMA_E_ARG, "n_pairs out of range");
     if (!d_read_off || !d_ref_off || !d_cost) return fail(ctx, GASMA_E_ARG, "null offsets/cost pointer");
@@ -474,25 +486,43 @@ int greedy_dev_impl(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_read_
     if (!aligned16(d_reads) || !aligned16(d_refs)) return fail(ctx, GASMA_E_ARG, "sequence buffers must be 16-byte aligned");
     CU(cudaSetDevice(ctx->device));
     if (n == 0) {
-        if (d_op_off) CU(cudaMemsetAsync(d_op_off, 0, 4, ctx->stream));
+        if (d_op_off && !carry_ops) CU(cudaMemsetAsync(d_op_off, 0, 4, ctx->stream));
+        return GASMA_OK;
+    }
+    const bool want_csr = d_ops != nullptr;
+    if (want_csr && n > kMaxCsrPairs) {   // very large batches: several steps that share the CSR array
+        for (int64_t lo = 0; lo < n; lo += kMaxCsrPairs) {
+            const int64_t cnt = n - lo < kMaxCsrPairs ? n - lo : kMaxCsrPairs;
+            const int rc = greedy_dev_impl(ctx, d_reads, d_read_off + lo, d_refs, d_ref_off + lo, cnt, d_cost + lo, d_ops, ops_cap,
+                                           d_op_off + lo, carry_ops || lo > 0, false);
+            if (rc) return rc;
+        }
         return GASMA_OK;
     }
     const int warps = greedy_tile_threads(ctx) / 32;
-    constexpr int T = 128;   // tile of the CSR scan / compaction kernels
-    const int64_t ntiles = (n + T - 1) / T;
+    const int64_t ntiles = (n + kCsrTile - 1) / kCsrTile;
     const int stride = 2 * ctx->params.max_length + 8;
     uint32_t* misc = (uint32_t*)ctx->misc.p;
-    const bool want_ops = d_ops != nullptr;
+    const bool want_ops = want_csr || rows_only;
+    const int q = ctx->g_parity;
     int rc;
+    if ((rc = reserve(ctx, ctx->ops_rows, (size_t)n * kRowPitch * sizeof(uint16_t)))) return rc;   // always: emit() is unconditional
     if (want_ops) {
         if ((rc = reserve(ctx, ctx->ops_stage, (size_t)n * stride * sizeof(uint16_t)))) return rc;
         if ((rc = reserve(ctx, ctx->nops, (size_t)n * 4))) return rc;
-        const void* before = ctx->g_tile_sums.p;
-        if ((rc = reserve(ctx, ctx->g_tile_sums, (size_t)ntiles * 4))) return rc;
-        if (ctx->g_tile_sums.p != before) CU(cudaMemsetAsync(ctx->g_tile_sums.p, 0, ctx->g_tile_sums.cap, ctx->stream));
-        if ((rc = reserve(ctx, ctx->tile_bases, (size_t)ntiles * 4))) return rc;
     }
-    uint32_t* tsums = want_ops ? (uint32_t*)ctx->g_tile_sums.p : nullptr;
+    if (want_csr) {
+        for (int j = 0; j < 2; ++j) {
+            const void* before = ctx->g_sums[j].p;
+            if ((rc = reserve(ctx, ctx->g_sums[j], (size_t)ntiles * 4))) return rc;
+            if (ctx->g_sums[j].p != before) {
+                CU(cudaMemsetAsync(ctx->g_sums[j].p, 0, ctx->g_sums[j].cap, ctx->stream));
+                ctx->g_dirty[j] = 0;
+            }
+        }
+    }
+    uint32_t* tsums = want_csr ? (uint32_t*)ctx->g_sums[q].p : nullptr;
+    uint16_t* rows = (uint16_t*)ctx->ops_rows.p;
     uint16_t* stage = want_ops ? (uint16_t*)ctx->ops_stage.p : nullptr;
     uint32_t* nops = want_ops ? (uint32_t*)ctx->nops.p : nullptr;
     const uint8_t* r = (const uint8_t*)d_reads;
@@ -502,27 +532,31 @@ int greedy_dev_impl(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_read_
     cudaEvent_t* evp = ctx->ev[0][ctx->ev_count[0] % gasma_ctx::kRing];
     CU(cudaEventRecord(evp[0], ctx->stream));
     switch (ctx->W) {
-        case 1: rc = launch_greedy_w<1>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, chunk_counter, misc, steps, tsums); break;
-        case 2: rc = launch_greedy_w<2>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, chunk_counter, misc, steps, tsums); break;
-        case 3: rc = launch_greedy_w<3>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, chunk_counter, misc, steps, tsums); break;
-        case 4: rc = launch_greedy_w<4>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, chunk_counter, misc, steps, tsums); break;
-        case 8: rc = launch_greedy_warp<8>(ctx, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, chunk_counter, misc, steps, tsums); break;
-        default: rc = launch_greedy_warp<16>(ctx, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, chunk_counter, misc, steps, tsums); break;
+        case 1: rc = launch_greedy_w<1>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, rows, stage, stride, nops, chunk_counter, misc, steps, tsums); break;
+        case 2: rc = launch_greedy_w<2>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, rows, stage, stride, nops, chunk_counter, misc, steps, tsums); break;
+        case 3: rc = launch_greedy_w<3>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, rows, stage, stride, nops, chunk_counter, misc, steps, tsums); break;
+        case 4: rc = launch_greedy_w<4>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, rows, stage, stride, nops, chunk_counter, misc, steps, tsums); break;
+        case 8: rc = launch_greedy_warp<8>(ctx, r, d_read_off, f, d_ref_off, n, d_cost, rows, stage, stride, nops, chunk_counter, misc, steps, tsums); break;
+        default: rc = launch_greedy_warp<16>(ctx, r, d_read_off, f, d_ref_off, n, d_cost, rows, stage, stride, nops, chunk_counter, misc, steps, tsums); break;
     }
     if (rc) return rc;
     CU(cudaEventRecord(evp[1], ctx->stream));
     ctx->ev_count[0]++;
     ctx->counter_clean = false;   // the kernel leaves its chunk counter past the end
-    if (want_ops) {
-        // the per-tile op counts were accumulated by the greedy kernel; the scan zeroes them again and resets the chunk counter
-        scan_tiles_kernel<<<1, 1024, 0, ctx->stream>>>(tsums, (uint32_t*)ctx->tile_bases.p, (int)ntiles, misc + 1, carry_ops ? misc + 1 : nullptr,
-                                                       true, chunk_counter);
+    if (want_csr) {
+        if (ntiles > ctx->g_dirty[q]) ctx->g_dirty[q] = (int)ntiles;
+        // one kernel: tile bases from the counts the greedy kernel accumulated, CSR offsets, coalesced op copy; it also
+        // zeroes the other count array for the next batch and resets the chunk counter
+        const int bp = ctx->base_parity;
+        compact_rows_kernel<kCsrTile><<<(unsigned)ntiles, kCsrTile, 0, ctx->stream>>>(
+            rows, stage, stride, nops, tsums, (uint32_t*)ctx->g_sums[q ^ 1].p, ctx->g_dirty[q ^ 1],
+            carry_ops ? misc + 8 + bp : nullptr, misc + 8 + (bp ^ 1), (long long)n, d_ops, (long long)ops_cap, d_op_off, chunk_counter);
         CU(cudaGetLastError());
+        ctx->g_dirty[q ^ 1] = 0;
+        ctx->g_parity = q ^ 1;
+        ctx->base_parity = bp ^ 1;
         ctx->counter_clean = true;
-        compact_ops_kernel<T, false><<<(unsigned)ntiles, T, 0, ctx->stream>>>(stage, stride, nops, (uint32_t*)ctx->tile_bases.p,
-                                                                     (long long)n, d_ops, (long long)ops_cap, d_op_off, 0);
-        CU(cudaGetLastError());
-        ctx->launches += 2;
+        ctx->launches += 1;
     }
     return GASMA_OK;
 }
@@ -532,9 +566,38 @@ int check_offsets(gasma_ctx* ctx, const uint32_t* off, int64_t n, const char* wh
 // Host-pointer greedy call on a large batch, pipelined over kSlices slices of pairs (slice edges on multiples of
 // 128 pairs).  Device mirrors are already reserved by the caller.  Streams: copy_in (H2D), ctx->stream (kernels),
 // copy_out (D2H); the CSR op array is shared by all slices, op_off continues across them on the device.
+int greedy_batch_pipelined_body(gasma_ctx* ctx, const char* reads, const uint32_t* read_off, const char* refs,
+                                const uint32_t* ref_off, int64_t n, int32_t* cost, gasma_cigar_op* ops, int64_t ops_cap,
+                                uint32_t* op_off);
+
+// Every error exit of the pipelined call goes through here: copies from / into the caller's buffers may still be
+// queued on the copy streams, and the per-tile op counts may be half accumulated.  Drain all three streams and put
+// the context back into its clean state before the caller gets its buffers back.
 int greedy_batch_pipelined(gasma_ctx* ctx, const char* reads, const uint32_t* read_off, const char* refs,
                            const uint32_t* ref_off, int64_t n, int32_t* cost, gasma_cigar_op* ops, int64_t ops_cap,
                            uint32_t* op_off) {
+    const int rc = greedy_batch_pipelined_body(ctx, reads, read_off, refs, ref_off, n, cost, ops, ops_cap, op_off);
+    if (rc != GASMA_OK && rc != GASMA_E_CAPACITY) {
+        const std::string keep = ctx->err;
+        cudaStreamSynchronize(ctx->copy_in);
+        cudaStreamSynchronize(ctx->stream);
+        cudaStreamSynchronize(ctx->copy_out);
+        for (int j = 0; j < 2; ++j) {
+            if (ctx->g_sums[j].p) cudaMemsetAsync(ctx->g_sums[j].p, 0, ctx->g_sums[j].cap, ctx->stream);
+            ctx->g_dirty[j] = 0;
+        }
+        cudaMemsetAsync(ctx->misc.p, 0, 4, ctx->stream);   // status word
+        cudaStreamSynchronize(ctx->stream);
+        cudaGetLastError();
+        ctx->counter_clean = false;
+        ctx->err = keep;
+    }
+    return rc;
+}
+
+int greedy_batch_pipelined_body(gasma_ctx* ctx, const char* reads, const uint32_t* read_off, const char* refs,
+                                const uint32_t* ref_off, int64_t n, int32_t* cost, gasma_cigar_op* ops, int64_t ops_cap,
+                                uint32_t* op_off) {
     const int S = ctx->slices;
     const size_t ob = (size_t)(n + 1) * 4;
     int64_t edge[gasma_ctx::kSlices + 1];
@@ -582,9 +645,9 @@ int greedy_batch_pipelined(gasma_ctx* ctx, const char* reads, const uint32_t* re
     {   // full validation of both offset arrays, hidden behind the first slice's DMA (8 MB of host reads for 1 M pairs)
         int vrc = check_offsets(ctx, read_off, n, "read");
         if (!vrc) vrc = check_offsets(ctx, ref_off, n, "ref");
-        if (vrc) { cudaStreamSynchronize(ctx->copy_in); return vrc; }
+        if (vrc) return vrc;
     }
-    CU(cudaMemsetAsync(misc + 1, 0, 4, ctx->stream));   // running op total
+    CU(cudaMemsetAsync(misc + 8 + ctx->base_parity, 0, 4, ctx->stream));   // running op total the first slice starts from
     for (int i = 0; i < S; ++i) {
         const int64_t lo = edge[i], cnt = edge[i + 1] - edge[i];
         if (cnt == 0) { CU(cudaEventRecord(ctx->ev_off[i], ctx->copy_out)); continue; }

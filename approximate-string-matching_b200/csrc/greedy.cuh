@@ -203,6 +203,11 @@ GASMA_HD int pcb(const uint32_t* base, int stride, int from, int to) {
     const uint32_t a = base[w0 * stride] & mlo, z = base[w1 * stride] & mhi;   // w0 == w1: both masks on one word
     int c = w0 == w1 ? popc32(a & mhi) : popc32(a) + popc32(z);
     if (w1 - w0 >= 2) c += popc32(base[(w0 + 1) * stride]);   // up to three words without a loop
+    // longer ranges are rare; the loop stays rolled (this function is inlined three times into a kernel whose speed
+    // depends on its code staying inside the 32 KB instruction-cache tier)
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1
+#endif
     for (int w = w0 + 2; w < w1; ++w) c += popc32(base[w * stride]);
     return c;
 }
@@ -210,19 +215,62 @@ GASMA_HD int pcb(const uint32_t* base, int stride, int from, int to) {
 template <int W>
 GASMA_HD const uint32_t* lane_base(const LaneStore<W>& S, int li) { return S.lanes + (size_t)(li * 2 * W) * S.stride; }
 
+// CIGAR ops of one pair while it is being aligned.  A pair's ops go to its PRIMARY ROW: kRowOps ops = one 32-byte
+// sector, rows of consecutive pairs contiguous -- a 1 M-pair batch stages into 32 MB that stay in L2 and are read
+// back coalesced.  The few pairs with more ops move to their OVERFLOW ROW (`cap` ops, enough for any traversal).
+// Rule for consumers: a list of n <= kRowKeep ops is in the primary row, a longer one is complete in the overflow row.
+//
+// The kernel is bound by instruction issue and the three emit sites of _update_CIGAR run on every step of every
+// warp, so emit() is an unconditional indexed store + increment.  Room for the (at most two) ops of the next
+// update() is checked ONCE before it (reserve2): while n <= kRowKeep the primary row has it; beyond that the list is
+// copied to the overflow row and continues there.
+constexpr int kRowOps = 16;
+constexpr int kRowKeep = kRowOps - 2;
+#ifndef GASMA_ROW_PITCH
+#define GASMA_ROW_PITCH 16
+#endif
+constexpr int kRowPitch = GASMA_ROW_PITCH;   // ops between the primary rows of consecutive pairs (>= kRowOps)
 struct OpSink {
-    uint16_t* ops;   // this pair's staging row (may be null: costs only)
-    int cap;
+    uint16_t* rows;  // primary rows [pairs][kRowOps]; never null (a launch that wants no ops still stages them)
+    uint16_t* ovf;   // overflow rows [pairs][cap]
+    int cap;         // ops an overflow row holds
+    uint32_t p;      // this pair's row index
+    uint16_t* ops;   // row being written
     int n;
+    GASMA_HD void begin(uint32_t pair) {
+        p = pair;
+        n = 0;
+        ops = rows + (size_t)pair * kRowPitch;
+    }
     GASMA_HD void emit(int code, int len) {
-        if (ops && n < cap) ops[n] = (uint16_t)((len << 3) | code);
+        ops[n] = (uint16_t)((len << 3) | code);
         ++n;
+    }
+    GASMA_HD void spill() {   // rare
+        uint16_t* prim = rows + (size_t)p * kRowPitch;
+        uint16_t* big = ovf + (size_t)p * cap;
+        if (ops == prim) {
+            for (int i = 0; i < n; ++i) big[i] = prim[i];
+            ops = big;
+        }
+        // an overflow row that is full as well cannot happen (cap covers the longest traversal; the caller flags
+        // n > cap); further ops then land on the primary row's first two slots instead of out of bounds
+        if (n + 2 > cap) ops = prim - n;
+    }
+    GASMA_HD void reserve2() {
+        if (n > kRowKeep) spill();
     }
     // _update_CIGAR, hurdle_matrix.h:238-251
     GASMA_HD void update(int best, int cur, int total) {
+        reserve2();
         if (best < cur) emit(1, cur - best);
         else if (best > cur) emit(2, best - cur);
         if (total > 0) emit(0, total);
+    }
+    GASMA_HD void finish() { reserve2(); }   // a list that ended at kRowKeep+1 or +2 ops in the primary row moves over too
+    // the list a consumer reads (n = the pair's op count)
+    static GASMA_HD const uint16_t* list(const uint16_t* rows, const uint16_t* ovf_rows, int stride, long long p, uint32_t n) {
+        return n <= (uint32_t)kRowKeep ? rows + (size_t)p * kRowPitch : ovf_rows + (size_t)p * stride;
     }
 };
 

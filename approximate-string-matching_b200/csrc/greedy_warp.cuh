@@ -61,7 +61,7 @@ template <int W, int WARPS>
 __global__ void __launch_bounds__(32 * WARPS)
 greedy_warp_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __restrict__ read_off,
                    const uint8_t* __restrict__ refs, const uint32_t* __restrict__ ref_off, long long n,
-                   int32_t* __restrict__ cost, uint16_t* __restrict__ ops_stage, int ops_stride,
+                   int32_t* __restrict__ cost, uint16_t* __restrict__ ops_rows, uint16_t* __restrict__ ops_ovf, int ops_stride,
                    uint32_t* __restrict__ nops_out, uint32_t* __restrict__ pair_counter,
                    uint32_t* __restrict__ status, unsigned long long* __restrict__ step_counter,
                    uint32_t* __restrict__ tile_sums) {
@@ -141,9 +141,11 @@ greedy_warp_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t*
         const int dl = nn - m;
         int cl = 0, cc = 0, pen = 0, steps = 0, n_ops = 0;
         bool first = true;
-        uint16_t* my_ops = ops_stage ? ops_stage + (size_t)p * ops_stride : nullptr;
+        // lane 0 keeps the pair's op list (primary row / overflow row, greedy.cuh:OpSink)
+        uint16_t* my_ops = nops_out ? ops_rows + (size_t)p * kRowPitch : nullptr;   // nops_out == nullptr: costs only
+        uint16_t* my_ovf = nops_out ? ops_ovf + (size_t)p * ops_stride : nullptr;
         auto emit = [&](int code, int len) {
-            if (lane == 0 && my_ops && n_ops < ops_stride) my_ops[n_ops] = (uint16_t)((len << 3) | code);
+            if (lane == 0 && my_ops && n_ops < ops_stride) (n_ops < kRowOps ? my_ops : my_ovf)[n_ops] = (uint16_t)((len << 3) | code);
             ++n_ops;
         };
         auto update_cigar = [&](int best, int cur, int total) {   // _update_CIGAR, hurdle_matrix.h:238-251
@@ -257,9 +259,11 @@ greedy_warp_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t*
             }
         }
         if (lane == 0) {
+            if (my_ops && n_ops > kRowKeep)   // consumers read lists of more than kRowKeep ops from the overflow row
+                for (int i = 0; i < (n_ops < kRowOps ? n_ops : kRowOps); ++i) my_ovf[i] = my_ops[i];
             cost[p] = pen;
             if (nops_out) nops_out[p] = (uint32_t)n_ops;
-            if (tile_sums && n_ops) atomicAdd(tile_sums + (p >> 7), (uint32_t)n_ops);
+            if (tile_sums && n_ops) atomicAdd(tile_sums + (p >> kCsrTileShift), (uint32_t)n_ops);
             if (n_ops > ops_stride) st_bits |= kStatusSteps;
             steps_total += (unsigned long long)steps;
         }

@@ -22,7 +22,9 @@ __device__ __forceinline__ uint4 ldg_stream16(const void* p) {
 
 __device__ __forceinline__ uint4 load_chunk(const uint8_t* __restrict__ buf, uint32_t a, uint32_t total) {
     if (a + 16u <= total) return ldg_stream16(buf + a);
-    // last partial chunk of the whole buffer: never read past the logical end (rare: kept small, not unrolled)
+    // last partial chunk of the whole buffer: never read past the logical end (rare: kept small, not unrolled).
+    // Inlined on purpose: as a real call it breaks the one-chunk-ahead software pipeline of stage_tile (measured:
+    // long-scoreboard stalls at the first use of a chunk nearly double).
     uint32_t w[4] = {0u, 0u, 0u, 0u};
 #pragma unroll 1
     for (uint32_t i = 0; a + i < total; ++i) {
@@ -74,6 +76,7 @@ __host__ __device__ constexpr int stream_elems(int tile) { return ((stream_chunk
 // coalesced 16-byte loads.  Results are written by pair index, so they do not depend on the schedule.
 // ---------------------------------------------------------------------------------------------
 constexpr int kPool = 32;   // pairs per chunk = per warp pool
+constexpr int kCsrTileShift = 9, kCsrTile = 1 << kCsrTileShift;   // pairs per CTA of compact_rows_kernel
 
 template <int W>
 __host__ __device__ constexpr size_t greedy_smem_bytes(int warps, int nl) {   // nl = lane slots per alignment (KParams::nl)
@@ -86,10 +89,10 @@ template <int W, int WARPS, bool CORR>
 __global__ void __launch_bounds__(32 * WARPS, CORR ? 1 : (WARPS == 8 ? 3 : (WARPS == 4 ? 5 : (WARPS == 2 ? 11 : 1))))
 greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __restrict__ read_off,
               const uint8_t* __restrict__ refs, const uint32_t* __restrict__ ref_off, long long n,
-              int32_t* __restrict__ cost, uint16_t* __restrict__ ops_stage, int ops_stride,
+              int32_t* __restrict__ cost, uint16_t* __restrict__ ops_rows, uint16_t* __restrict__ ops_ovf, int ops_stride,
               uint32_t* __restrict__ nops_out, uint32_t* __restrict__ chunk_counter, int refill_threshold,
               uint32_t* __restrict__ status, unsigned long long* __restrict__ step_counter,
-              uint32_t* __restrict__ tile_sums) {   // optional: op count per 128-pair tile, accumulated here (input of scan_tiles_kernel)
+              uint32_t* __restrict__ tile_sums) {   // optional: op count per kCsrTile pairs, accumulated here (input of compact_rows_kernel)
     constexpr int BITS = 64 * W;
     constexpr int T = 32 * WARPS;
     constexpr int SE = stream_elems<W>(kPool);
@@ -150,8 +153,10 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
             pf = kOffsets;
         } else if (pf == kOffsets) {
             const uint32_t r0 = __shfl_sync(0xffffffffu, nx_ro, 0) & ~127u, f0 = __shfl_sync(0xffffffffu, nx_fo, 0) & ~127u;
+#pragma unroll 1
             for (uint32_t a = r0 + 128u * lane; a < nx_re; a += 128u * 32u)
                 asm volatile("prefetch.global.L2 [%0];" ::"l"(reads + a));
+#pragma unroll 1
             for (uint32_t a = f0 + 128u * lane; a < nx_fe; a += 128u * 32u)
                 asm volatile("prefetch.global.L2 [%0];" ::"l"(refs + a));
             pf = kReady;
@@ -161,18 +166,25 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
     bool active = false;
     long long my_p = 0;
     PairState ps;
-    OpSink sink{nullptr, 0, 0};
+    // a launch that wants no ops (nops_out == nullptr) still stages them in the primary rows (unconditional emit); its
+    // "overflow row" is the primary row itself, so longer lists just wrap onto its first slots
+    OpSink sink{ops_rows, nops_out ? ops_ovf : ops_rows, nops_out ? ops_stride : kRowOps, 0u, nullptr, 0};
     uint32_t st = 0;
     uint32_t steps_done = 0;
 
     for (;;) {
-        if (pf != kReady && pf != kDone) advance();
         const uint32_t idle = __ballot_sync(0xffffffffu, !active);
         const int n_idle = __popc(idle);
         if (n_idle >= refill_threshold || n_idle == 32) {
+            // The claim pipeline has ONE call site (below the hand-out, one stage per iteration, so that the chunk after a
+            // freshly staged one is claimed in the same iteration): when the pool is empty and the next chunk is not
+            // ready yet (start of the kernel, a very short pool), the warp simply comes round again -- stepping
+            // whatever threads are still active on the way.
             if (pool_next == pool_count && pf != kDone) {
                 // ---- stage the claimed chunk (whole warp, converged) ----
-                while (pf != kReady && pf != kDone) advance();   // start of the kernel / a very short pool
+                // the pool ran empty before the next chunk's pipeline finished (start of the kernel, pairs that finish
+                // quickly): finish it now rather than spin through iterations with idle threads
+                while (pf != kReady && pf != kDone) advance();
                 if (pf == kReady) {
                     pool_p0 = (long long)nx_chunk * kPool;
                     pool_count = nx_count;
@@ -188,8 +200,7 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
                                               side ? ftotal : rtotal, side ? s_f0 : s_r0, side ? s_f1 : s_r1,
                                               stream_chunks<W>(kPool), lane, 32);
                     __syncwarp();
-                    pf = kNone;
-                    advance();   // claim the chunk after this one right away
+                    pf = kNone;   // the chunk after this one is claimed right below
                 }
             }
             // ---- hand the pool's next pairs to the idle threads ----
@@ -216,13 +227,14 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
                     const int rbit = (int)(ro_q - rbase), fbit = (int)(fo_q - fbase);
                     pair_init32<W, CORR>(P, reinterpret_cast<const uint32_t*>(s_r0), reinterpret_cast<const uint32_t*>(s_r1), rbit, m,
                                          reinterpret_cast<const uint32_t*>(s_f0), reinterpret_cast<const uint32_t*>(s_f1), fbit, nn, S, ps);
-                    sink = OpSink{ops_stage ? ops_stage + (size_t)my_p * ops_stride : nullptr, ops_stride, 0};
+                    sink.begin((uint32_t)my_p);
                     active = true;
                 }
             }
             pool_next = imin(pool_count, pool_next + n_idle);
             __syncwarp();
         }
+        if (pf != kReady && pf != kDone) advance();
         if (__ballot_sync(0xffffffffu, active) == 0u) {
             if (pf == kDone && pool_next == pool_count) break;
             continue;   // every pair handed out so far was rejected, or the pool just ran empty
@@ -230,9 +242,10 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
         if (active) {
             if (pair_step<W, CORR>(P, S, ps, sink, st)) {
                 pair_finish<W, CORR>(P, S, ps, sink);
+                sink.finish();
                 cost[my_p] = ps.cost;
                 if (nops_out) nops_out[my_p] = (uint32_t)sink.n;
-                if (tile_sums && sink.n) atomicAdd(tile_sums + (my_p >> 7), (uint32_t)sink.n);
+                if (tile_sums && sink.n) atomicAdd(tile_sums + (my_p >> kCsrTileShift), (uint32_t)sink.n);
                 if (sink.n > ops_stride) st |= kStatusSteps;  // cannot happen: the stride covers the step limit
                 steps_done += (uint32_t)ps.steps;
                 active = false;
@@ -293,6 +306,106 @@ __global__ void __launch_bounds__(1024) scan_tiles_kernel(uint32_t* __restrict__
     }
     if (tid == 0 && total_out) *total_out = s_carry;
     if (tid == 0 && reset_word) *reset_word = 0u;
+}
+
+// ---------------------------------------------------------------------------------------------
+// CSR of the greedy path in ONE kernel (no separate scan launch): the greedy kernel has already accumulated the op
+// count of every kCsrTile-pair tile in `sums`, so a CTA gets its tile's base by adding up its predecessors' counts
+// (<= 4 coalesced loads per thread for a 1 M-pair batch, all L2 hits), then scans its own pairs, gathers their ops
+// from the 32-byte primary rows (overflow rows for the few longer lists) in shared memory and writes them out 16
+// bytes at a time.  op_off[p] = base + tile base + prefix inside the tile; op_off[n] = total.
+// Housekeeping for the next batch, so that a greedy step is two launches and no memset:
+//   * `sums_next` (the OTHER parity's count array, used by the next greedy launch) is zeroed up to `dirty_next`
+//   * `reset_word` (the greedy kernel's chunk counter) is set to 0
+//   * base_in / base_out: running op total across the slices of one pipelined host call (two words, alternating,
+//     because every CTA reads the base while the last CTA writes the next one)
+// ---------------------------------------------------------------------------------------------
+constexpr int kCsrSmemOps = kCsrTile * kRowOps;   // a tile whose lists all fit their primary rows always fits
+
+template <int T>
+__global__ void __launch_bounds__(T)
+compact_rows_kernel(const uint16_t* __restrict__ rows, const uint16_t* __restrict__ ovf, int ops_stride,
+                    const uint32_t* __restrict__ nops, const uint32_t* __restrict__ sums, uint32_t* __restrict__ sums_next,
+                    int dirty_next, const uint32_t* __restrict__ base_in, uint32_t* __restrict__ base_out, long long n,
+                    uint16_t* __restrict__ ops_out, long long ops_cap, uint32_t* __restrict__ op_off,
+                    uint32_t* __restrict__ reset_word) {
+    static_assert(T == kCsrTile, "one thread per pair of the tile");
+    __shared__ uint32_t s_warp[T / 32];
+    __shared__ uint32_t s_pref[T / 32];
+    __shared__ __align__(16) uint16_t s_ops[kCsrSmemOps + 8];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const long long p = (long long)blockIdx.x * T + tid;
+    // housekeeping first: it does not depend on anything below
+    for (int i = blockIdx.x * T + tid; i < dirty_next; i += gridDim.x * T) sums_next[i] = 0u;
+    if (blockIdx.x == 0 && tid == 0 && reset_word) *reset_word = 0u;
+    // ---- base of this tile = ops of all tiles before it ----
+    uint32_t acc = 0u;
+    for (int i = tid; i < (int)blockIdx.x; i += T) acc += sums[i];
+    acc = __reduce_add_sync(0xffffffffu, acc);
+    // ---- exclusive scan of this tile's op counts ----
+    const uint32_t v = p < n ? nops[p] : 0u;
+    uint32_t inc = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= d) inc += t;
+    }
+    if (lane == 31) s_warp[warp] = inc;
+    if (lane == 0) s_pref[warp] = acc;
+    __syncthreads();
+    uint32_t wbase = 0u, tile_total = 0u, before = 0u;
+#pragma unroll
+    for (int i = 0; i < T / 32; ++i) {
+        wbase += (i < warp) ? s_warp[i] : 0u;
+        tile_total += s_warp[i];
+        before += s_pref[i];
+    }
+    const uint32_t tile_base = (base_in ? *base_in : 0u) + before;
+    const uint32_t local = wbase + inc - v;
+    const uint32_t off = tile_base + local;
+    const uint32_t shift = (uint32_t)((reinterpret_cast<uintptr_t>(ops_out + tile_base) >> 1) & 7u);
+    const bool via_smem = tile_total <= (uint32_t)kCsrSmemOps && (long long)tile_base + tile_total <= ops_cap;
+    if (p < n) {
+        op_off[p] = off;
+        if (p == n - 1) {
+            op_off[n] = off + v;
+            if (base_out) *base_out = off + v;
+        }
+        if (v <= (uint32_t)kRowKeep) {   // the common case: one 32-byte sector, read as two 16-byte loads
+            const uint4* rp = reinterpret_cast<const uint4*>(rows + (size_t)p * kRowPitch);
+            uint4 q[2];
+            q[0] = v ? rp[0] : make_uint4(0u, 0u, 0u, 0u);
+            q[1] = v > 8u ? rp[1] : make_uint4(0u, 0u, 0u, 0u);
+            const uint32_t w[8] = {q[0].x, q[0].y, q[0].z, q[0].w, q[1].x, q[1].y, q[1].z, q[1].w};
+#pragma unroll
+            for (uint32_t e = 0; e < (uint32_t)kRowKeep; ++e) {
+                if (e < v) {
+                    const uint16_t op = (uint16_t)(w[e >> 1] >> (16u * (e & 1u)));
+                    if (via_smem) s_ops[shift + local + e] = op;
+                    else if ((long long)(off + e) < ops_cap) ops_out[off + e] = op;
+                }
+            }
+        } else {
+            const uint16_t* src = ovf + (size_t)p * ops_stride;
+            for (uint32_t e = 0; e < v; ++e) {
+                if (via_smem) s_ops[shift + local + e] = src[e];
+                else if ((long long)(off + e) < ops_cap) ops_out[off + e] = src[e];
+            }
+        }
+    }
+    if (!via_smem) return;   // block-uniform
+    __syncthreads();
+    // s_ops[shift + k] -> ops_out[tile_base + k]; dst = ops_out + tile_base - shift is 16-byte aligned
+    uint16_t* dst = ops_out + tile_base - shift;
+    const uint32_t end = shift + tile_total;
+    for (uint32_t c = tid; 8u * c < end; c += T) {
+        const uint32_t lo = 8u * c;
+        if (lo >= shift && lo + 8u <= end) {
+            *reinterpret_cast<uint4*>(dst + lo) = *reinterpret_cast<const uint4*>(s_ops + lo);
+        } else {
+            for (uint32_t e = lo < shift ? shift : lo; e < lo + 8u && e < end; ++e) dst[e] = s_ops[e];
+        }
+    }
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -4,7 +4,7 @@
 //
 // gasma_greedy_batch_dev keeps its scratch (per-pair CIGAR staging rows, op counts, per-tile sums / bases, the chunk
 // counter) in context buffers that grow with cudaMalloc.  This variant keeps the same scratch in ONE file-scope
-// __device__ array of fixed size: every GPU that loads the library holds it (8.6 MB) until the process exits, and
+// __device__ array of fixed size: every GPU that loads the library holds it (8.8 MB) until the process exits, and
 // the call itself allocates nothing -- no cudaMalloc / cudaFree / reserve().
 //
 // In host code `g_noalloc_scratch` is only a host-side stand-in for the symbol, NOT a device address: the address
@@ -17,12 +17,12 @@ namespace {
 
 constexpr int kNoallocMaxPairs = GASMA_NOALLOC_MAX_PAIRS;
 constexpr int kNoallocMaxLength = GASMA_NOALLOC_MAX_LENGTH;
-constexpr int kNoallocTiles = (kNoallocMaxPairs + 127) / 128;
-constexpr size_t kNoallocStageBytes = (size_t)kNoallocMaxPairs * (2 * kNoallocMaxLength + 8) * sizeof(uint16_t);
-constexpr size_t kNoallocNopsOff = kNoallocStageBytes;                                  // uint32 [pairs]
+constexpr int kNoallocTiles = (kNoallocMaxPairs + kCsrTile - 1) / kCsrTile;
+constexpr size_t kNoallocStageBytes = (size_t)kNoallocMaxPairs * (2 * kNoallocMaxLength + 8) * sizeof(uint16_t);   // overflow rows
+constexpr size_t kNoallocRowsOff = kNoallocStageBytes;                                                    // primary rows [pairs][kRowOps]
+constexpr size_t kNoallocNopsOff = kNoallocRowsOff + (size_t)kNoallocMaxPairs * kRowPitch * sizeof(uint16_t);   // uint32 [pairs]
 constexpr size_t kNoallocSumsOff = kNoallocNopsOff + (size_t)kNoallocMaxPairs * 4;      // uint32 [tiles]
-constexpr size_t kNoallocBasesOff = kNoallocSumsOff + (size_t)kNoallocTiles * 4;        // uint32 [tiles]
-constexpr size_t kNoallocWordsOff = kNoallocBasesOff + (size_t)kNoallocTiles * 4;       // [0] chunk counter, [1] op total
+constexpr size_t kNoallocWordsOff = kNoallocSumsOff + (size_t)kNoallocTiles * 4;        // [0] chunk counter, [1] op total
 constexpr size_t kNoallocBytes = (kNoallocWordsOff + 64 + 255) / 256 * 256;
 
 }  // namespace
@@ -74,17 +74,16 @@ int gasma_greedy_batch_dev_noalloc(gasma_ctx* ctx, const char* d_reads, const ui
     unsigned char* base = nullptr;
     int rc = noalloc_scratch(ctx, &base);
     if (rc) return rc;
-    constexpr int T = 128;
-    const int64_t ntiles = (n + T - 1) / T;
+    const int64_t ntiles = (n + kCsrTile - 1) / kCsrTile;
     const int stride = 2 * ctx->params.max_length + 8;
     const bool want_ops = d_ops != nullptr;
     uint16_t* stage = want_ops ? (uint16_t*)base : nullptr;
+    uint16_t* rows = (uint16_t*)(base + kNoallocRowsOff);   // always: the kernel stages ops unconditionally
     uint32_t* nops = want_ops ? (uint32_t*)(base + kNoallocNopsOff) : nullptr;
     uint32_t* tsums = want_ops ? (uint32_t*)(base + kNoallocSumsOff) : nullptr;
-    uint32_t* tbases = (uint32_t*)(base + kNoallocBasesOff);
     uint32_t* words = (uint32_t*)(base + kNoallocWordsOff);
     uint32_t* misc = (uint32_t*)ctx->misc.p;   // status + step counter stay with the context (allocated by gasma_create)
-    // the array keeps the last call's contents: clear what must start at zero (tile sums, bases, chunk counter, total)
+    // the array keeps the last call's contents: clear what must start at zero (tile sums, chunk counter, total)
     CU(cudaMemsetAsync(base + kNoallocSumsOff, 0, kNoallocBytes - kNoallocSumsOff, ctx->stream));
     const uint8_t* r = (const uint8_t*)d_reads;
     const uint8_t* f = (const uint8_t*)d_refs;
@@ -95,20 +94,18 @@ int gasma_greedy_batch_dev_noalloc(gasma_ctx* ctx, const char* d_reads, const ui
     const bool keep_clean = ctx->counter_clean;
     ctx->counter_clean = true;
     switch (ctx->W) {
-        case 1: rc = launch_greedy_w<1>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, words, misc, steps, tsums); break;
-        case 2: rc = launch_greedy_w<2>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, words, misc, steps, tsums); break;
-        case 3: rc = launch_greedy_w<3>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, words, misc, steps, tsums); break;
-        default: rc = launch_greedy_w<4>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, stage, stride, nops, words, misc, steps, tsums); break;
+        case 1: rc = launch_greedy_w<1>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, rows, stage, stride, nops, words, misc, steps, tsums); break;
+        case 2: rc = launch_greedy_w<2>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, rows, stage, stride, nops, words, misc, steps, tsums); break;
+        case 3: rc = launch_greedy_w<3>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, rows, stage, stride, nops, words, misc, steps, tsums); break;
+        default: rc = launch_greedy_w<4>(ctx, warps, r, d_read_off, f, d_ref_off, n, d_cost, rows, stage, stride, nops, words, misc, steps, tsums); break;
     }
     ctx->counter_clean = keep_clean;
     if (rc) return rc;
     if (want_ops) {
-        scan_tiles_kernel<<<1, 1024, 0, ctx->stream>>>(tsums, tbases, (int)ntiles, words + 1, nullptr, false, nullptr);
+        compact_rows_kernel<kCsrTile><<<(unsigned)ntiles, kCsrTile, 0, ctx->stream>>>(
+            rows, stage, stride, nops, tsums, tsums, 0, nullptr, words + 1, (long long)n, d_ops, (long long)ops_cap, d_op_off, nullptr);
         CU(cudaGetLastError());
-        compact_ops_kernel<T, false><<<(unsigned)ntiles, T, 0, ctx->stream>>>(stage, stride, nops, tbases, (long long)n, d_ops,
-                                                                             (long long)ops_cap, d_op_off, 0);
-        CU(cudaGetLastError());
-        ctx->launches += 2;
+        ctx->launches += 1;
     }
     return GASMA_OK;
 }

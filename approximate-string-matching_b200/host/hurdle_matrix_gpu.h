@@ -128,6 +128,32 @@ public:
 
     gasma_ctx* context() { return ctx_; }
 
+    // lane range of the staged pair (hurdle_matrix.h:634-644): -k..k, or the widened band of a -DCORRECTION build
+    int lower_bound() const {
+#ifdef CORRECTION
+        if (read_.size() > ref_.size()) return (int)ref_.size() - (int)read_.size() - k_;
+#endif
+        return -k_;
+    }
+    int upper_bound() const {
+#ifdef CORRECTION
+        if (read_.size() <= ref_.size()) return (int)ref_.size() - (int)read_.size() + k_;
+#endif
+        return k_;
+    }
+
+protected:
+    // 2-bit planes of the staged pair as the device packs them (sse3_convert2bit1, bit_convert.cpp:248): W words each.
+    // For debug views only (include/compat/hurdle_matrix.h: print(), operator[]).
+    void planes(uint64_t* a0, uint64_t* a1, uint64_t* b0, uint64_t* b1) {
+        const int W = max_length_ / 64;
+        std::string both = read_ + ref_;
+        const uint32_t off[3] = {0u, (uint32_t)read_.size(), (uint32_t)both.size()};
+        std::vector<uint64_t> p0((size_t)2 * W), p1((size_t)2 * W);
+        check(gasma_pack2bit_batch(ctx_, both.data(), off, 2, p0.data(), p1.data()));
+        for (int j = 0; j < W; ++j) { a0[j] = p0[j]; a1[j] = p1[j]; b0[j] = p0[W + j]; b1[j] = p1[W + j]; }
+    }
+
 private:
     static std::string render(const gasma_cigar_op* ops, int n) {
         std::string s((size_t)gasma_render_cigar(ops, n, nullptr, 0), '\0');

@@ -113,28 +113,33 @@ class ClockSampler:
 
     def _pump(self):
         for line in self.proc.stdout:
-            if self.on:
-                self.lines.append(line.strip())
+            self.lines.append((self.on, line.strip()))
 
     def stop(self):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.25)
         self.proc.terminate()
-        sm, mx, reasons = [], [], set()
-        for ln in self.lines:
+        sm, sm_load, mx, reasons = [], [], [], set()
+        for on, ln in self.lines:
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 9:
                 continue
             try:
                 sm.append(float(f[1])); mx.append(float(f[2]))
+                if on:
+                    sm_load.append(float(f[1]))
             except ValueError:
                 continue
             for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
                 if v.lower().startswith("active"):
                     reasons.add(name)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+        # the timed regions are ~10 ms long and nvidia-smi samples every 100 ms: samples that fell inside a GPU leg
+        # (generation + warm-up + timed region) are counted apart; the median is theirs when there are at least 3
+        use = sm_load if len(sm_load) >= 3 else sm
+        return {"sm_mhz": float(np.median(use)) if use else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "samples_in_gpu_legs": len(sm_load), "sm_mhz_min": min(sm) if sm else None,
+                "reasons": sorted(reasons)}
 
 
 def load_pkg():

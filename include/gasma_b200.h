@@ -131,7 +131,7 @@ int gasma_greedy_batch_dev(gasma_ctx* ctx,
 /* No counterpart in the reference; added for callers that cannot call
  * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same inputs, outputs
  * and results as gasma_greedy_batch_dev, but the call allocates NOTHING: its scratch (per-pair CIGAR staging rows,
- * op counts, per-tile sums, chunk counter) is a file-scope __device__ array of the library, 8.6 MB that every GPU
+ * op counts, per-tile sums, chunk counter) is a file-scope __device__ array of the library, 8.8 MB that every GPU
  * which loads the library holds until the process exits.  Limits: n_pairs <= GASMA_NOALLOC_MAX_PAIRS and the
  * context's max_length <= GASMA_NOALLOC_MAX_LENGTH; anything larger is rejected with GASMA_E_UNSUPPORTED.
  * All calls on one device share the array: calls that overlap on the GPU (different streams or contexts) race on

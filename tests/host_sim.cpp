@@ -80,8 +80,16 @@ int sim_greedy(const KParams& P, const uint8_t* reads, const uint32_t* roff, con
                 extract_plane<W>(reinterpret_cast<const uint32_t*>(f0.data()), fbit, nn, B0);
                 extract_plane<W>(reinterpret_cast<const uint32_t*>(f1.data()), fbit, nn, B1);
                 LaneStore<W> S{lanes.data(), state.data(), 1};
-                OpSink sink{ops_stage ? ops_stage + (size_t)(p0 + t) * stride : nullptr, stride, 0};
+                // primary row (kRowOps ops) + overflow row, like the kernels; the harness then leaves the complete list in
+                // the pair's staging row whichever of the two holds it
+                alignas(16) uint16_t prim[kRowOps];
+                uint16_t* row = ops_stage ? ops_stage + (size_t)(p0 + t) * stride : nullptr;
+                std::vector<uint16_t> big(stride);
+                OpSink sink{prim, row ? row : big.data(), stride, 0u, nullptr, 0};
+                sink.begin(0u);
                 st = greedy_pair<W, CORR>(P, A0, A1, B0, B1, m, nn, S, sink, c, steps);
+                sink.finish();
+                if (row && sink.n <= kRowKeep) for (int i = 0; i < sink.n; ++i) row[i] = prim[i];
                 my = (uint32_t)sink.n;
             }
             cost[p0 + t] = c;

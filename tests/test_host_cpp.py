@@ -190,3 +190,76 @@ def test_mapper_sam_matches_oracle(drivers, ol, tmp_path):
                 merged.append(run)
         assert rec[5] == ("".join("%d%s" % (ln, "MID=X"[c]) for c, ln in merged) or "*")
         assert rec[0].startswith("read") and rec[10] == "I" * len(rec[9])
+
+
+# ---- the reference's OWN drivers, unmodified, against include/compat (drop-in boundary) ---------------------------
+REF = "/root/reference/GASMA"
+REFDRV = os.path.join(ROOT, "tests", "_build", "refdrv")
+
+
+def build_reference_drivers():
+    """Compile scratch copies of GASMA/main.cpp and GASMA/benchmark/benchmark.cpp -- byte for byte the reference's
+    files, placed away from the reference's headers because a quoted #include looks beside the source first -- with
+    -I include/compat.  Outputs stay under tests/_build (git-ignored; they travel to the GPU box)."""
+    os.makedirs(REFDRV, exist_ok=True)
+    built = {}
+    for name, src in (("ref_main", "main.cpp"), ("ref_benchmark", "benchmark/benchmark.cpp")):
+        text = open(os.path.join(REF, src), "rb").read()
+        scratch = os.path.join(REFDRV, name + ".cpp")
+        with open(scratch, "wb") as f:
+            f.write(text)
+        out = os.path.join(REFDRV, name)
+        subprocess.run(["g++", "-std=c++17", "-O2", "-pthread", "-I", os.path.join(ROOT, "include", "compat"), "-o", out, scratch,
+                        "-L" + os.path.dirname(HOST), "-lgasma_b200", "-Wl,-rpath," + os.path.dirname(HOST)], check=True)
+        os.remove(scratch)          # no reference source is kept in the tree, not even in the scratch directory
+        built[name] = out
+    return built
+
+
+def test_reference_drivers_compile_unmodified(drivers):
+    if not os.path.isdir(REF):
+        pytest.skip("/root/reference absent (GPU box): the binaries were built in the container")
+    built = build_reference_drivers()
+    assert all(os.path.exists(p) for p in built.values())
+    import torch
+    if not torch.cuda.is_available():
+        r = subprocess.run([built["ref_main"]], capture_output=True, text=True)
+        assert r.returncode != 0 and "no CPU path" in r.stderr      # fails loudly, no fallback
+
+
+@pytest.mark.gpu
+def test_reference_demo_runs_unmodified(drivers, ol):
+    """GASMA/main.cpp:5-19 compiled unmodified: prints the 7 lanes, then the CIGAR, the cost and the LCM line."""
+    exe = os.path.join(REFDRV, "ref_main")
+    if not os.path.exists(exe):
+        if not os.path.isdir(REF):
+            pytest.skip("tests/_build/refdrv/ref_main was not built in the container")
+        exe = build_reference_drivers()["ref_main"]
+    out = subprocess.run([exe], check=True, capture_output=True, text=True).stdout.split("\n")
+    read = "TGCGTCGCAGTGTCGAAAAAAATCTAAAGGGCCTACCGGGCCCCTTCATGAAGAGCAGGGAAAGAATCTCTATACTATTACTAATGGAAAGCAGTCTTGG"
+    ref = "TGCGTCGCAGTGTCGAAATAAAATCTAAAGGGCCTACCGGGCCCCTTCATGAAGAGTAGGTAAAGAATCTCTAGTACTACTACTAATGGAAAGCAGTCTTGG"
+    # lanes: _construct_hurdles + flip_short_hurdles(1) restated on python ints from the oracle's planes
+    a0, a1 = [int(v[0]) | (int(v[1]) << 64) for v in ol.oracle_pack(read.encode(), 2)]
+    b0, b1 = [int(v[0]) | (int(v[1]) << 64) for v in ol.oracle_pack(ref.encode(), 2)]
+    M = (1 << 128) - 1
+    for i, l in enumerate(range(-3, 4)):
+        v = (((a0 >> -l) ^ b0) | ((a1 >> -l) ^ b1)) if l < 0 else (((b0 >> l) ^ a0) | ((b1 >> l) ^ a1))
+        f = v & ((v >> 1) | ((v << 1) & M))
+        assert out[i] == "lane %d:" % l + "".join("1" if (f >> j) & 1 else "0" for j in range(128)), l
+    assert out[7] == "" and out[8] == "22M1D50M1D28M" and out[9] == "cost: 6"      # golden G1 (SURVEY.md 8c)
+    s1 = b"GCCCCGTCCCAGCACAGGCAGCGGGGATGCTCTAGAGCGATGTCGACCTGGGAAAGGCGCTGGGGCGCGCCGAATTCCAAAGGAGTTCCGTAAGGTTCAG"
+    ops = np.array([(22 << 3), (1 << 3) | 2, (50 << 3), (1 << 3) | 2, (28 << 3)], np.uint16)
+    buf = np.zeros(256, np.uint8)
+    n = ol.oracle().go_lcm(ol._ptr(np.frombuffer(s1, np.uint8)), len(s1), ol._ptr(ops), len(ops), 3, ol._ptr(buf), 256)
+    assert out[10] == buf[:n].tobytes().decode()
+
+
+@pytest.mark.gpu
+def test_reference_benchmark_driver_links_and_reports_missing_file(drivers):
+    """GASMA/benchmark/benchmark.cpp:27-31 (USE_SIMULATED_DATA false) names a file that only exists on its author's
+    machine: like the reference, the harness reports that it cannot open it and prints an empty report."""
+    exe = os.path.join(REFDRV, "ref_benchmark")
+    if not os.path.exists(exe):
+        pytest.skip("tests/_build/refdrv/ref_benchmark was not built in the container")
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert "SRR611076.data" in r.stdout + r.stderr

@@ -1,7 +1,7 @@
 # A/B of library builds on the greedy bench line: kernel time from a plain run, executed warp instructions and average
 # active threads of the greedy kernel from a metrics-only ncu pass of the same command.
 #   tools/ab_instr.sh path/to/a.so path/to/b.so ...
-CMD="python bench.py --steps 6 --warmup 3 --no-cpu-baseline --no-full-path"
+CMD="python bench.py --steps 6 --warmup 3 --no-cpu-baseline --no-full-path --no-configs --no-parity"
 for lib in "$@"; do
   export GASMA_B200_LIB=$PWD/$lib
   $CMD 2>/dev/null | python -c "

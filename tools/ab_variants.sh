@@ -1,7 +1,7 @@
 # A/B of prebuilt library variants (approximate-string-matching_b200/variants/*.so) on the greedy bench line
 for v in "$@"; do
   for rep in 1 2; do
-  GASMA_B200_LIB=$PWD/approximate-string-matching_b200/variants/$v.so python bench.py --steps 20 --warmup 3 --no-cpu-baseline --no-full-path 2>/dev/null | python -c "
+  GASMA_B200_LIB=$PWD/approximate-string-matching_b200/variants/$v.so python bench.py --steps 20 --warmup 3 --no-cpu-baseline --no-full-path --no-configs --no-parity 2>/dev/null | python -c "
 import sys,json
 for l in sys.stdin:
     l=l.strip()
