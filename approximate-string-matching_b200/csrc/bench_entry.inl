@@ -28,15 +28,17 @@ int benchmark_dev_impl(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_re
     const size_t ob = (size_t)(n + 1) * 4;
     if (!d_gcost) { if ((rc = reserve(ctx, ctx->bm_gcost, (size_t)n * 4))) return rc; d_gcost = (int32_t*)ctx->bm_gcost.p; }
     if (!d_nwpen) { if ((rc = reserve(ctx, ctx->bm_nwpen, (size_t)n * 4))) return rc; d_nwpen = (int32_t*)ctx->bm_nwpen.p; }
+    if (ctx->kp.x == 1 && ctx->kp.o == 1 && ctx->kp.e == 1 && ctx->W <= 4) {
+        // unit penalties (what the reference's benchmark always runs): verifier and counters are one kernel, and it reads
+        // the greedy CIGAR straight from the staging rows -- no CSR is built for it (two dominant launches per batch)
+        if ((rc = greedy_dev_impl(ctx, d_reads, d_read_off, d_refs, d_ref_off, n, d_gcost, nullptr, 0, nullptr, false, /*rows_only=*/true))) return rc;
+        return nw_counters_dev_impl(ctx, d_reads, d_read_off, d_refs, d_ref_off, n, d_gcost, d_nwpen, d_answers, d_counters);
+    }
     if ((rc = reserve(ctx, ctx->bm_goff, ob))) return rc;
     const int64_t cap = n * (2 * (int64_t)ctx->params.max_length + 8);
     if ((rc = reserve(ctx, ctx->bm_gops, (size_t)cap * 2))) return rc;
     uint32_t* goff = (uint32_t*)ctx->bm_goff.p;
     if ((rc = greedy_dev_impl(ctx, d_reads, d_read_off, d_refs, d_ref_off, n, d_gcost, (gasma_cigar_op*)ctx->bm_gops.p, cap, goff))) return rc;
-    if (ctx->kp.x == 1 && ctx->kp.o == 1 && ctx->kp.e == 1 && ctx->W <= 4)
-        // unit penalties (what the reference's benchmark always runs): verifier and counters are one kernel
-        return nw_counters_dev_impl(ctx, d_reads, d_read_off, d_refs, d_ref_off, n, d_gcost, d_nwpen,
-                                    (const gasma_cigar_op*)ctx->bm_gops.p, goff, d_answers, d_counters);
     if ((rc = reserve(ctx, ctx->bm_noff, ob))) return rc;
     if ((rc = reserve(ctx, ctx->bm_nops, (size_t)cap * 2))) return rc;
     uint32_t* noff = (uint32_t*)ctx->bm_noff.p;

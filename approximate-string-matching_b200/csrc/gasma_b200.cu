@@ -68,7 +68,7 @@ struct gasma_ctx {
     DevBuf d_reads, d_refs, d_read_off, d_ref_off, d_cost, d_ops, d_op_off, d_p0, d_p1;
     DevBuf gen_len, d_bound, nw_deferred, nw_tb, nw_pool_hi, nw_pool_tb;
     // gasma_benchmark_batch scratch: both CIGAR CSR arrays, penalties, counters, answers
-    DevBuf bm_gops, bm_goff, bm_nops, bm_noff, bm_gcost, bm_nwpen, bm_counters, bm_answers, bm_hard;
+    DevBuf bm_gops, bm_goff, bm_nops, bm_noff, bm_gcost, bm_nwpen, bm_counters, bm_answers, bm_hard, bm_nstage, bm_nnops;
     int64_t bm_gcap = 0, bm_ncap = 0;
     uint32_t* h_misc = nullptr;  // pinned, 32 words: [0..3] device misc mirror, [8..9] op totals, [10..17] counters
     // timing hooks: a ring of event pairs per dominant kernel (0 = greedy, 1 = NW, 2 = LEAP), read by gasma_kernel_time_ms
@@ -340,7 +340,7 @@ void gasma_destroy(gasma_ctx* c) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     DevBuf* bufs[] = {&c->g_sums[0], &c->g_sums[1], &c->ops_rows, &c->ops_stage, &c->nops, &c->tile_sums, &c->tile_bases, &c->misc, &c->d_reads, &c->d_refs,
                       &c->d_read_off, &c->d_ref_off, &c->d_cost, &c->d_ops, &c->d_op_off, &c->d_p0, &c->d_p1, &c->gen_len, &c->d_bound, &c->nw_deferred, &c->nw_tb, &c->nw_pool_hi, &c->nw_pool_tb,
-                      &c->bm_hard, &c->bm_gops, &c->bm_goff, &c->bm_nops, &c->bm_noff, &c->bm_gcost, &c->bm_nwpen, &c->bm_counters, &c->bm_answers};
+                      &c->bm_hard, &c->bm_gops, &c->bm_goff, &c->bm_nops, &c->bm_noff, &c->bm_gcost, &c->bm_nwpen, &c->bm_counters, &c->bm_answers, &c->bm_nstage, &c->bm_nnops};
     for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
     if (c->h_misc) cudaFreeHost(c->h_misc);
     for (auto& kind : c->ev) for (auto& pair : kind) for (auto& ev : pair) if (ev) cudaEventDestroy(ev);

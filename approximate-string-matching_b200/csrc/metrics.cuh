@@ -114,10 +114,23 @@ GASMA_HD void runs3_positions(const uint32_t E[NW], const uint32_t B[NW], uint32
         c2 = t3 >> 30;
     }
 }
-// toggles of a CIGAR's qualifying runs (see lcm_positions) in NW words; positions >= 32*NW are dropped
+// mask of the bits below position n of a 32-bit word; n <= 0 gives 0, n >= 32 all ones
+GASMA_HD uint32_t bits_below(int n) {
+#if defined(__CUDA_ARCH__)
+    return __funnelshift_lc(0xFFFFFFFFu, 0u, (uint32_t)imax(n, 0));   // clamps the shift at 32
+#else
+    return n <= 0 ? 0u : (n >= 32 ? 0xFFFFFFFFu : (0xFFFFFFFFu >> (32 - n)));
+#endif
+}
+// Read positions under a CIGAR's qualifying runs (see lcm_positions), straight as NW mask words: a run over the
+// positions [a, z) sets, in word w, the bits below z - 32w that are not below a - 32w.  Every word is addressed by a
+// compile-time index (toggling word a >> 5 of a register array makes the compiler index it at run time, i.e. keep it
+// in local memory).  Positions >= 32*NW are dropped.
 template <int NW>
-GASMA_HD void lcm_toggles(const uint16_t* ops, int nops, int thr, uint32_t t[NW]) {
+GASMA_HD void lcm_mask(const uint16_t* ops, int nops, int thr, uint32_t t[NW]) {
+#if defined(__CUDA_ARCH__)
 #pragma unroll
+#endif
     for (int w = 0; w < NW; ++w) t[w] = 0u;
     int idx = 0;
     for (int oi = 0; oi < nops; ++oi) {
@@ -125,26 +138,12 @@ GASMA_HD void lcm_toggles(const uint16_t* ops, int nops, int thr, uint32_t t[NW]
         if (code == 2) continue;
         if (!(code == 1 || code == 4 || len < thr)) {
             const int a = idx, z = idx + len;
+#if defined(__CUDA_ARCH__)
 #pragma unroll
-            for (int w = 0; w < NW; ++w) {
-                if ((a >> 5) == w) t[w] ^= 1u << (a & 31);
-                if ((z >> 5) == w) t[w] ^= 1u << (z & 31);
-            }
+#endif
+            for (int w = 0; w < NW; ++w) t[w] |= bits_below(z - 32 * w) & ~bits_below(a - 32 * w);
         }
         idx += len;
-    }
-}
-// prefix XOR over all bits: ones between a run's two toggles
-template <int NW>
-GASMA_HD void prefix_xor_fill(uint32_t t[NW]) {
-    uint32_t carry = 0u;
-#pragma unroll
-    for (int w = 0; w < NW; ++w) {
-        uint32_t v = t[w];
-        v ^= v << 1; v ^= v << 2; v ^= v << 4; v ^= v << 8; v ^= v << 16;
-        v ^= carry;
-        carry = (v >> 31) ? 0xFFFFFFFFu : 0u;
-        t[w] = v;
     }
 }
 GASMA_HD int ctz32m(uint32_t x) {  // x != 0

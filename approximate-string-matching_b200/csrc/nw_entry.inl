@@ -103,7 +103,7 @@ int launch_nw_counters_w(gasma_ctx* ctx, const uint8_t* reads, const uint32_t* r
     CU(cudaEventRecord(mev[0], ctx->stream));
     CU(cudaMemsetAsync(dcount, 0, 8, ctx->stream));   // deferred count + hard count (misc[4], misc[5])
     auto tk = nw_band_kernel<W, TT, kNwCounters>;
-    const size_t tsmem = myers_trace_smem_bytes<W>(TT) + kTileGops * sizeof(uint16_t);   // + the tile's greedy ops
+    const size_t tsmem = myers_trace_smem_bytes<W>(TT);
     CU(cudaFuncSetAttribute(tk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsmem));
     tk<<<(unsigned)((n + TT - 1) / TT), TT, tsmem, ctx->stream>>>(reads, roff, refs, foff, (long long)n, gcost, penalty, nullptr, stride,
                                                                 nullptr, (uint32_t*)ctx->nw_deferred.p, dcount, misc, ca);
@@ -124,27 +124,32 @@ int launch_nw_counters_w(gasma_ctx* ctx, const uint8_t* reads, const uint32_t* r
     return GASMA_OK;
 }
 
+// The greedy CIGAR is read from the staging rows the greedy step of the same context just filled (rows_only mode of
+// greedy_dev_impl): ctx->ops_rows / ops_stage / nops.  The verifier's own rows for deferred pairs go to bm_nstage.
 int nw_counters_dev_impl(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_read_off, const char* d_refs,
                          const uint32_t* d_ref_off, int64_t n, const int32_t* d_gcost, int32_t* d_penalty,
-                         const gasma_cigar_op* d_gops, const uint32_t* d_goff, const int32_t* d_answers, uint64_t* d_counters) {
+                         const int32_t* d_answers, uint64_t* d_counters) {
     const int stride = 2 * ctx->params.max_length + 8;
     int rc;
-    if ((rc = reserve(ctx, ctx->ops_stage, (size_t)n * stride * sizeof(uint16_t)))) return rc;
-    if ((rc = reserve(ctx, ctx->nops, (size_t)n * 4))) return rc;
+    if ((rc = reserve(ctx, ctx->bm_nstage, (size_t)n * stride * sizeof(uint16_t)))) return rc;
+    if ((rc = reserve(ctx, ctx->bm_nnops, (size_t)n * 4))) return rc;
     if ((rc = reserve(ctx, ctx->bm_hard, (size_t)n * (8 * ctx->W + 1) * 4))) return rc;
-    const NwCounterArgs ca{d_gops, d_goff, d_answers, (unsigned long long*)d_counters,
-                           (uint32_t*)ctx->bm_hard.p, (uint32_t*)ctx->misc.p + 5, (uint32_t)n};
+    const NwCounterArgs ca{(const uint16_t*)ctx->ops_rows.p, (const uint16_t*)ctx->ops_stage.p, stride, (const uint32_t*)ctx->nops.p,
+                           d_answers, (unsigned long long*)d_counters,
+                           (uint32_t*)ctx->bm_hard.p, (uint32_t*)ctx->misc.p + 5, (uint32_t)n, (uint32_t*)ctx->misc.p + 6};
     const uint8_t* r = (const uint8_t*)d_reads;
     const uint8_t* f = (const uint8_t*)d_refs;
-    uint16_t* stage = (uint16_t*)ctx->ops_stage.p;
-    uint32_t* nops = (uint32_t*)ctx->nops.p;
+    uint16_t* stage = (uint16_t*)ctx->bm_nstage.p;
+    uint32_t* nops = (uint32_t*)ctx->bm_nnops.p;
     switch (ctx->W) {
-        case 1: return launch_nw_counters_w<1>(ctx, r, d_read_off, f, d_ref_off, n, d_gcost, d_penalty, ca, stage, stride, nops);
-        case 2: return launch_nw_counters_w<2>(ctx, r, d_read_off, f, d_ref_off, n, d_gcost, d_penalty, ca, stage, stride, nops);
-        case 3: return launch_nw_counters_w<3>(ctx, r, d_read_off, f, d_ref_off, n, d_gcost, d_penalty, ca, stage, stride, nops);
-        case 4: return launch_nw_counters_w<4>(ctx, r, d_read_off, f, d_ref_off, n, d_gcost, d_penalty, ca, stage, stride, nops);
+        case 1: rc = launch_nw_counters_w<1>(ctx, r, d_read_off, f, d_ref_off, n, d_gcost, d_penalty, ca, stage, stride, nops); break;
+        case 2: rc = launch_nw_counters_w<2>(ctx, r, d_read_off, f, d_ref_off, n, d_gcost, d_penalty, ca, stage, stride, nops); break;
+        case 3: rc = launch_nw_counters_w<3>(ctx, r, d_read_off, f, d_ref_off, n, d_gcost, d_penalty, ca, stage, stride, nops); break;
+        case 4: rc = launch_nw_counters_w<4>(ctx, r, d_read_off, f, d_ref_off, n, d_gcost, d_penalty, ca, stage, stride, nops); break;
+        default: return fail(ctx, GASMA_E_UNSUPPORTED, "the NW verifier covers max_length <= 256 (the greedy path covers 512 and 1024)");
     }
-    return fail(ctx, GASMA_E_UNSUPPORTED, "the NW verifier covers max_length <= 256 (the greedy path covers 512 and 1024)");
+    if (rc == GASMA_OK) ctx->counter_clean = true;   // the verifier reset the greedy kernel's chunk counter
+    return rc;
 }
 
 int nw_dev_impl(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_read_off, const char* d_refs,

@@ -76,7 +76,11 @@ nw_kernel(int x, int o, int e, const uint8_t* __restrict__ reads, const uint32_t
                 NwScratch S{s_H + tid, s_I + tid, T,
                             ops_stage ? tb + (size_t)(p - first) * BITS * nw_tb_words_fast<W>() : nullptr, nw_tb_words_fast<W>()};
                 pen = nw_forward<W>(x, o, e, A0, A1, B0, B1, m, nn, bd, S);
-                if (ops_stage)
+                if (bound && bound[p] >= 0 && pen > bound[p]) {
+                    // the caller's bound was no upper bound (a banded result above it proves that): nw_wide_kernel
+                    // redoes the pair on the full matrix
+                    deferred[atomicAdd(deferred_count, 1u)] = (uint32_t)p;
+                } else if (ops_stage)
                     cnt = (uint32_t)nw_traceback<W>(A0, A1, B0, B1, m, nn, bd, S, ops_stage + (size_t)p * ops_stride, ops_stride);
             }
         }
@@ -122,10 +126,16 @@ nw_wide_kernel(int x, int o, int e, const uint8_t* __restrict__ reads, const uin
 #pragma unroll
             for (int j = 0; j < W; ++j) if (j == (i >> 6)) { B0[j] |= b0 << (i & 63); B1[j] |= b1 << (i & 63); }
         }
-        const NwBand bd = nw_band(m, nn, o, e, bound ? bound[p] : -1);
+        const int bnd = bound ? bound[p] : -1;   // read before penalty[p] is written: the two may alias
+        NwBand bd = nw_band(m, nn, o, e, bnd);
         NwScratch S{pool_hi + (size_t)slot * 2 * HN, pool_hi + (size_t)slot * 2 * HN + HN, 1,
                     ops_stage ? pool_tb + (size_t)slot * BITS * nw_tb_words_wide<W>() : nullptr, nw_tb_words_wide<W>()};
-        penalty[p] = nw_forward<W>(x, o, e, A0, A1, B0, B1, m, nn, bd, S);
+        int pen = nw_forward<W>(x, o, e, A0, A1, B0, B1, m, nn, bd, S);
+        if (bnd >= 0 && pen > bnd) {   // not an upper bound after all: the full matrix decides
+            bd = nw_band(m, nn, o, e, -1);
+            pen = nw_forward<W>(x, o, e, A0, A1, B0, B1, m, nn, bd, S);
+        }
+        penalty[p] = pen;
         if (ops_stage) {
             const int cnt = nw_traceback<W>(A0, A1, B0, B1, m, nn, bd, S, ops_stage + (size_t)p * ops_stride, ops_stride);
             if (nops_out) nops_out[p] = (uint32_t)cnt;
@@ -138,10 +148,16 @@ template <int W>
 __host__ __device__ constexpr size_t myers_smem_bytes(int tile) {
     return 4 * (size_t)stream_elems<W>(tile) * 2 + 2 * (size_t)(tile + 1) * 4 + 64;
 }
-// the banded kernel adds the per-alignment traceback windows: 1/kTraceParts of the 64W columns at a time x 8 bytes
+// The banded kernel needs, per alignment, the traceback windows of one part of the columns plus the checkpoints of
+// the recurrence at the part boundaries (nw_myers.cuh:myers_band_walk).  The 2-bit streams of the tile staging are dead
+// once every thread holds its planes in registers, so both live in the SAME shared memory (one barrier in between).
+template <int W>
+__host__ __device__ constexpr size_t myers_trace_bytes(int tile) {
+    return ((size_t)myers_trace_slots(64 * W) * sizeof(TraceCol) + (size_t)(kTraceParts - 1) * sizeof(BandCk)) * tile;
+}
 template <int W>
 __host__ __device__ constexpr size_t myers_trace_smem_bytes(int tile) {
-    return myers_smem_bytes<W>(tile) + (size_t)myers_trace_slots(64 * W) * sizeof(TraceCol) * tile;
+    return myers_trace_bytes<W>(tile) > myers_smem_bytes<W>(tile) ? myers_trace_bytes<W>(tile) : myers_smem_bytes<W>(tile);
 }
 
 template <int W, int T>
@@ -192,29 +208,33 @@ nw_myers_kernel(const uint8_t* __restrict__ reads, const uint32_t* __restrict__ 
 }
 
 // Banded verifier: one 32-bit window per column (nw_myers.cuh), penalty and traceback in one pass.
-// `bound` is an upper bound on every pair's optimum: the greedy penalty, or the exact optimum from nw_myers_kernel
-// (it may then alias `penalty`).  Pairs whose band has more than 32 diagonals are appended to `deferred` for
-// nw_wide_kernel (general Gotoh, same traceback rule) with their exact optimum in `penalty` as its bound.
+// `bound` is MEANT to be an upper bound on every pair's optimum: the greedy penalty, or the exact optimum from
+// nw_myers_kernel (it may then alias `penalty`).  It is not trusted: the greedy penalty is no upper bound in
+// SEMI_GLOBAL mode or when |n-m| > k (the out-of-band destination lane counts no hurdles).  A valid bound gives a
+// banded result <= bound and an invalid one a result > bound (the banded value is the cost of a real path), so
+// `result > bound` is a complete test; such a pair is redone inside the band of its exact optimum (full columns).
+// Pairs whose band has more than 32 diagonals even then are appended to `deferred` for nw_wide_kernel (general
+// Gotoh, same traceback rule) with their exact optimum in `penalty` as its bound.
 //   MODE 0: penalty only (no shared-memory windows)
 //   MODE 1: penalty + CIGAR ops into the pair's staging row (back to front) + nops_out
 //   MODE 2: penalty + the benchmark's counters (metrics.cuh): the walk hands its '=' steps to the coverage test
-//           as bit masks, no NW CIGAR is written.  bound = the greedy penalty, g_ops/g_off = the greedy CIGAR CSR.
+//           as bit masks, no NW CIGAR is written.  bound = the greedy penalty; the greedy CIGAR is read where the
+//           greedy kernel left it (32-byte primary rows, overflow rows; greedy.cuh:OpSink) -- no CSR in between.
 //           A deferred pair is not counted here: nw_wide_kernel writes its CIGAR and
 //           nw_deferred_counters_kernel counts it from there.
 constexpr int kNwPenalty = 0, kNwOps = 1, kNwCounters = 2;
-// MODE 2 keeps the greedy CIGAR ops of the tile's pairs (one contiguous CSR range) in shared memory, copied with
-// coalesced loads next to the tile staging: the per-pair loop over them then runs on shared-memory latency instead
-// of one dependent L2 round trip per op at a handful of active threads.  A tile with more ops reads them from global.
-constexpr int kTileGops = 512;
 
 struct NwCounterArgs {
-    const uint16_t* g_ops;        // greedy CIGAR (CSR)
-    const uint32_t* g_off;
+    const uint16_t* g_rows;       // greedy CIGAR: primary rows [n][kRowPitch]
+    const uint16_t* g_ovf;        // overflow rows [n][g_stride], complete lists of the pairs with more than kRowKeep ops
+    int g_stride;
+    const uint32_t* g_nops;       // ops per pair
     const int32_t* answers;       // optional (read_answer_file); INT32_MIN or null = use the NW penalty
     unsigned long long* counters; // total, nw_correct, greedy_correct, greedy_coverage
     uint32_t* hard;               // [8W+1][hard_cap]: pairs whose coverage needs the sequential test (cover_hard_kernel)
     uint32_t* hard_count;
     uint32_t hard_cap;
+    uint32_t* reset_word;         // optional: set to 0 (the greedy kernel's chunk counter, for the next batch)
 };
 
 template <int W, int T, int MODE>
@@ -227,27 +247,21 @@ nw_band_kernel(const uint8_t* __restrict__ reads, const uint32_t* __restrict__ r
     constexpr int BITS = 64 * W;
     constexpr bool TRACE = MODE != kNwPenalty;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    TraceCol* s_tb = reinterpret_cast<TraceCol*>(smem_raw);                       // [col][T]
-    uint16_t* s_r0 = reinterpret_cast<uint16_t*>(s_tb + (TRACE ? (size_t)myers_trace_slots(BITS) * T : 0));
+    // phase A view: tile staging
+    uint16_t* s_r0 = reinterpret_cast<uint16_t*>(smem_raw);
     uint16_t* s_r1 = s_r0 + stream_elems<W>(T);
     uint16_t* s_f0 = s_r1 + stream_elems<W>(T);
     uint16_t* s_f1 = s_f0 + stream_elems<W>(T);
     uint32_t* s_roff = reinterpret_cast<uint32_t*>(s_f1 + stream_elems<W>(T));
     uint32_t* s_foff = s_roff + (T + 1);
-    uint16_t* s_gops = reinterpret_cast<uint16_t*>(s_foff + (T + 1));   // MODE 2 only (kTileGops entries)
+    // phase B view (after the barrier below): traceback windows [slot][T], checkpoints [part][T]
+    TraceCol* s_tb = reinterpret_cast<TraceCol*>(smem_raw);
+    BandCk* s_ck = reinterpret_cast<BandCk*>(s_tb + (size_t)myers_trace_slots(BITS) * T);
 
     const int tid = threadIdx.x;
     const long long p0 = (long long)blockIdx.x * T;
     const int np = (int)((n - p0) < (long long)T ? (n - p0) : (long long)T);
-    uint32_t g_lo = 0u;
-    bool gops_staged = false;
-    if (MODE == kNwCounters) {
-        g_lo = ca.g_off[p0];
-        const uint32_t g_cnt = ca.g_off[p0 + np] - g_lo;
-        gops_staged = g_cnt <= (uint32_t)kTileGops;
-        if (gops_staged)
-            for (uint32_t i = tid; i < g_cnt; i += T) s_gops[i] = ca.g_ops[g_lo + i];
-    }
+    if (MODE == kNwCounters && blockIdx.x == 0 && tid == 0 && ca.reset_word) *ca.reset_word = 0u;
     for (int i = tid; i <= np; i += T) { s_roff[i] = read_off[p0 + i]; s_foff[i] = ref_off[p0 + i]; }
     for (int i = tid; i < stream_elems<W>(T); i += T) { s_r0[i] = 0; s_r1[i] = 0; s_f0[i] = 0; s_f1[i] = 0; }
     __syncthreads();
@@ -258,44 +272,64 @@ nw_band_kernel(const uint8_t* __restrict__ reads, const uint32_t* __restrict__ r
 
     uint32_t st = 0;
     uint32_t c_tot = 0, c_nw = 0, c_gr = 0, c_cov = 0;   // MODE 2
+    const long long p = p0 + tid;
+    int m = 0, nn = 0, bnd = INT32_MIN;
+    uint64_t A0[W], A1[W], B0[W], B1[W];
+    bool live = false;
     if (tid < np) {
-        const long long p = p0 + tid;
-        const int m = (int)(s_roff[tid + 1] - s_roff[tid]);
-        const int nn = (int)(s_foff[tid + 1] - s_foff[tid]);
+        m = (int)(s_roff[tid + 1] - s_roff[tid]);
+        nn = (int)(s_foff[tid + 1] - s_foff[tid]);
         if (!ok) st |= kStatusTile;
         if (m > BITS || nn > BITS) st |= kStatusLength;
-        const int bnd = bound[p];
-        int cnt = 0;
-        if (st != 0 || bnd == INT32_MIN) {   // INT32_MIN: rejected by the pass that produced the bound
-            penalty[p] = INT32_MIN;
-        } else {
-            uint64_t A0[W], A1[W], B0[W], B1[W];
+        bnd = bound[p];
+        live = st == 0 && bnd != INT32_MIN;   // INT32_MIN: rejected by the pass that produced the bound
+        if (live) {
             const int rbit = (int)(s_roff[tid] - rbase), fbit = (int)(s_foff[tid] - fbase);
             extract_plane<W>(reinterpret_cast<const uint32_t*>(s_r0), rbit, m, A0);
             extract_plane<W>(reinterpret_cast<const uint32_t*>(s_r1), rbit, m, A1);
             extract_plane<W>(reinterpret_cast<const uint32_t*>(s_f0), fbit, nn, B0);
             extract_plane<W>(reinterpret_cast<const uint32_t*>(s_f1), fbit, nn, B1);
-            NwBand bd = nw_band(m, nn, 1, 1, bnd);
-            if (!myers_band_fits(bd)) {
-                // a loose bound (rare: the greedy penalty is usually close): get the exact optimum from full columns
-                // first; its band is the narrowest there is
-                const int exact = myers_forward<W>(A0, A1, B0, B1, m, nn);
-                bd = nw_band(m, nn, 1, 1, exact);
-                penalty[p] = exact;
+        } else {
+            penalty[p] = INT32_MIN;
+        }
+    }
+    if (TRACE) __syncthreads();   // the streams are dead: their memory becomes the traceback windows
+    int cnt = 0;
+    if (live) {
+        CoverTrace<W> t;
+        OpsBackSink sink{MODE == kNwOps ? ops_stage + (size_t)p * ops_stride + ops_stride : nullptr};
+        uint16_t* const row_end = sink.wp;
+        int bu = bnd < 0 ? 0 : bnd, pen = 0;
+        bool have_exact = false, done = false;
+#pragma unroll 1
+        for (int attempt = 0; attempt < 3 && !done; ++attempt) {
+            const NwBand bd = nw_band(m, nn, 1, 1, bu);
+            if (myers_band_fits(bd)) {
+                if (MODE == kNwCounters) {
+                    pen = myers_band_cover<W>(A0, A1, B0, B1, m, nn, bd.hi, s_tb + tid, T, s_ck + tid, T, t);
+                } else {
+                    sink.wp = row_end;
+                    pen = myers_band_align<W>(A0, A1, B0, B1, m, nn, bd.hi, TRACE ? s_tb + tid : nullptr, T, s_ck + tid, T, sink);
+                }
+                if (pen <= bu) { done = true; break; }   // the bound held: pen is the optimum
+            } else if (have_exact) {
+                break;   // even the narrowest band is too wide for the window
             }
-            if (!myers_band_fits(bd)) {
-                deferred[atomicAdd(deferred_count, 1u)] = (uint32_t)p;   // nw_wide_kernel, bounded by penalty[p]
-            } else if (MODE == kNwCounters) {
-                CoverTrace<W> t;
-                const int pen = myers_band_cover<W>(A0, A1, B0, B1, m, nn, bd.hi, s_tb + tid, T, t);
-                penalty[p] = pen;
+            // a loose bound (band too wide) or an invalid one (result above it): the exact optimum from full columns
+            bu = myers_forward<W>(A0, A1, B0, B1, m, nn);
+            have_exact = true;
+        }
+        if (!done) {
+            penalty[p] = bu;                                         // exact: the bound of nw_wide_kernel
+            deferred[atomicAdd(deferred_count, 1u)] = (uint32_t)p;
+        } else {
+            penalty[p] = pen;
+            cnt = (int)(row_end - sink.wp);
+            if (MODE == kNwCounters) {
                 uint32_t P1[2 * W], P2[2 * W], a0[2 * W], a1[2 * W];
                 runs3_positions<2 * W>(t.E, t.B, P2);                    // LCM2: read positions under '=' runs >= 3
-                const uint32_t g0 = ca.g_off[p];
-                const int gn = (int)(ca.g_off[p + 1] - g0);
-                if (gops_staged) lcm_toggles<2 * W>(s_gops + (g0 - g_lo), gn, 1, P1);
-                else lcm_toggles<2 * W>(ca.g_ops + g0, gn, 1, P1);
-                prefix_xor_fill<2 * W>(P1);                              // LCM1: read positions under greedy M runs
+                const uint32_t gn = ca.g_nops[p];
+                lcm_mask<2 * W>(OpSink::list(ca.g_rows, ca.g_ovf, ca.g_stride, p, gn), (int)gn, 1, P1);   // LCM1: read positions under greedy M runs
 #pragma unroll
                 for (int w = 0; w < W; ++w) {
                     a0[2 * w] = (uint32_t)A0[w]; a0[2 * w + 1] = (uint32_t)(A0[w] >> 32);
@@ -325,15 +359,10 @@ nw_band_kernel(const uint8_t* __restrict__ reads, const uint32_t* __restrict__ r
                     }
                     h[(size_t)(8 * W) * ca.hard_cap] = (uint32_t)m;
                 }
-            } else {
-                OpsBackSink sink{MODE == kNwOps ? ops_stage + (size_t)p * ops_stride + ops_stride : nullptr};
-                const uint16_t* row_end = sink.wp;
-                penalty[p] = myers_band_align<W>(A0, A1, B0, B1, m, nn, bd.hi, TRACE ? s_tb + tid : nullptr, T, sink);
-                cnt = (int)(row_end - sink.wp);
             }
         }
-        if (MODE == kNwOps) nops_out[p] = (uint32_t)cnt;
     }
+    if (MODE == kNwOps && tid < np) nops_out[p] = (uint32_t)cnt;
     const uint32_t wst = __reduce_or_sync(0xffffffffu, st);
     if (wst && (tid & 31) == 0) atomicOr(status, wst);
     if (MODE == kNwCounters) {
@@ -388,8 +417,8 @@ nw_deferred_counters_kernel(const uint8_t* __restrict__ reads, const uint32_t* _
         const int pen = penalty[p];
         const int correct = (ca.answers && ca.answers[p] != INT32_MIN) ? ca.answers[p] : pen;
         uint32_t scratch[2 * kCovWords];
-        const uint32_t r0 = read_off[p], g0 = ca.g_off[p], cnt = n_cnt[p];
-        const int cov = coverage_pair(reads + r0, (int)(read_off[p + 1] - r0), ca.g_ops + g0, (int)(ca.g_off[p + 1] - g0),
+        const uint32_t r0 = read_off[p], gn = ca.g_nops[p], cnt = n_cnt[p];
+        const int cov = coverage_pair(reads + r0, (int)(read_off[p + 1] - r0), OpSink::list(ca.g_rows, ca.g_ovf, ca.g_stride, p, gn), (int)gn,
                                       n_stage + (size_t)p * ops_stride + (ops_stride - cnt), (int)cnt, scratch, 1);
         atomicAdd(&ca.counters[0], 1ull);
         atomicAdd(&ca.counters[1], (unsigned long long)(pen == correct));

@@ -94,20 +94,29 @@ GASMA_HD int myers_forward(const uint64_t A0[W], const uint64_t A1[W], const uin
 #pragma unroll
     for (int w = 0; w < NW32; ++w) { pv[w] = 0xFFFFFFFFu; mv[w] = 0u; }
     int score = m;
-    uint64_t b0 = 0, b1 = 0;
-    for (int j = 0; j < n; ++j) {
-        if ((j & 63) == 0) {   // next 64 reference characters
+    // 64 reference characters per block; the block loop is unrolled so that B0[q] / B1[q] have compile-time indices
+    // (a run-time index would put every plane array of the calling kernel into local memory)
+#if defined(__CUDA_ARCH__)
 #pragma unroll
-            for (int q = 0; q < W; ++q)
-                if (q == (j >> 6)) { b0 = B0[q]; b1 = B1[q]; }
+#endif
+    for (int q = 0; q < W; ++q) {
+        if (64 * q >= n) continue;
+        uint64_t b0 = B0[q], b1 = B1[q];
+        const int jend = imin(64, n - 64 * q);
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1
+#endif
+        for (int j = 0; j < jend; ++j) {
+            const uint32_t k0 = (uint32_t)0 - (uint32_t)(b0 & 1ull), k1 = (uint32_t)0 - (uint32_t)(b1 & 1ull);
+            b0 >>= 1;
+            b1 >>= 1;
+            uint32_t eq[NW32], dg[NW32];
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+            for (int w = 0; w < NW32; ++w) eq[w] = ~(a0[w] ^ k0) & ~(a1[w] ^ k1);
+            score += myers_column<NW32>(eq, pv, mv, dg, m);   // dg is dead here and compiled away
         }
-        const uint32_t k0 = (uint32_t)0 - (uint32_t)(b0 & 1ull), k1 = (uint32_t)0 - (uint32_t)(b1 & 1ull);
-        b0 >>= 1;
-        b1 >>= 1;
-        uint32_t eq[NW32], dg[NW32];
-#pragma unroll
-        for (int w = 0; w < NW32; ++w) eq[w] = ~(a0[w] ^ k0) & ~(a1[w] ^ k1);
-        score += myers_column<NW32>(eq, pv, mv, dg, m);   // dg is dead here and compiled away
     }
     return score;
 }
@@ -141,11 +150,21 @@ GASMA_HD uint32_t word32_of(const uint64_t v[W], int w) {   // 32-bit word w of 
         if (j == (w >> 1)) x = v[j];
     return (uint32_t)(x >> ((w & 1) * 32));
 }
+// 32-bit word w of the vector for a COMPILE-TIME w (callers unroll): no run-time index into the register array
+template <int W>
+GASMA_HD uint32_t half32(const uint64_t v[W], int w) { return (uint32_t)(v[w >> 1] >> ((w & 1) * 32)); }
 GASMA_HD uint32_t funnel32_l(uint32_t lo, uint32_t hi, int s) {  // high word of (hi:lo) << s, 0 <= s < 32
 #if defined(__CUDA_ARCH__)
     return __funnelshift_l(lo, hi, s);
 #else
     return (uint32_t)(((((uint64_t)hi << 32) | lo) << s) >> 32);
+#endif
+}
+GASMA_HD int popc32m(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+    return __popc(x);
+#else
+    return __builtin_popcount(x);
 #endif
 }
 GASMA_HD uint32_t brev32(uint32_t x) {
@@ -163,27 +182,46 @@ GASMA_HD uint32_t brev32(uint32_t x) {
 // does the band of `bound` fit the 32-bit window?  (hi - 31 <= lo: the window then covers the whole band)
 GASMA_HD bool myers_band_fits(const NwBand& bd) { return bd.hi - bd.lo + 1 <= 32; }
 
-// Columns [1, j_end] of the banded matrix (1-based; j_end <= n).  When tb != nullptr the windows of the columns
-// j > j_store are kept at slot j - 1 - j_store.  Returns H[m][j_end] (meaningful when row m is inside the last
-// window, which it is for j_end == n).
+// State of the banded recurrence between two columns: the vertical deltas of the window (pv / mv) and the number of
+// free diagonal steps its top cell has taken so far.  Column 0: H(i,0) = |i| -> +1 below row 0, -1 at and above it;
+// bit b of the window of column j is row j - hi + b.
+struct BandCols {
+    uint32_t pv, mv;
+    int diag0;
+};
+GASMA_HD BandCols myers_band_start(int hi) {
+    const uint32_t pv = hi >= 31 ? 0u : 0xFFFFFFFFu << (hi + 1);
+    return BandCols{pv, ~pv, 0};
+}
+
+// Columns j_begin+1 .. j_end (1-based) of the banded matrix, continuing from the state `c` left after column j_begin
+// (myers_band_start for j_begin == 0).  When tb != nullptr the windows of these columns are kept at slots 0, 1, ...
+// (slot s = column j_begin + 1 + s).  Resumable at any column, so a caller can checkpoint `c` and recompute a range
+// of columns later without starting from column 0.
 template <int W>
-GASMA_HD int myers_band_forward(const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W], const uint64_t B1[W],
-                                int m, int hi, int j_store, int j_end, TraceCol* tb, int stride) {
-    // column 0: H(i,0) = |i|  ->  +1 below row 0, -1 at and above it; bit b is row b - hi
-    uint32_t pv = hi >= 31 ? 0u : 0xFFFFFFFFu << (hi + 1);
-    uint32_t mv = ~pv;
-    int diag0 = 0;   // zero-cost diagonal steps of the window's top cell
-    // read planes shifted up by hi, so that the window of (0-based) column c is bits [c, c+32) of the shifted plane
-    uint32_t c0 = word32_of<W>(A0, 0), c1 = word32_of<W>(A1, 0);
-    uint32_t wl0 = funnel32_l(0u, c0, hi), wl1 = funnel32_l(0u, c1, hi);
+GASMA_HD void myers_band_run(const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W], const uint64_t B1[W], int hi,
+                             int j_begin, int j_end, BandCols& c, TraceCol* tb, int stride) {
+    uint32_t pv = c.pv, mv = c.mv;
+    int diag0 = c.diag0;
     TraceCol* out = tb;
-    for (int cb = 0; 32 * cb < j_end; ++cb) {
-        const uint32_t n0 = word32_of<W>(A0, cb + 1), n1 = word32_of<W>(A1, cb + 1);
-        const uint32_t wh0 = funnel32_l(c0, n0, hi), wh1 = funnel32_l(c1, n1, hi);
-        c0 = n0; c1 = n1;
-        uint32_t r0 = brev32(word32_of<W>(B0, cb)), r1 = brev32(word32_of<W>(B1, cb));   // next ref character in bit 31
-        const int cend = imin(32, j_end - 32 * cb);
-        for (int s = 0; s < cend; ++s) {
+    // One 32-column block at a time.  The loop over blocks is unrolled with a range test per block so that every plane
+    // word is named by a compile-time index: a run-time index would put the plane arrays into local memory.
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (int cb = 0; cb < 2 * W; ++cb) {
+        if (32 * cb >= j_end || 32 * (cb + 1) <= j_begin) continue;
+        const int s0 = imax(j_begin - 32 * cb, 0), cend = imin(32, j_end - 32 * cb);
+        // read planes shifted up by hi, so that the window of (0-based) column q is bits [q, q+32) of the shifted plane
+        const uint32_t al0 = cb > 0 ? half32<W>(A0, cb - 1) : 0u, am0 = half32<W>(A0, cb), ah0 = cb + 1 < 2 * W ? half32<W>(A0, cb + 1) : 0u;
+        const uint32_t al1 = cb > 0 ? half32<W>(A1, cb - 1) : 0u, am1 = half32<W>(A1, cb), ah1 = cb + 1 < 2 * W ? half32<W>(A1, cb + 1) : 0u;
+        const uint32_t wl0 = funnel32_l(al0, am0, hi), wh0 = funnel32_l(am0, ah0, hi);
+        const uint32_t wl1 = funnel32_l(al1, am1, hi), wh1 = funnel32_l(am1, ah1, hi);
+        uint32_t r0 = brev32(half32<W>(B0, cb)) << s0, r1 = brev32(half32<W>(B1, cb)) << s0;   // next ref character in bit 31
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1
+#endif
+        for (int s = s0; s < cend; ++s) {
             const uint32_t k0 = (uint32_t)((int32_t)r0 >> 31), k1 = (uint32_t)((int32_t)r1 >> 31);
             r0 <<= 1;
             r1 <<= 1;
@@ -197,27 +235,35 @@ GASMA_HD int myers_band_forward(const uint64_t A0[W], const uint64_t A1[W], cons
             mv = php & xv;
             const uint32_t zero = xh | mvi;   // Hyyro's D0: H(i,j) == H(i-1,j-1), i.e. dv + dh' == 0
             diag0 += (int)(zero & 1u);
-            if (tb && 32 * cb + s >= j_store) {
+            if (tb) {
                 const uint32_t dg = eq | ~zero;
                 *out = TraceCol{dg, eq | (~dg & pv)};
                 out += stride;
             }
         }
-        wl0 = wh0; wl1 = wh1;
     }
-    // top cell of the last window: H(-hi,0) = hi, +1 per column unless the diagonal step was free; then down to row m
-    const int b = imax(-1, m - j_end + hi);   // < 0 only in a partial recomputation, whose result is not used
-    const uint32_t mask = (b >= 31 ? 0xFFFFFFFFu : ((1u << (b + 1)) - 1u)) & ~1u;
-    int score = hi + j_end - diag0;
-#if defined(__CUDA_ARCH__)
-    score += __popc(pv & mask) - __popc(mv & mask);
-#else
-    score += __builtin_popcount(pv & mask) - __builtin_popcount(mv & mask);
-#endif
-    return score;
+    c.pv = pv; c.mv = mv; c.diag0 = diag0;
 }
 
-// Resumable walk back: emits runs while j > j_lo (and i > 0), reading the entries stored with base column j_store.
+// H[m][j] from the state after column j (row m must be inside that column's window, which it is for j == n):
+// top cell of the window: H(-hi,0) = hi, +1 per column unless the diagonal step was free; then down to row m.
+GASMA_HD int myers_band_score(const BandCols& c, int m, int j, int hi) {
+    const int b = imax(-1, m - j + hi);
+    const uint32_t mask = (b >= 31 ? 0xFFFFFFFFu : ((1u << (b + 1)) - 1u)) & ~1u;
+    return hi + j - c.diag0 + popc32m(c.pv & mask) - popc32m(c.mv & mask);
+}
+
+// Columns [1, j_end] from column 0 (penalty-only callers).  Returns H[m][j_end].
+template <int W>
+GASMA_HD int myers_band_forward(const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W], const uint64_t B1[W],
+                                int m, int hi, int j_end) {
+    BandCols c = myers_band_start(hi);
+    myers_band_run<W>(A0, A1, B0, B1, hi, 0, j_end, c, nullptr, 0);
+    return myers_band_score(c, m, j_end, hi);
+}
+
+// Resumable walk back: emits runs while j > j_lo (and i > 0), reading the entries of the columns j_lo+1 .. stored at
+// slots 0, 1, ... (slot = column - 1 - j_lo).
 // A finished run goes to the sink: sink.flush(code, length, i) with i = the read row the run started after (walking
 // backwards), i.e. the run covers the 0-based read positions [i, i + rows it consumed).
 struct MyersTrace {
@@ -239,121 +285,152 @@ GASMA_HD void myers_trace_push(MyersTrace& t, Sink& sink, int code, int len) {
     }
     t.run += len;
 }
+// a walker bound to its sink: the part driver below only needs live / col / start / segment / finish
 template <class Sink>
-GASMA_HD void myers_trace_segment(MyersTrace& t, Sink& sink, int j_lo, int j_store, const TraceCol* tb, int stride) {
-    const TraceCol* col = tb + (size_t)(t.j - 1 - j_store) * stride;
-    while (t.i > 0 && t.j > j_lo) {
-        const TraceCol c = *col;
-        const int dg = (int)((c.dg >> (t.b & 31)) & 1u), sel = (int)((c.sel >> (t.b & 31)) & 1u);
-        // dg: '=' (3) / 'X' (4) by sel;  otherwise I (1) when sel (up is optimal), else D (2)
-        myers_trace_push(t, sink, dg ? 4 - sel : 2 - sel, 1);
-        const int di = dg | sel, dj = dg | (sel ^ 1);
-        t.i -= di;
-        t.j -= dj;
-        t.b += dj - di;
-        col -= dj ? stride : 0;
+struct OpsWalker {
+    MyersTrace t;
+    Sink& sink;
+    GASMA_HD bool live() const { return t.i > 0 && t.j > 0; }
+    GASMA_HD int col() const { return t.j; }
+    GASMA_HD void start(int m, int n, int hi) { t = MyersTrace{m, n, m - n + hi, -1, 0}; }
+    GASMA_HD void segment(int j_lo, const TraceCol* tb, int stride) {
+        const TraceCol* col = tb + (size_t)(t.j - 1 - j_lo) * stride;
+        while (t.i > 0 && t.j > j_lo) {
+            const TraceCol c = *col;
+            const int dg = (int)((c.dg >> (t.b & 31)) & 1u), sel = (int)((c.sel >> (t.b & 31)) & 1u);
+            // dg: '=' (3) / 'X' (4) by sel;  otherwise I (1) when sel (up is optimal), else D (2)
+            myers_trace_push(t, sink, dg ? 4 - sel : 2 - sel, 1);
+            const int di = dg | sel, dj = dg | (sel ^ 1);
+            t.i -= di;
+            t.j -= dj;
+            t.b += dj - di;
+            col -= dj ? stride : 0;
+        }
     }
-}
-// the boundary tail (first row / first column) and the flush of the last run
-template <class Sink>
-GASMA_HD void myers_trace_finish(MyersTrace& t, Sink& sink) {
-    if (t.i > 0) { myers_trace_push(t, sink, 1, t.i); t.i = 0; }
-    if (t.j > 0) myers_trace_push(t, sink, 2, t.j);
-    myers_trace_push(t, sink, -2, 0);
-}
-
-// Penalty and (when tb != nullptr) traceback of one alignment whose band fits the window.  Only 1/kTraceParts of the
-// columns is resident at a time: the last part is stored and walked first, then the columns below are recomputed
-// part by part into the same slots ((kTraceParts+1)/2 x the column work for 1/kTraceParts of the shared memory,
-// i.e. that many more alignments in flight per SM).  tb holds myers_trace_slots(n) entries per alignment.
-// Returns the penalty; the runs of the walk go to `sink`.
-#ifndef GASMA_TRACE_PARTS
-#define GASMA_TRACE_PARTS 3
-#endif
-constexpr int kTraceParts = GASMA_TRACE_PARTS;
-GASMA_HD int myers_part_start(int n, int part) { return (int)((long long)n * part / kTraceParts); }
-GASMA_HD constexpr int myers_trace_slots(int max_n) { return (max_n + kTraceParts - 1) / kTraceParts; }
-template <int W, class Sink>
-GASMA_HD int myers_band_align(const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W], const uint64_t B1[W],
-                              int m, int n, int hi, TraceCol* tb, int stride, Sink& sink) {
-    if (m == 0 || n == 0) {
-        if (tb) { MyersTrace t{m, n, 0, -1, 0}; myers_trace_finish(t, sink); }
-        return imax(m, n);
+    // the boundary tail (first row / first column) and the flush of the last run
+    GASMA_HD void finish() {
+        if (t.i > 0) { myers_trace_push(t, sink, 1, t.i); t.i = 0; }
+        if (t.j > 0) myers_trace_push(t, sink, 2, t.j);
+        myers_trace_push(t, sink, -2, 0);
     }
-    if (!tb) return myers_band_forward<W>(A0, A1, B0, B1, m, hi, 0, n, nullptr, 0);
-    MyersTrace t{m, n, m - n + hi, -1, 0};
-    int pen = 0;
-#pragma unroll
-    for (int part = kTraceParts - 1; part >= 0; --part) {
-        if (!(t.i > 0 && t.j > 0)) break;
-        const int lo = myers_part_start(n, part);
-        const int h = myers_band_forward<W>(A0, A1, B0, B1, m, hi, lo, t.j, tb, stride);   // t.j == n the first time
-        if (part == kTraceParts - 1) pen = h;
-        myers_trace_segment(t, sink, lo, lo, tb, stride);
-    }
-    myers_trace_finish(t, sink);
-    return pen;
-}
+};
 
 // ---- the walk without a CIGAR: what the coverage counter needs from it, as bit masks over read positions ----
 // benchmark_coverage.h:26-67 with threshold 3 keeps the read positions under '=' runs of length >= 3.  The walk
 // consumes the read rows in descending order, so it just records, per consumed row p (0-based position),
 //   E[p] = the row was consumed by an '=' step,   B[p] = a D step happened between row p and the row above it
 // (a D does not consume a row but ends a run), 32 positions per word, accumulated in registers and flushed when a
-// word is complete.  No run lengths, no per-run branches; metrics.cuh:runs3_positions turns E, B into the positions.
+// word is complete (a statically unrolled select: a dynamically indexed register array would live in local memory).
+// No run lengths, no per-run branches; metrics.cuh:runs3_positions turns E, B into the positions.
 template <int W>
 struct CoverTrace {
     int i, j, b;
     uint32_t e, brk;       // word under construction
     uint32_t pend;         // a D step since the last consumed row
     uint32_t E[2 * W], B[2 * W];
-};
-template <int W>
-GASMA_HD void myers_cover_segment(CoverTrace<W>& t, int j_lo, int j_store, const TraceCol* tb, int stride) {
-    const TraceCol* col = tb + (size_t)(t.j - 1 - j_store) * stride;
-    while (t.i > 0 && t.j > j_lo) {
-        const TraceCol c = *col;
-        const uint32_t dg = (c.dg >> (t.b & 31)) & 1u, sel = (c.sel >> (t.b & 31)) & 1u;
-        const uint32_t di = dg | sel, dj = dg | (sel ^ 1u);   // diagonal: both; up (I): row only; left (D): column only
-        const int p = t.i - 1;
-        const uint32_t bit = di << (p & 31);
-        t.e |= (dg & sel) ? bit : 0u;
-        t.brk |= t.pend ? bit : 0u;
-        t.pend = di ^ 1u;
-        if (di && (p & 31) == 0) {
-            t.E[p >> 5] = t.e;
-            t.B[p >> 5] = t.brk;
-            t.e = t.brk = 0u;
-        }
-        t.i -= (int)di;
-        t.j -= (int)dj;
-        t.b += (int)dj - (int)di;
-        col -= dj ? stride : 0;
+    GASMA_HD bool live() const { return i > 0 && j > 0; }
+    GASMA_HD int col() const { return j; }
+    GASMA_HD void start(int m, int n, int hi) {
+        i = m; j = n; b = m - n + hi;
+        e = brk = pend = 0u;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+        for (int w = 0; w < 2 * W; ++w) { E[w] = 0u; B[w] = 0u; }
     }
+    GASMA_HD void land(int w) {   // the word under construction is word w
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+        for (int q = 0; q < 2 * W; ++q)
+            if (q == w) { E[q] = e; B[q] = brk; }
+        e = brk = 0u;
+    }
+    GASMA_HD void segment(int j_lo, const TraceCol* tb, int stride) {
+        const TraceCol* col = tb + (size_t)(j - 1 - j_lo) * stride;
+        while (i > 0 && j > j_lo) {
+            const TraceCol c = *col;
+            const uint32_t dg = (c.dg >> (b & 31)) & 1u, sel = (c.sel >> (b & 31)) & 1u;
+            const uint32_t di = dg | sel, dj = dg | (sel ^ 1u);   // diagonal: both; up (I): row only; left (D): column only
+            const int p = i - 1;
+            const uint32_t bit = di << (p & 31);
+            e |= (dg & sel) ? bit : 0u;
+            brk |= pend ? bit : 0u;
+            pend = di ^ 1u;
+            if (di && (p & 31) == 0) land(p >> 5);
+            i -= (int)di;
+            j -= (int)dj;
+            b += (int)dj - (int)di;
+            col -= dj ? stride : 0;
+        }
+    }
+    GASMA_HD void finish() {
+        if (i > 0) land((i - 1) >> 5);   // rows left at column 0 are an I run; the word under construction still has to land
+    }
+};
+
+// Penalty and walk of one alignment whose band fits the window.  Only 1/kTraceParts of the columns is resident at a
+// time (tb holds myers_trace_slots(n) entries per alignment).  Pass 1 runs the columns once, part by part, leaving a
+// checkpoint of the recurrence (8 bytes) at every part boundary and keeping only the last part's windows; that part
+// is walked, then each earlier part is recomputed FROM ITS CHECKPOINT into the same slots and walked.  Column work:
+// n + n(K-1)/K instead of the n(K+1)/2 of recomputing from column 0, so K can be large: shared memory per alignment
+// is 8(ceil(n/K) + K - 1) bytes and that, not the column work, decides how many alignments an SM holds.
+// ck: K-1 checkpoints, entry p-1 (state before part p) at ck[(p-1) * ck_stride].  One rolled loop over the 2K-1
+// tasks keeps a single instance of the column code in the kernel.
+#ifndef GASMA_TRACE_PARTS
+#define GASMA_TRACE_PARTS 6
+#endif
+constexpr int kTraceParts = GASMA_TRACE_PARTS;
+GASMA_HD int myers_part_start(int n, int part) { return (int)((long long)n * part / kTraceParts); }
+GASMA_HD constexpr int myers_trace_slots(int max_n) { return (max_n + kTraceParts - 1) / kTraceParts; }
+struct alignas(8) BandCk { uint32_t pv, mv; };   // the diagonal-step count is only needed by the first pass (score)
+template <int W, class Walker>
+GASMA_HD int myers_band_walk(const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W], const uint64_t B1[W],
+                             int m, int n, int hi, TraceCol* tb, int stride, BandCk* ck, int ck_stride, Walker& wk) {
+    constexpr int K = kTraceParts;
+    wk.start(m, n, hi);
+    if (m == 0 || n == 0) { wk.finish(); return imax(m, n); }
+    BandCols c = myers_band_start(hi);
+    int pen = 0;
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1
+#endif
+    for (int task = 0; task < 2 * K - 1; ++task) {
+        const bool first_pass = task < K;
+        const int part = first_pass ? task : 2 * K - 2 - task;
+        const int lo = myers_part_start(n, part);
+        int end;
+        if (first_pass) {
+            end = myers_part_start(n, part + 1);
+            if (part > 0) ck[(size_t)(part - 1) * ck_stride] = BandCk{c.pv, c.mv};
+        } else {
+            if (!wk.live()) break;
+            end = wk.col();   // <= the start of the part walked before: the walk may have gone past its first columns
+            if (part > 0) { const BandCk k = ck[(size_t)(part - 1) * ck_stride]; c = BandCols{k.pv, k.mv, 0}; }
+            else c = myers_band_start(hi);
+        }
+        const bool store = task >= K - 1;
+        myers_band_run<W>(A0, A1, B0, B1, hi, lo, end, c, store ? tb : nullptr, stride);
+        if (task == K - 1) pen = myers_band_score(c, m, n, hi);
+        if (store) wk.segment(lo, tb, stride);
+    }
+    wk.finish();
+    return pen;
 }
-// Penalty + E/B masks of one alignment whose band fits the window (same part-resident scheme as myers_band_align).
+
+// penalty + CIGAR ops (tb == nullptr: penalty only)
+template <int W, class Sink>
+GASMA_HD int myers_band_align(const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W], const uint64_t B1[W],
+                              int m, int n, int hi, TraceCol* tb, int stride, BandCk* ck, int ck_stride, Sink& sink) {
+    if (!tb) return (m == 0 || n == 0) ? imax(m, n) : myers_band_forward<W>(A0, A1, B0, B1, m, hi, n);
+    OpsWalker<Sink> wk{MyersTrace{}, sink};
+    return myers_band_walk<W>(A0, A1, B0, B1, m, n, hi, tb, stride, ck, ck_stride, wk);
+}
+// penalty + E/B masks
 template <int W>
 GASMA_HD int myers_band_cover(const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W], const uint64_t B1[W],
-                              int m, int n, int hi, TraceCol* tb, int stride, CoverTrace<W>& t) {
-    t.i = m; t.j = n; t.b = m - n + hi;
-    t.e = t.brk = t.pend = 0u;
-#pragma unroll
-    for (int w = 0; w < 2 * W; ++w) { t.E[w] = 0u; t.B[w] = 0u; }
-    if (m == 0 || n == 0) return imax(m, n);   // only I or only D: no '=' at all
-    int pen = 0;
-#pragma unroll
-    for (int part = kTraceParts - 1; part >= 0; --part) {
-        if (!(t.i > 0 && t.j > 0)) break;
-        const int lo = myers_part_start(n, part);
-        const int h = myers_band_forward<W>(A0, A1, B0, B1, m, hi, lo, t.j, tb, stride);
-        if (part == kTraceParts - 1) pen = h;
-        myers_cover_segment<W>(t, lo, lo, tb, stride);
-    }
-    if (t.i > 0) {   // rows left at column 0 are an I run; the word under construction still has to land
-        t.E[(t.i - 1) >> 5] = t.e;
-        t.B[(t.i - 1) >> 5] = t.brk;
-    }
-    return pen;
+                              int m, int n, int hi, TraceCol* tb, int stride, BandCk* ck, int ck_stride, CoverTrace<W>& t) {
+    return myers_band_walk<W>(A0, A1, B0, B1, m, n, hi, tb, stride, ck, ck_stride, t);
 }
 
 }  // namespace gasma

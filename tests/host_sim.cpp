@@ -176,7 +176,9 @@ int sim_myers(const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, c
     constexpr int BITS = 64 * W;
     int64_t nwin = 0;
     std::vector<uint16_t> r0(elems<W>(T)), r1(elems<W>(T)), f0(elems<W>(T)), f1(elems<W>(T));
-    std::vector<TraceCol> tb((size_t)BITS);
+    // exactly the kernel's budget: one part of the columns resident + the checkpoints at the part boundaries
+    std::vector<TraceCol> tb((size_t)myers_trace_slots(BITS));
+    std::vector<BandCk> ck((size_t)kTraceParts);
     std::vector<uint32_t> tbw((size_t)BITS * ((2 * BITS + 1 + 7) / 8));
     std::vector<int32_t> H(2 * BITS + 2), I(2 * BITS + 2);
     for (int64_t p0 = 0; p0 < n; p0 += T) {
@@ -209,7 +211,7 @@ int sim_myers(const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, c
             if (myers_band_fits(bd)) {
                 ++nwin;
                 OpsBackSink sink{row ? row + stride : nullptr};
-                const int pen = myers_band_align<W>(A0, A1, B0, B1, m, nn, bd.hi, ops_stage ? tb.data() : nullptr, 1, sink);
+                const int pen = myers_band_align<W>(A0, A1, B0, B1, m, nn, bd.hi, ops_stage ? tb.data() : nullptr, 1, ck.data(), 1, sink);
                 if (full >= 0 && pen != full) return -2;
                 penalty[p] = pen;
                 if (ops_stage) nops[p] = (uint32_t)(row + stride - sink.wp);
@@ -236,7 +238,8 @@ int sim_counters(const uint8_t* reads, const uint32_t* roff, const uint8_t* refs
     constexpr int BITS = 64 * W;
     const int stride = 2 * BITS + 8;
     std::vector<uint16_t> r0(elems<W>(T)), r1(elems<W>(T)), f0(elems<W>(T)), f1(elems<W>(T)), row(stride);
-    std::vector<TraceCol> tb((size_t)BITS);
+    std::vector<TraceCol> tb((size_t)myers_trace_slots(BITS));
+    std::vector<BandCk> ck((size_t)kTraceParts);
     std::vector<uint32_t> tbw((size_t)BITS * ((2 * BITS + 1 + 7) / 8));
     std::vector<int32_t> H(2 * BITS + 2), I(2 * BITS + 2);
     int64_t ndef = 0;
@@ -260,11 +263,10 @@ int sim_counters(const uint8_t* reads, const uint32_t* roff, const uint8_t* refs
             int pen, cov;
             if (myers_band_fits(bd)) {
                 CoverTrace<W> ct;
-                pen = myers_band_cover<W>(A0, A1, B0, B1, m, nn, bd.hi, tb.data(), 1, ct);
+                pen = myers_band_cover<W>(A0, A1, B0, B1, m, nn, bd.hi, tb.data(), 1, ck.data(), 1, ct);
                 uint32_t P1[2 * W], P2[2 * W], a0[2 * W], a1[2 * W];
                 runs3_positions<2 * W>(ct.E, ct.B, P2);
-                lcm_toggles<2 * W>(gops + goff[p], (int)(goff[p + 1] - goff[p]), 1, P1);
-                prefix_xor_fill<2 * W>(P1);
+                lcm_mask<2 * W>(gops + goff[p], (int)(goff[p + 1] - goff[p]), 1, P1);   // LCM1: read positions under greedy M runs
                 for (int w = 0; w < W; ++w) {
                     a0[2 * w] = (uint32_t)A0[w]; a0[2 * w + 1] = (uint32_t)(A0[w] >> 32);
                     a1[2 * w] = (uint32_t)A1[w]; a1[2 * w + 1] = (uint32_t)(A1[w] >> 32);
