@@ -45,7 +45,7 @@ EXPORTS = [
     "gasma_nw_batch", "gasma_nw_batch_dev", "gasma_metrics_dev",
     "gasma_generate_ref_capacity", "gasma_generate_dev", "gasma_generate", "gasma_render_cigar",
     "gasma_benchmark_batch", "gasma_benchmark_batch_dev", "gasma_leap_batch", "gasma_leap_batch_dev",
-    "gasma_greedy_batch_dev_noalloc",
+    "gasma_greedy_batch_dev_noalloc", "gasma_set_mask_variant",
 ]
 
 _lib = None
@@ -70,6 +70,7 @@ def lib():
     L.gasma_last_error.restype = C.c_char_p
     L.gasma_set_band.argtypes = [vp, i32]
     L.gasma_set_correction.argtypes = [vp, i32, i32]
+    L.gasma_set_mask_variant.argtypes = [vp, i32]
     L.gasma_set_stream.argtypes = [vp, vp]
     L.gasma_synchronize.argtypes = [vp]
     L.gasma_launch_count.argtypes = [vp]
@@ -158,6 +159,10 @@ class Aligner:
         """The reference's -DCORRECTION band (hurdle_matrix.h:634-641): lanes widened towards lane n-m; max_delta =
         largest |ref_len - read_len| the context keeps lane slots for."""
         self._check(self._L.gasma_set_correction(self._ctx, 1 if enabled else 0, max_delta))
+
+    def set_mask_variant(self, variant):
+        """0 = flip_short_hurdles(1) (as shipped), 1 = flip_short_hurdles(2), 2 = + flip_short_matches(1) (utils.h:200-240)."""
+        self._check(self._L.gasma_set_mask_variant(self._ctx, variant))
 
     def set_stream(self, cuda_stream_ptr):
         self._check(self._L.gasma_set_stream(self._ctx, C.c_void_p(cuda_stream_ptr)))

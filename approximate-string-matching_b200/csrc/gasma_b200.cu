@@ -41,6 +41,7 @@ struct gasma_ctx {
     int greedy_warps = 0;       // warps per CTA of the thread-per-pair greedy kernel: 0 = most resident warps (env GASMA_GREEDY_WARPS: 2, 4, 8)
     bool counter_clean = false;  // the greedy kernel's chunk counter is 0 (left so by scan_tiles_kernel of the previous batch)
     int auto_warps = 0;         // the choice made for the current (W, lanes); reset by derive()
+    int mask_variant = 0;       // gasma_set_mask_variant: 0 flip_short_hurdles(1), 1 flip_short_hurdles(2), 2 + flip_short_matches(1)
     int correction = 0;         // gasma_set_correction: widened band of the reference's -DCORRECTION build
     int max_delta = 0;          // largest |ref_len - read_len| the widened band has lane slots for
     cudaStream_t stream = nullptr;      // stream all work goes to
@@ -146,13 +147,13 @@ int greedy_warps_for(int nl) {
     return 0;
 }
 
-template <int W, int WARPS, bool CORR>
+template <int W, int WARPS, bool CORR, int FLIP = 0>
 int launch_greedy_t(gasma_ctx* ctx, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, const uint32_t* foff,
                     int64_t n, int32_t* cost, uint16_t* rows, uint16_t* stage, int stride, uint32_t* nops, uint32_t* chunk_counter,
                     uint32_t* status, unsigned long long* steps, uint32_t* tsums) {
     size_t smem = greedy_smem_bytes<W>(WARPS, ctx->kp.nl);
     if (const char* env = getenv("GASMA_SMEM_PAD")) smem += (size_t)atoi(env);   // occupancy experiments only
-    auto kern = greedy_kernel<W, WARPS, CORR>;
+    auto kern = greedy_kernel<W, WARPS, CORR, FLIP>;
     CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 32 * WARPS, smem));
@@ -173,6 +174,14 @@ template <int W>
 int launch_greedy_w(gasma_ctx* ctx, int warps, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs,
                     const uint32_t* foff, int64_t n, int32_t* cost, uint16_t* rows, uint16_t* stage, int stride, uint32_t* nops,
                     uint32_t* chunk_counter, uint32_t* status, unsigned long long* steps, uint32_t* tsums) {
+    if (ctx->mask_variant) {   // the other mask variants: one CTA shape each, not tuned further
+        if (ctx->mask_variant == 1) {
+            if (warps == 4) return launch_greedy_t<W, 4, false, 1>(ctx, reads, roff, refs, foff, n, cost, rows, stage, stride, nops, chunk_counter, status, steps, tsums);
+            return launch_greedy_t<W, 1, false, 1>(ctx, reads, roff, refs, foff, n, cost, rows, stage, stride, nops, chunk_counter, status, steps, tsums);
+        }
+        if (warps == 4) return launch_greedy_t<W, 4, false, 2>(ctx, reads, roff, refs, foff, n, cost, rows, stage, stride, nops, chunk_counter, status, steps, tsums);
+        return launch_greedy_t<W, 1, false, 2>(ctx, reads, roff, refs, foff, n, cost, rows, stage, stride, nops, chunk_counter, status, steps, tsums);
+    }
     if (!ctx->kp.correction && warps == 4) {
         // CTA shape: per-warp work is independent, so the shape only decides how many warps an SM holds (shared
         // memory per warp is fixed, the per-CTA reservation and the register file are not).  Pick the most resident warps.
@@ -379,6 +388,7 @@ int gasma_set_correction(gasma_ctx* ctx, int enabled, int max_delta) {
     if (!ctx) return GASMA_E_ARG;
     if (enabled && (max_delta < 0 || max_delta + ctx->params.k > GASMA_MAX_K))
         return fail(ctx, GASMA_E_BAND, "max_delta=%d: need 0 <= max_delta and max_delta + k <= MAX_K=%d", max_delta, GASMA_MAX_K);
+    if (enabled && ctx->mask_variant) return fail(ctx, GASMA_E_UNSUPPORTED, "the widened band is not combined with the other mask variants");
     const int old_c = ctx->correction, old_d = ctx->max_delta;
     ctx->correction = enabled ? 1 : 0;
     ctx->max_delta = enabled ? max_delta : 0;
@@ -389,6 +399,15 @@ int gasma_set_correction(gasma_ctx* ctx, int enabled, int max_delta) {
         return fail(ctx, GASMA_E_UNSUPPORTED, "k=%d + max_delta=%d lanes with max_length=%d do not fit shared memory", ctx->params.k,
                     max_delta, ctx->params.max_length);
     }
+    return GASMA_OK;
+}
+
+int gasma_set_mask_variant(gasma_ctx* ctx, int variant) {
+    if (!ctx) return GASMA_E_ARG;
+    if (variant < 0 || variant > 2) return fail(ctx, GASMA_E_ARG, "mask variant must be 0 (flip_short_hurdles(1)), 1 (flip_short_hurdles(2)) or 2 (+ flip_short_matches(1))");
+    if (variant && ctx->W > 4) return fail(ctx, GASMA_E_UNSUPPORTED, "the other mask variants cover max_length <= 256");
+    if (variant && ctx->correction) return fail(ctx, GASMA_E_UNSUPPORTED, "the other mask variants are not combined with the widened band");
+    ctx->mask_variant = variant;
     return GASMA_OK;
 }
 

@@ -84,9 +84,39 @@ GASMA_HD uint32_t funnel_r1(uint32_t lo, uint32_t hi) {  // bits of (hi:lo) >> 1
     return (lo >> 1) | (hi << 31);
 #endif
 }
-// word of flip_short_hurdles(1): a hurdle survives iff a neighbouring bit is a hurdle too (edges see 0)
-GASMA_HD uint32_t flip_word(uint32_t prev, uint32_t cur, uint32_t next) {
-    return cur & (funnel_l1(prev, cur) | funnel_r1(cur, next));
+GASMA_HD uint32_t funnel_l2(uint32_t lo, uint32_t hi) {  // bits of (hi:lo) << 2, upper word
+#if defined(__CUDA_ARCH__)
+    return __funnelshift_l(lo, hi, 2);
+#else
+    return (hi << 2) | (lo >> 30);
+#endif
+}
+GASMA_HD uint32_t funnel_r2(uint32_t lo, uint32_t hi) {  // bits of (hi:lo) >> 2, lower word
+#if defined(__CUDA_ARCH__)
+    return __funnelshift_r(lo, hi, 2);
+#else
+    return (lo >> 2) | (hi << 30);
+#endif
+}
+// One word of the lane the highway search runs on (hurdle_matrix.h:453), from three neighbouring words of the original
+// mask.  FLIP selects the aligner's mask variant at compile time (utils.h:200-240):
+//   0  flip_short_hurdles(1): a hurdle survives iff a neighbouring bit is a hurdle too (edges see 0) -- as shipped
+//   1  flip_short_hurdles(2): ... iff a bit at distance 1 or 2 is a hurdle
+//   2  flip_short_hurdles(1).flip_short_matches(1): then a non-hurdle between two hurdles becomes a hurdle; at the
+//      ends of the vector the missing neighbour counts as a hurdle (shift_left_one / shift_right_one feed a 1,
+//      utils.h:155-163).  The neighbour words' edge bits of the intermediate mask are rebuilt from prev / next;
+//      first / last say whether `cur` is word 0 / the top word of the vector (only read by variant 2).
+template <int FLIP>
+GASMA_HD uint32_t flip_word(uint32_t prev, uint32_t cur, uint32_t next, bool first, bool last) {
+    if (FLIP == 1) return cur & (funnel_l1(prev, cur) | funnel_r1(cur, next) | funnel_l2(prev, cur) | funnel_r2(cur, next));
+    const uint32_t f = cur & (funnel_l1(prev, cur) | funnel_r1(cur, next));
+    if (FLIP != 2) return f;
+    // bit 31 of the intermediate mask's previous word, bit 0 of its next word (1 beyond the ends of the vector)
+    const uint32_t fp = first ? 1u : ((prev >> 31) & ((prev >> 30) | cur) & 1u);
+    const uint32_t fn = last ? 1u : (next & ((cur >> 31) | (next >> 1)) & 1u);
+    const uint32_t below = (f << 1) | fp;          // bit i = intermediate bit i-1
+    const uint32_t above = (f >> 1) | (fn << 31);  // bit i = intermediate bit i+1
+    return f | (below & above);
 }
 
 // The closest highway of a lane at/after column sc (hurdle_matrix.h:296-303 on the flipped lane):
@@ -95,7 +125,7 @@ GASMA_HD uint32_t flip_word(uint32_t prev, uint32_t cur, uint32_t next) {
 // One loop serves both searches (it flips from "looking for a 0" to "looking for a 1" in place and carries on in
 // the same word), touching only the words between sc and the end of the highway.
 // `base` points at word 0 of the lane's original mask for this thread.
-template <int W>
+template <int W, int FLIP = 0>
 GASMA_HD void scan_highway_loop(const uint32_t* base, int stride, int sc, int& sp, int& len) {
     constexpr int NW = 2 * W, BITS = 64 * W;
     sp = imax(sc, BITS);
@@ -107,7 +137,7 @@ GASMA_HD void scan_highway_loop(const uint32_t* base, int stride, int sc, int& s
     uint32_t next = w + 1 < NW ? base[(w + 1) * stride] : 0u;
     uint32_t inv = 0xFFFFFFFFu, mask = 0xFFFFFFFFu << (sc & 31);
     for (;;) {
-        const uint32_t t = (flip_word(prev, cur, next) ^ inv) & mask;
+        const uint32_t t = (flip_word<FLIP>(prev, cur, next, w == 0, w == NW - 1) ^ inv) & mask;
         if (t) {
             const int pos = 32 * w + ctz32(t);
             if (inv == 0u) { len = pos - sp; return; }
@@ -127,7 +157,7 @@ GASMA_HD void scan_highway_loop(const uint32_t* base, int stride, int sc, int& s
 // Continuation of a search whose highway start sp is known and whose flipped lane holds no hurdle in [sp, q):
 // len = (first hurdle at/after bit q) - sp, BITS if none follows.  Words that start beyond the destination column de
 // are not visited: a highway that long is clamped to the destination by the caller whatever its exact end.
-template <int W>
+template <int W, int FLIP = 0>
 GASMA_HD int scan_highway_tail(const uint32_t* base, int stride, int q, int de, int sp) {
     constexpr int NW = 2 * W, BITS = 64 * W;
     int w = q >> 5;
@@ -137,7 +167,7 @@ GASMA_HD int scan_highway_tail(const uint32_t* base, int stride, int q, int de, 
     uint32_t mask = 0xFFFFFFFFu << (q & 31);
     for (;;) {
         const uint32_t next = w + 1 < NW ? base[(w + 1) * stride] : 0u;
-        const uint32_t t = flip_word(prev, cur, next) & mask;
+        const uint32_t t = flip_word<FLIP>(prev, cur, next, w == 0, w == NW - 1) & mask;
         if (t) return 32 * w + ctz32(t) - sp;
         if (++w >= NW || 32 * w > de) return BITS;
         prev = cur;
@@ -159,7 +189,7 @@ GASMA_HD uint32_t funnel_r(uint32_t lo, uint32_t hi, int s) {  // low word of (h
 // (~1/error-rate bases), so the loop is only needed when a run does not end inside the window.
 // `de` is the lane's destination column: the caller clamps any highway with sp+len > de to the destination, so a
 // run that leaves the window beyond de needs no exact end (len = BITS stands for "past the destination").
-template <int W>
+template <int W, int FLIP = 0>
 GASMA_HD void scan_highway(const uint32_t* base, int stride, int sc, int de, int& sp, int& len) {
     constexpr int NW = 2 * W, BITS = 64 * W;
     const int w = sc >> 5, b = sc & 31;
@@ -169,7 +199,9 @@ GASMA_HD void scan_highway(const uint32_t* base, int stride, int sc, int de, int
     const uint32_t o1 = w + 1 < NW ? base[(w + 1) * stride] : 0u;
     const uint32_t o2 = w + 2 < NW ? base[(w + 2) * stride] : 0u;
     const uint32_t o3 = w + 3 < NW ? base[(w + 3) * stride] : 0u;
-    const uint32_t f0 = flip_word(om, o0, o1), f1 = flip_word(o0, o1, o2), f2 = flip_word(o1, o2, o3);
+    // words beyond the vector are zero and must stay zero: they are never "last"
+    const uint32_t f0 = flip_word<FLIP>(om, o0, o1, w == 0, w == NW - 1), f1 = flip_word<FLIP>(o0, o1, o2, false, w + 1 == NW - 1),
+                   f2 = flip_word<FLIP>(o1, o2, o3, false, w + 2 == NW - 1);
     const uint32_t lo = funnel_r(f0, f1, b), hi = funnel_r(f1, f2, b);   // flipped lane bits [sc, sc+64), zero fill
     const uint32_t zlo = ~lo, zhi = ~hi;
     bool resolved = false;
@@ -183,11 +215,11 @@ GASMA_HD void scan_highway(const uint32_t* base, int stride, int sc, int de, int
             resolved = true;
         } else {   // the highway leaves the window: no hurdle up to the end of the vector / past the destination, or go on
             sp = sc + fz;
-            len = (sc + 64 >= BITS || sc + 64 > de) ? BITS : scan_highway_tail<W>(base, stride, sc + 64, de, sp);
+            len = (sc + 64 >= BITS || sc + 64 > de) ? BITS : scan_highway_tail<W, FLIP>(base, stride, sc + 64, de, sp);
             resolved = true;
         }
     }
-    if (!resolved) scan_highway_loop<W>(base, stride, sc, sp, len);   // 64 hurdles in a row
+    if (!resolved) scan_highway_loop<W, FLIP>(base, stride, sc, sp, len);   // 64 hurdles in a row
 }
 
 // pop_count_between(from,to), utils.h:263-270 = shift_left(from).shift_right(from+BITS-to).pop_count():
@@ -380,7 +412,7 @@ GASMA_HD void pair_init(const KParams& P, const uint64_t A0[W], const uint64_t A
 
 // One _step() (hurdle_matrix.h:407-434) including its _update_highway_list and _choose_best_highway.
 // Returns true when the traversal is over (the caller then runs pair_finish).
-template <int W, bool CORR = false>
+template <int W, bool CORR = false, int FLIP = 0>
 GASMA_HD bool pair_step(const KParams& P, const LaneStore<W>& S, PairState& ps, OpSink& sink, uint32_t& status) {
     constexpr int BITS = 64 * W;
     const int x = P.x, o = P.o, e = P.e;
@@ -406,7 +438,7 @@ GASMA_HD bool pair_step(const KParams& P, const LaneStore<W>& S, PairState& ps, 
         int sp = st_sp(st), len = st_len(st), nsw = st_nsw(st);
         if (sp < sc) {  // cache miss: look up the closest highway of this lane (:293-310)
             nsw = iabs(l - cl);
-            scan_highway<W>(lane_base<W>(S, li), S.stride, sc, de, sp, len);
+            scan_highway<W, FLIP>(lane_base<W>(S, li), S.stride, sc, de, sp, len);
             if (sp + len > de) { len = imax(0, de - sp); reach = true; }
         }
         const int sw = leap_cost ? slp(cl, l, o, e) : 0;
@@ -480,14 +512,14 @@ GASMA_HD void pair_finish(const KParams& P, const LaneStore<W>& S, PairState& ps
 }
 
 // The whole alignment of one pair (host harness, and kernels that do not interleave pairs).  Returns status bits.
-template <int W, bool CORR = false>
+template <int W, bool CORR = false, int FLIP = 0>
 GASMA_HD uint32_t greedy_pair(const KParams& P, const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W],
                               const uint64_t B1[W], int m, int n, const LaneStore<W>& S, OpSink& sink, int& cost_out,
                               int& steps_out) {
     PairState ps;
     uint32_t status = 0;
     pair_init<W, CORR>(P, A0, A1, B0, B1, m, n, S, ps);
-    while (!pair_step<W, CORR>(P, S, ps, sink, status)) {}
+    while (!pair_step<W, CORR, FLIP>(P, S, ps, sink, status)) {}
     pair_finish<W, CORR>(P, S, ps, sink);
     cost_out = ps.cost;
     steps_out = ps.steps;

@@ -85,7 +85,8 @@ __host__ __device__ constexpr size_t greedy_smem_bytes(int warps, int nl) {   //
            + 64;
 }
 
-template <int W, int WARPS, bool CORR>
+// FLIP: the aligner's mask variant (greedy.cuh:flip_word), 0 = the reference as shipped
+template <int W, int WARPS, bool CORR, int FLIP = 0>
 __global__ void __launch_bounds__(32 * WARPS, CORR ? 1 : (WARPS == 8 ? 3 : (WARPS == 4 ? 5 : (WARPS == 2 ? 11 : 1))))
 greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __restrict__ read_off,
               const uint8_t* __restrict__ refs, const uint32_t* __restrict__ ref_off, long long n,
@@ -240,7 +241,7 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
             continue;   // every pair handed out so far was rejected, or the pool just ran empty
         }
         if (active) {
-            if (pair_step<W, CORR>(P, S, ps, sink, st)) {
+            if (pair_step<W, CORR, FLIP>(P, S, ps, sink, st)) {
                 pair_finish<W, CORR>(P, S, ps, sink);
                 sink.finish();
                 cost[my_p] = ps.cost;

@@ -153,7 +153,8 @@ __host__ __device__ constexpr size_t myers_smem_bytes(int tile) {
 // once every thread holds its planes in registers, so both live in the SAME shared memory (one barrier in between).
 template <int W>
 __host__ __device__ constexpr size_t myers_trace_bytes(int tile) {
-    return ((size_t)myers_trace_slots(64 * W) * sizeof(TraceCol) + (size_t)(kTraceParts - 1) * sizeof(BandCk)) * tile;
+    return ((size_t)myers_trace_slots(64 * W) * sizeof(TraceCol) + (size_t)(kTraceParts - 1) * sizeof(BandCk) +
+            (size_t)2 * W * sizeof(CoverWord)) * tile;   // + the coverage walk's E/B words (counters mode)
 }
 template <int W>
 __host__ __device__ constexpr size_t myers_trace_smem_bytes(int tile) {
@@ -237,8 +238,11 @@ struct NwCounterArgs {
     uint32_t* reset_word;         // optional: set to 0 (the greedy kernel's chunk counter, for the next batch)
 };
 
+#ifndef GASMA_NW_MINBLOCKS
+#define GASMA_NW_MINBLOCKS 1
+#endif
 template <int W, int T, int MODE>
-__global__ void __launch_bounds__(T)
+__global__ void __launch_bounds__(T, GASMA_NW_MINBLOCKS)
 nw_band_kernel(const uint8_t* __restrict__ reads, const uint32_t* __restrict__ read_off, const uint8_t* __restrict__ refs,
                const uint32_t* __restrict__ ref_off, long long n, const int32_t* bound, int32_t* penalty,
                uint16_t* __restrict__ ops_stage, int ops_stride, uint32_t* __restrict__ nops_out,
@@ -257,6 +261,7 @@ nw_band_kernel(const uint8_t* __restrict__ reads, const uint32_t* __restrict__ r
     // phase B view (after the barrier below): traceback windows [slot][T], checkpoints [part][T]
     TraceCol* s_tb = reinterpret_cast<TraceCol*>(smem_raw);
     BandCk* s_ck = reinterpret_cast<BandCk*>(s_tb + (size_t)myers_trace_slots(BITS) * T);
+    CoverWord* s_eb = reinterpret_cast<CoverWord*>(s_ck + (size_t)(kTraceParts - 1) * T);   // [2W][T]
 
     const int tid = threadIdx.x;
     const long long p0 = (long long)blockIdx.x * T;
@@ -306,7 +311,7 @@ nw_band_kernel(const uint8_t* __restrict__ reads, const uint32_t* __restrict__ r
             const NwBand bd = nw_band(m, nn, 1, 1, bu);
             if (myers_band_fits(bd)) {
                 if (MODE == kNwCounters) {
-                    pen = myers_band_cover<W>(A0, A1, B0, B1, m, nn, bd.hi, s_tb + tid, T, s_ck + tid, T, t);
+                    pen = myers_band_cover<W>(A0, A1, B0, B1, m, nn, bd.hi, s_tb + tid, T, s_ck + tid, T, s_eb + tid, T, t);
                 } else {
                     sink.wp = row_end;
                     pen = myers_band_align<W>(A0, A1, B0, B1, m, nn, bd.hi, TRACE ? s_tb + tid : nullptr, T, s_ck + tid, T, sink);

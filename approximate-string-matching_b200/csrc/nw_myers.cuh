@@ -194,6 +194,11 @@ GASMA_HD BandCols myers_band_start(int hi) {
     return BandCols{pv, ~pv, 0};
 }
 
+#ifndef GASMA_NW_COL_UNROLL
+#define GASMA_NW_COL_UNROLL 2
+#endif
+constexpr int kNwColUnroll = GASMA_NW_COL_UNROLL;   // unroll factor of the column loop (loop overhead vs code size)
+
 // Columns j_begin+1 .. j_end (1-based) of the banded matrix, continuing from the state `c` left after column j_begin
 // (myers_band_start for j_begin == 0).  When tb != nullptr the windows of these columns are kept at slots 0, 1, ...
 // (slot s = column j_begin + 1 + s).  Resumable at any column, so a caller can checkpoint `c` and recompute a range
@@ -219,7 +224,7 @@ GASMA_HD void myers_band_run(const uint64_t A0[W], const uint64_t A1[W], const u
         const uint32_t wl1 = funnel32_l(al1, am1, hi), wh1 = funnel32_l(am1, ah1, hi);
         uint32_t r0 = brev32(half32<W>(B0, cb)) << s0, r1 = brev32(half32<W>(B1, cb)) << s0;   // next ref character in bit 31
 #if defined(__CUDA_ARCH__)
-#pragma unroll 1
+#pragma unroll(kNwColUnroll)
 #endif
         for (int s = s0; s < cend; ++s) {
             const uint32_t k0 = (uint32_t)((int32_t)r0 >> 31), k1 = (uint32_t)((int32_t)r1 >> 31);
@@ -320,14 +325,20 @@ struct OpsWalker {
 // consumes the read rows in descending order, so it just records, per consumed row p (0-based position),
 //   E[p] = the row was consumed by an '=' step,   B[p] = a D step happened between row p and the row above it
 // (a D does not consume a row but ends a run), 32 positions per word, accumulated in registers and flushed when a
-// word is complete (a statically unrolled select: a dynamically indexed register array would live in local memory).
+// word is complete.  A finished word goes to the alignment's 2W slots in shared memory with ONE store (the kernel is
+// bound by the ALU pipe, the load/store pipe is nearly idle; a run-time index into a register array would mean local
+// memory, a statically unrolled select 4W ALU instructions on almost every step of a warp) and E, B are read back
+// with compile-time indices when the walk is over.
 // No run lengths, no per-run branches; metrics.cuh:runs3_positions turns E, B into the positions.
+struct alignas(8) CoverWord { uint32_t e, b; };
 template <int W>
 struct CoverTrace {
     int i, j, b;
     uint32_t e, brk;       // word under construction
     uint32_t pend;         // a D step since the last consumed row
-    uint32_t E[2 * W], B[2 * W];
+    CoverWord* slots;      // word w at slots[w * slot_stride]
+    int slot_stride;
+    uint32_t E[2 * W], B[2 * W];   // valid after finish()
     GASMA_HD bool live() const { return i > 0 && j > 0; }
     GASMA_HD int col() const { return j; }
     GASMA_HD void start(int m, int n, int hi) {
@@ -336,14 +347,10 @@ struct CoverTrace {
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
-        for (int w = 0; w < 2 * W; ++w) { E[w] = 0u; B[w] = 0u; }
+        for (int w = 0; w < 2 * W; ++w) slots[w * slot_stride] = CoverWord{0u, 0u};
     }
     GASMA_HD void land(int w) {   // the word under construction is word w
-#if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
-        for (int q = 0; q < 2 * W; ++q)
-            if (q == w) { E[q] = e; B[q] = brk; }
+        slots[w * slot_stride] = CoverWord{e, brk};
         e = brk = 0u;
     }
     GASMA_HD void segment(int j_lo, const TraceCol* tb, int stride) {
@@ -366,6 +373,14 @@ struct CoverTrace {
     }
     GASMA_HD void finish() {
         if (i > 0) land((i - 1) >> 5);   // rows left at column 0 are an I run; the word under construction still has to land
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+        for (int w = 0; w < 2 * W; ++w) {
+            const CoverWord c = slots[w * slot_stride];
+            E[w] = c.e;
+            B[w] = c.b;
+        }
     }
 };
 
@@ -381,7 +396,7 @@ struct CoverTrace {
 #define GASMA_TRACE_PARTS 6
 #endif
 constexpr int kTraceParts = GASMA_TRACE_PARTS;
-GASMA_HD int myers_part_start(int n, int part) { return (int)((long long)n * part / kTraceParts); }
+GASMA_HD int myers_part_start(int n, int part) { return (int)((unsigned)(n * part) / (unsigned)kTraceParts); }   // n <= 256
 GASMA_HD constexpr int myers_trace_slots(int max_n) { return (max_n + kTraceParts - 1) / kTraceParts; }
 struct alignas(8) BandCk { uint32_t pv, mv; };   // the diagonal-step count is only needed by the first pass (score)
 template <int W, class Walker>
@@ -429,7 +444,10 @@ GASMA_HD int myers_band_align(const uint64_t A0[W], const uint64_t A1[W], const 
 // penalty + E/B masks
 template <int W>
 GASMA_HD int myers_band_cover(const uint64_t A0[W], const uint64_t A1[W], const uint64_t B0[W], const uint64_t B1[W],
-                              int m, int n, int hi, TraceCol* tb, int stride, BandCk* ck, int ck_stride, CoverTrace<W>& t) {
+                              int m, int n, int hi, TraceCol* tb, int stride, BandCk* ck, int ck_stride, CoverWord* slots,
+                              int slot_stride, CoverTrace<W>& t) {
+    t.slots = slots;
+    t.slot_stride = slot_stride;
     return myers_band_walk<W>(A0, A1, B0, B1, m, n, hi, tb, stride, ck, ck_stride, t);
 }
 

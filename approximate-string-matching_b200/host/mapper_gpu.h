@@ -32,6 +32,7 @@ struct mapper_record {
     size_t window_len;
     int cost = 0;           // get_cost()
     std::string cigar;      // SAM CIGAR built from the greedy ops
+    bool rejected = false;  // |window - read| > MAX_K after clipping at the contig end: not aligned, written as unmapped
 };
 
 class mapper_gpu {
@@ -57,10 +58,17 @@ public:
         else if (start + len > reference.size()) len = reference.size() - start;
         mapper_record r;
         r.read_index = read_index; r.ref_id = ref_id; r.window_start = start; r.window_len = len;
-        pending_.push_back(r);
         // hurdle_matrix::reset cuts both strings at MAX_LENGTH (hurdle_matrix.h:626-627)
-        reads_.append(query, 0, (size_t)max_length_);
-        refs_.append(reference, start, std::min(len, (size_t)max_length_));
+        const size_t m = std::min(query.size(), (size_t)max_length_), w = std::min(len, (size_t)max_length_);
+        // A window clipped at the end of its contig can differ from the read by more than MAX_K bases: out of bounds in
+        // the reference, GASMA_E_BAND for the WHOLE batch here.  Such a hit is not aligned (it travels through the batch
+        // as an empty pair) and comes back as an unmapped record instead of aborting the chunk.
+        r.rejected = (m > w ? m - w : w - m) > (size_t)GASMA_MAX_K;
+        pending_.push_back(r);
+        if (!r.rejected) {
+            reads_.append(query, 0, m);
+            refs_.append(reference, start, w);
+        }
         read_off_.push_back((uint32_t)reads_.size());
         ref_off_.push_back((uint32_t)refs_.size());
     }
@@ -80,16 +88,23 @@ public:
             rc = gasma_greedy_batch(ctx_, reads_.data(), read_off_.data(), refs_.data(), ref_off_.data(), n, cost_.data(),
                                     ops_.data(), (int64_t)ops_.size(), op_off_.data());
         }
-        if (rc != GASMA_OK) throw std::runtime_error(std::string("mapper_gpu::flush: ") + gasma_last_error(ctx_));
+        if (rc != GASMA_OK) {   // nothing of this chunk survives a failed call: do not leave it pending for the next flush
+            const std::string why = gasma_last_error(ctx_);
+            reset_pending();
+            throw std::runtime_error("mapper_gpu::flush: " + why);
+        }
         for (int64_t i = 0; i < n; ++i) {
             mapper_record& r = pending_[(size_t)i];
-            r.cost = cost_[(size_t)i];
-            r.cigar = sam_cigar(ops_.data() + op_off_[(size_t)i], (int)(op_off_[(size_t)i + 1] - op_off_[(size_t)i]));
+            if (r.rejected) {
+                r.cost = 0;
+                r.cigar.clear();
+            } else {
+                r.cost = cost_[(size_t)i];
+                r.cigar = sam_cigar(ops_.data() + op_off_[(size_t)i], (int)(op_off_[(size_t)i + 1] - op_off_[(size_t)i]));
+            }
             out.push_back(std::move(r));
         }
-        pending_.clear();
-        reads_.clear(); refs_.clear();
-        read_off_.assign(1, 0u); ref_off_.assign(1, 0u);
+        reset_pending();
         batches_++;
     }
     int64_t batches() const { return batches_; }
@@ -99,6 +114,10 @@ public:
     // POS is the 1-based form of the reference's ref_offset = start + 2 (:88, its TODO included); MAPQ = 60 + cost (:91).
     static void write_sam_record(FILE* f, const mapper_record& r, const std::string& read_id, const std::string& ref_name,
                                  const std::string& seq, const std::string& qual) {
+        if (r.rejected) {   // hit that could not be aligned (window clipped at a contig end): SAM "unmapped" record
+            fprintf(f, "%s\t4\t*\t0\t0\t*\t*\t0\t0\t%s\t%s\n", read_id.c_str(), seq.c_str(), qual.empty() ? "*" : qual.c_str());
+            return;
+        }
         fprintf(f, "%s\t0\t%s\t%zu\t%d\t%s\t*\t0\t0\t%s\t%s\n", read_id.c_str(), ref_name.c_str(), r.window_start + 2 + 1,
                 60 + r.cost, r.cigar.empty() ? "*" : r.cigar.c_str(), seq.c_str(), qual.empty() ? "*" : qual.c_str());
     }
@@ -127,6 +146,11 @@ public:
     }
 
 private:
+    void reset_pending() {
+        pending_.clear();
+        reads_.clear(); refs_.clear();
+        read_off_.assign(1, 0u); ref_off_.assign(1, 0u);
+    }
     gasma_ctx* ctx_ = nullptr;
     int max_length_;
     int64_t batches_ = 0;

@@ -86,6 +86,15 @@ int gasma_set_band(gasma_ctx* ctx, int k);
  * |n-m| + k > GASMA_MAX_K (past the reference's lane arrays), fails the batch with GASMA_E_BAND.  Results are
  * bit-exact to the unmodified reference compiled with -DCORRECTION.  enabled == 0 restores lanes -k..k. */
 int gasma_set_correction(gasma_ctx* ctx, int enabled, int max_delta);
+/* The aligner's other mask variants.  hurdle_matrix.h:453 runs the highway search on
+ * mask.flip_short_hurdles(1) and carries a commented-out .flip_short_matches(1); int_128bit also offers
+ * flip_short_hurdles(2) (utils.h:200-240).  variant 0 = flip_short_hurdles(1) (the reference as shipped, default),
+ * 1 = flip_short_hurdles(2), 2 = flip_short_hurdles(1).flip_short_matches(1).  Penalties and hurdle counts are always
+ * taken from the original mask, as in the reference.  Bit-exact to the unmodified reference with that call site
+ * changed (oracle/ref_driver.cpp does it with a macro around the unmodified header).  max_length <= 256; not combined
+ * with gasma_set_correction.  The int_256bit type (utils.h:274-549, README "Using AVX2") is NOT offered: in the
+ * reference it reads an uninitialised upper half (hurdle_matrix.h:262-275), so it has no defined result. */
+int gasma_set_mask_variant(gasma_ctx* ctx, int variant);
 /* Use the caller's cudaStream_t (e.g. torch's current stream) for all work of this context.  The handle is
  * taken literally: NULL means the legacy default stream.  A fresh context uses a private non-blocking stream. */
 int gasma_set_stream(gasma_ctx* ctx, void* cuda_stream);

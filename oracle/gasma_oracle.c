@@ -68,11 +68,30 @@ static int bv_pcb(const bv_t* v, int from, int to, int W) {
     bv_t b = bv_up(&a, from + 64 * W - to, W);
     return bv_popcount(&b, W);
 }
-/* utils.h:200-216 with threshold 1: v & ((v>>1) | (v<<1)) */
-static bv_t bv_flip_short_hurdles(const bv_t* v, int W) {
+/* utils.h:200-216: threshold 1: v & ((v>>1) | (v<<1)); threshold 2: v & ((v>>1) | (v<<1) | (v>>2) | (v<<2)) */
+static bv_t bv_flip_short_hurdles(const bv_t* v, int W, int threshold) {
     bv_t l = bv_down(v, 1, W), r = bv_up(v, 1, W), out; bv_zero(&out);
-    for (int i = 0; i < W; ++i) out.w[i] = v->w[i] & (l.w[i] | r.w[i]);
+    bv_t l2, r2; bv_zero(&l2); bv_zero(&r2);
+    if (threshold > 1) { l2 = bv_down(v, 2, W); r2 = bv_up(v, 2, W); }
+    for (int i = 0; i < W; ++i) out.w[i] = v->w[i] & (l.w[i] | r.w[i] | l2.w[i] | r2.w[i]);
     return out;
+}
+/* utils.h:223-240 with threshold 1: v | (shift_left_one(v) & shift_right_one(v)): a 0 between two 1s becomes 1;
+ * shift_left_one (:160-163) feeds a 1 into the top bit, shift_right_one (:155-158) a 1 into bit 0 */
+static bv_t bv_flip_short_matches(const bv_t* v, int W) {
+    bv_t l = bv_down(v, 1, W), r = bv_up(v, 1, W), out; bv_zero(&out);
+    l.w[W - 1] |= 1ull << 63;
+    r.w[0] |= 1ull;
+    for (int i = 0; i < W; ++i) out.w[i] = v->w[i] | (l.w[i] & r.w[i]);
+    return out;
+}
+/* the lane the highway search runs on (hurdle_matrix.h:453 and its commented-out tail):
+ * variant 0: flip_short_hurdles(1) (the reference as shipped); 1: flip_short_hurdles(2);
+ * 2: flip_short_hurdles(1).flip_short_matches(1) */
+static bv_t bv_search_lane(const bv_t* v, int W, int variant) {
+    bv_t f = bv_flip_short_hurdles(v, W, variant == 1 ? 2 : 1);
+    if (variant == 2) f = bv_flip_short_matches(&f, W);
+    return f;
 }
 
 /* bit_convert.cpp:248-369 (output side only): plane0 bit i = c in {C,T}, plane1 bit i = c in {G,T},
@@ -163,7 +182,7 @@ int go_greedy(const char* read, int read_len, const char* ref, int ref_len, cons
             for (int i = 0; i < W; ++i) v.w[i] = (s0.w[i] ^ A0.w[i]) | (s1.w[i] ^ A1.w[i]);
         }
         orig[IX(l)] = v;
-        flip[IX(l)] = bv_flip_short_hurdles(&v, W);
+        flip[IX(l)] = bv_search_lane(&v, W, p->mask_variant);
         sp[IX(l)] = -1;
         sw[IX(l)] = hc[IX(l)] = nsw[IX(l)] = nh[IX(l)] = BITS;
         de[IX(l)] = calc_destination(m, n, l);

@@ -36,6 +36,8 @@ typedef struct {
     double match_prob, mismatch_prob, indel_prob; /* hurdle_matrix.h:557-559 */
     int correction;      /* 1 = the reference built with -DCORRECTION (hurdle_matrix.h:501-512, :634-641):
                           * lanes [-k, n-m+k] for m <= n, [n-m-k, k] otherwise; 0 = lanes -k..k */
+    int mask_variant;    /* lane the highway search runs on (hurdle_matrix.h:453): 0 = flip_short_hurdles(1) as shipped,
+                          * 1 = flip_short_hurdles(2), 2 = flip_short_hurdles(1).flip_short_matches(1) (utils.h:200-240) */
 } go_params;
 
 /* bit_convert.cpp:248 semantics for one string, tail [len, 64W) = 'A' (00) */

@@ -26,7 +26,26 @@
 #include <vector>
 #include <algorithm>
 
+// The aligner's other mask variants: hurdle_matrix.h:453 hard-codes
+//     lanes[...] = mask.flip_short_hurdles(1);//.flip_short_matches(1);
+// Built with -DGASMA_REF_MASK_VARIANT=1 that call site reads flip_short_hurdles(2), with =2 it reads
+// flip_short_hurdles(1).flip_short_matches(1) -- by a macro that is active only while hurdle_matrix.h is read, AFTER
+// utils.h (where int_128bit defines both functions, utils.h:200-240) has been included untouched.  The reference's
+// sources are not edited.
+#ifdef GASMA_REF_MASK_VARIANT
+#include "utils.h"
+#if GASMA_REF_MASK_VARIANT == 1
+#define flip_short_hurdles(t) flip_short_hurdles(2)
+#elif GASMA_REF_MASK_VARIANT == 2
+#define flip_short_hurdles(t) flip_short_hurdles(1).flip_short_matches(1)
+#else
+#error "GASMA_REF_MASK_VARIANT must be 1 or 2"
+#endif
+#endif
 #include "hurdle_matrix.h"                 // -I /root/reference/GASMA  (pulls utils.h, bit_convert.h, mask.h)
+#ifdef GASMA_REF_MASK_VARIANT
+#undef flip_short_hurdles
+#endif
 #include "benchmark/benchmark_coverage.h"  // unmodified coverage metric
 
 namespace {

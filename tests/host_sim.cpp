@@ -45,7 +45,7 @@ bool stage(const uint8_t* buf, uint32_t base16, uint32_t end, uint32_t total, ui
     return ok;
 }
 
-template <int W, bool CORR = false>
+template <int W, bool CORR = false, int FLIP = 0>
 int sim_greedy(const KParams& P, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, const uint32_t* foff,
                int64_t n, int T, int32_t* cost, uint16_t* ops_stage, int stride, uint32_t* nops, uint32_t* status_out,
                int64_t* steps_out) {
@@ -87,7 +87,7 @@ int sim_greedy(const KParams& P, const uint8_t* reads, const uint32_t* roff, con
                 std::vector<uint16_t> big(stride);
                 OpSink sink{prim, row ? row : big.data(), stride, 0u, nullptr, 0};
                 sink.begin(0u);
-                st = greedy_pair<W, CORR>(P, A0, A1, B0, B1, m, nn, S, sink, c, steps);
+                st = greedy_pair<W, CORR, FLIP>(P, A0, A1, B0, B1, m, nn, S, sink, c, steps);
                 sink.finish();
                 if (row && sink.n <= kRowKeep) for (int i = 0; i < sink.n; ++i) row[i] = prim[i];
                 my = (uint32_t)sink.n;
@@ -263,7 +263,8 @@ int sim_counters(const uint8_t* reads, const uint32_t* roff, const uint8_t* refs
             int pen, cov;
             if (myers_band_fits(bd)) {
                 CoverTrace<W> ct;
-                pen = myers_band_cover<W>(A0, A1, B0, B1, m, nn, bd.hi, tb.data(), 1, ck.data(), 1, ct);
+                CoverWord eb[2 * W];
+                pen = myers_band_cover<W>(A0, A1, B0, B1, m, nn, bd.hi, tb.data(), 1, ck.data(), 1, eb, 1, ct);
                 uint32_t P1[2 * W], P2[2 * W], a0[2 * W], a1[2 * W];
                 runs3_positions<2 * W>(ct.E, ct.B, P2);
                 lcm_mask<2 * W>(gops + goff[p], (int)(goff[p + 1] - goff[p]), 1, P1);   // LCM1: read positions under greedy M runs
@@ -412,6 +413,18 @@ int sim_greedy_batch_corr(int W, int T, int k, int x, int o, int e, int global, 
         case 3: return sim_greedy<3, true>(P, reads, roff, refs, foff, n, T, cost, ops_stage, stride, nops, status, steps);
         case 4: return sim_greedy<4, true>(P, reads, roff, refs, foff, n, T, cost, ops_stage, stride, nops, status, steps);
     }
+    return -1;
+}
+
+// the aligner's other mask variants (gasma_set_mask_variant): 1 = flip_short_hurdles(2), 2 = + flip_short_matches(1)
+int sim_greedy_batch_mask(int variant, int W, int T, int k, int x, int o, int e, int global, double pm, double pmm, double pid,
+                          const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, const uint32_t* foff, int64_t n,
+                          int32_t* cost, uint16_t* ops_stage, int stride, uint32_t* nops, uint32_t* status, int64_t* steps) {
+    KParams P{k, x, o, e, global, std::log(pm / 0.25), std::log(pmm / 0.25), std::log(pid / 2 / 0.25)};
+#define GASMA_SIM_CASE(WW, FF) if (W == WW && variant == FF) return sim_greedy<WW, false, FF>(P, reads, roff, refs, foff, n, T, cost, ops_stage, stride, nops, status, steps)
+    GASMA_SIM_CASE(1, 1); GASMA_SIM_CASE(2, 1); GASMA_SIM_CASE(3, 1); GASMA_SIM_CASE(4, 1);
+    GASMA_SIM_CASE(1, 2); GASMA_SIM_CASE(2, 2); GASMA_SIM_CASE(3, 2); GASMA_SIM_CASE(4, 2);
+#undef GASMA_SIM_CASE
     return -1;
 }
 

@@ -29,7 +29,7 @@ class GoParams(C.Structure):
     _fields_ = [("k", C.c_int), ("x", C.c_int), ("o", C.c_int), ("e", C.c_int),
                 ("global_", C.c_int), ("W", C.c_int),
                 ("match_prob", C.c_double), ("mismatch_prob", C.c_double), ("indel_prob", C.c_double),
-                ("correction", C.c_int)]
+                ("correction", C.c_int), ("mask_variant", C.c_int)]
 
 
 class GoGenConfig(C.Structure):
@@ -155,6 +155,25 @@ def ref_corr():
     return _ref_corr
 
 
+_ref_mask = {}
+
+
+def ref_mask_available(variant):
+    return os.path.exists(os.path.join(ORACLE_DIR, "_ref", "libgasma_ref_mask%d.so" % variant))
+
+
+def ref_mask(variant):
+    """The unmodified reference with the highway search on another mask variant (hurdle_matrix.h:453, utils.h:200-240):
+    1 = flip_short_hurdles(2), 2 = flip_short_hurdles(1).flip_short_matches(1).  See oracle/ref_driver.cpp."""
+    if variant not in _ref_mask:
+        L = C.CDLL(os.path.join(ORACLE_DIR, "_ref", "libgasma_ref_mask%d.so" % variant))
+        L.gasma_ref_greedy_batch.restype = C.c_int
+        L.gasma_ref_greedy_batch.argtypes = ([C.c_void_p] * 4 + [C.c_int64] + [C.c_int] * 4 + [C.c_double] * 3 +
+                                             [C.c_int] * 2 + [C.c_void_p, C.c_void_p, C.c_int])
+        _ref_mask[variant] = L
+    return _ref_mask[variant]
+
+
 # ----------------------------------------------------------------------------------------------
 # batch containers: concatenated ASCII + CSR offsets (the layout the C ABI uses)
 # ----------------------------------------------------------------------------------------------
@@ -193,8 +212,8 @@ def batch_from_strings(reads, refs):
     return Batch.from_pairs([(r.encode(), f.encode()) for r, f in zip(reads, refs)])
 
 
-def make_params(k=3, x=1, o=1, e=1, W=2, global_=1, probs=DEFAULT_PROBS, correction=0):
-    return GoParams(k, x, o, e, global_, W, probs[0], probs[1], probs[2], correction)
+def make_params(k=3, x=1, o=1, e=1, W=2, global_=1, probs=DEFAULT_PROBS, correction=0, mask_variant=0):
+    return GoParams(k, x, o, e, global_, W, probs[0], probs[1], probs[2], correction, mask_variant)
 
 
 def gen_config(seed, length, error_rate, mismatch_rate=0.96, mode=0, profile=None):
@@ -321,8 +340,8 @@ def render_all(ops, op_off):
 # unmodified reference calls
 # ----------------------------------------------------------------------------------------------
 def ref_greedy(b, k=3, x=1, o=1, e=1, probs=DEFAULT_PROBS, mode=0, threads=1, want_text=True, stride=1280,
-               correction=False):
-    L = ref_corr() if correction else ref()
+               correction=False, mask_variant=0):
+    L = ref_corr() if correction else (ref_mask(mask_variant) if mask_variant else ref())
     cost = np.zeros(b.n, np.int32)
     text = np.zeros(b.n * stride, np.uint8) if want_text else None
     need = L.gasma_ref_greedy_batch(_ptr(b.reads), _ptr(b.read_off), _ptr(b.refs), _ptr(b.ref_off), b.n,

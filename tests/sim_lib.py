@@ -8,7 +8,7 @@ def _p(a):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
 
 
-def sim_greedy(S, ol, b, p, T=128, max_delta=None):
+def sim_greedy(S, ol, b, p, T=128, max_delta=None, mask_variant=0):
     """max_delta != None: the widened band (KParams::correction) with 2k+1+max_delta lane slots."""
     S.sim_greedy_batch.argtypes = [C.c_int] * 7 + [C.c_double] * 3 + [C.c_void_p] * 4 + [
         C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
@@ -22,7 +22,10 @@ def sim_greedy(S, ol, b, p, T=128, max_delta=None):
     steps = np.zeros(1, np.int64)
     head = (p.W, T, p.k, p.x, p.o, p.e, p.global_, p.match_prob, p.mismatch_prob, p.indel_prob)
     tail = (_p(b.reads), _p(b.read_off), _p(b.refs), _p(b.ref_off), b.n, _p(cost), _p(stage), stride, _p(nops), _p(st), _p(steps))
-    if max_delta is None:
+    if mask_variant:
+        S.sim_greedy_batch_mask.argtypes = [C.c_int] + S.sim_greedy_batch.argtypes
+        rc = S.sim_greedy_batch_mask(mask_variant, *head, *tail)
+    elif max_delta is None:
         rc = S.sim_greedy_batch(*head, *tail)
     else:
         rc = S.sim_greedy_batch_corr(*head, max_delta, *tail)

@@ -292,3 +292,36 @@ def test_gpu_widened_band_matches_oracle(pkg, ol, W):
     assert ei.value.code == -3   # GASMA_E_BAND
     with pytest.raises(pkg.GasmaError):
         al.set_correction(True, 48)    # max_delta + k > MAX_K
+
+
+@pytest.mark.parametrize("variant", [1, 2])
+def test_gpu_mask_variants(pkg, ol, golden, variant):
+    """gasma_set_mask_variant: the highway search on flip_short_hurdles(2) / flip_short_hurdles(1).flip_short_matches(1)
+    (utils.h:200-240), against the unmodified reference's outputs for that call site and against the oracle."""
+    for s in golden("greedy_ref_mask.json")["sets"]:
+        if s["variant"] != variant:
+            continue
+        ps = s["params"]
+        al = pkg.Aligner(k=ps["k"], x=ps["x"], o=ps["o"], e=ps["e"], match_prob=ps["probs"][0], mismatch_prob=ps["probs"][1],
+                         indel_prob=ps["probs"][2])
+        al.set_mask_variant(variant)
+        out, text = _run(pkg, al, _batch(ol, s["pairs"]))
+        assert out["cost"].tolist() == s["cost"], s["name"]
+        assert text == s["cigar"], s["name"]
+        al.close()
+    rng = np.random.default_rng(660 + variant)
+    for W in (1, 2, 3, 4):
+        b = ol.random_batch(rng, 20000, 1, 64 * W, 0.3, 0.3, 50)
+        al = pkg.Aligner(k=5, x=1, o=2, e=1, max_length=64 * W)
+        al.set_mask_variant(variant)
+        out, _ = _run(pkg, al, b)
+        r = ol.oracle_greedy(b, ol.make_params(5, 1, 2, 1, W, 1, mask_variant=variant), threads=8)
+        assert out["cost"].tolist() == r["cost"].tolist()
+        assert out["op_off"].tolist() == r["op_off"].tolist()
+        assert out["ops"][:out["n_ops"]].tolist() == r["ops"].tolist()
+        al.set_mask_variant(0)      # and back: the default aligner again
+        out0, _ = _run(pkg, al, b)
+        assert out0["cost"].tolist() == ol.oracle_greedy(b, ol.make_params(5, 1, 2, 1, W, 1), threads=8)["cost"].tolist()
+        al.close()
+    with pytest.raises(pkg.GasmaError):
+        pkg.Aligner(max_length=512).set_mask_variant(1)

@@ -100,3 +100,31 @@ def test_gpu_benchmark_batch_noisy_pairs(pkg, ol, W, penalties):
     assert out["counters"].tolist() == exp
     assert 0 < exp[3] < b.n
     al.close()
+
+
+@pytest.mark.parametrize("mode", ["semi_global", "out_of_band", "general_penalties"])
+def test_gpu_benchmark_batch_when_greedy_is_no_upper_bound(pkg, ol, mode):
+    """The verifier sizes its band from the greedy penalty, which is NOT an upper bound on the optimum in SEMI_GLOBAL
+    mode (lane switches at the ends are free) nor for pairs with |n-m| > k (the out-of-band destination lane counts
+    no hurdles).  A banded result above the bound exposes that, and the pair is redone from its exact optimum: NW
+    penalties, their tracebacks (through the coverage counter) and all counters must still equal the oracle's."""
+    rng = np.random.default_rng({"semi_global": 911, "out_of_band": 912, "general_penalties": 913}[mode])
+    x, o, e = (2, 3, 1) if mode == "general_penalties" else (1, 1, 1)
+    g = 0 if mode == "semi_global" else 1
+    # indel-heavy pairs with length differences well beyond k = 3
+    b = ol.random_batch(rng, 20000, 20, 128, 0.25, 0.7 if mode != "semi_global" else 0.4, 40)
+    og = ol.oracle_greedy(b, ol.make_params(3, x, o, e, 2, g), threads=8)
+    on = ol.oracle_nw(b, x, o, e, threads=8)
+    below = int((og["cost"] < on["penalty"]).sum())
+    assert below > 0, "the case must contain pairs whose greedy penalty is below the optimum"
+    exp = [int(v) for v in ol.oracle_metrics(b, og, on)]
+    al = pkg.Aligner(x=x, o=o, e=e, max_length=128, alignment_type=1 - g)
+    out = al.benchmark_batch(b.reads, b.read_off, b.refs, b.ref_off, want_penalties=True)
+    assert out["greedy_cost"].tolist() == og["cost"].tolist()
+    assert int((out["nw_penalty"] != on["penalty"]).sum()) == 0
+    assert out["counters"].tolist() == exp
+    # the same through the stand-alone verifier call with the greedy penalties as (invalid) bounds
+    nw = al.nw_batch(b.reads, b.read_off, b.refs, b.ref_off, bound=og["cost"], want_ops=True)
+    assert int((nw["penalty"] != on["penalty"]).sum()) == 0
+    assert np.array_equal(nw["op_off"], on["op_off"]) and np.array_equal(nw["ops"][:nw["n_ops"]], on["ops"])
+    al.close()

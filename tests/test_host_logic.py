@@ -125,3 +125,27 @@ def test_numa_binding_helper(pkg, tmp_path, monkeypatch):
     shutil.rmtree(sysfs / "devices/system/node/node0")
     assert shard.bind_host_to_device(0, str(sysfs)) is None
     assert shard._parse_cpulist("0-3,8,10-11") == {0, 1, 2, 3, 8, 10, 11}
+
+
+@pytest.mark.parametrize("variant", [1, 2])
+def test_mask_variant_logic_matches_oracle_and_golden(ol, host_sim, golden, variant):
+    """flip_word<FLIP> (greedy.cuh) -- flip_short_hurdles(2) and flip_short_hurdles(1).flip_short_matches(1), rebuilt word
+    by word inside the highway scans -- against the oracle for W = 1..4 and against the unmodified reference's outputs."""
+    rng = np.random.default_rng(640 + variant)
+    for W in (1, 2, 3, 4):
+        for (k, x, o, e, g) in [(3, 1, 1, 1, 1), (7, 2, 3, 1, 1), (3, 1, 1, 1, 0)]:
+            b = ol.random_batch(rng, 1200, 1, 64 * W, 0.35, 0.3, 50)
+            p = ol.make_params(k, x, o, e, W, g, mask_variant=variant)
+            r = ol.oracle_greedy(b, p, threads=4, want_text=True)
+            cost, text, st, steps = sim_lib.sim_greedy(host_sim, ol, b, p, mask_variant=variant)
+            assert st == 0
+            assert cost.tolist() == r["cost"].tolist(), (W, k)
+            assert text == r["text"], (W, k)
+            assert steps == r["steps"]
+    for s in golden("greedy_ref_mask.json")["sets"]:
+        if s["variant"] != variant:
+            continue
+        ps = s["params"]
+        p = ol.make_params(ps["k"], ps["x"], ps["o"], ps["e"], 2, 1, tuple(ps["probs"]), mask_variant=variant)
+        cost, text, st, _ = sim_lib.sim_greedy(host_sim, ol, _batch(ol, s["pairs"]), p, mask_variant=variant)
+        assert st == 0 and cost.tolist() == s["cost"] and text == s["cigar"], s["name"]

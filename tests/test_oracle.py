@@ -277,3 +277,31 @@ def test_coverage_port_vs_reference_fuzz(ol):
         assert c1 == c2, (a, bb)
         n_cov += 1
     assert n_lcm + n_cov >= 100000
+
+
+# ---- the aligner's other mask variants: flip_short_hurdles(2), flip_short_matches(1) ----
+def test_oracle_mask_variants_match_golden(ol, golden):
+    total = 0
+    for s in golden("greedy_ref_mask.json")["sets"]:
+        ps = s["params"]
+        p = ol.make_params(ps["k"], ps["x"], ps["o"], ps["e"], 2, 1, tuple(ps["probs"]), mask_variant=s["variant"])
+        r = ol.oracle_greedy(_batch(ol, s["pairs"]), p, threads=4, want_text=True)
+        assert r["cost"].tolist() == s["cost"], (s["name"], s["variant"])
+        assert r["text"] == s["cigar"], (s["name"], s["variant"])
+        total += len(s["cost"])
+    assert total > 4000
+
+
+def test_oracle_mask_variants_vs_reference_fresh(ol):
+    """Fresh fuzz against the unmodified reference whose call site hurdle_matrix.h:453 runs the other variant."""
+    rng = np.random.default_rng(515)
+    for variant in (1, 2):
+        if not ol.ref_mask_available(variant):
+            pytest.skip("oracle/_ref/libgasma_ref_mask*.so not built (needs /root/reference)")
+        b = ol.random_batch(rng, 5000, 1, 128, 0.3, 0.3, 50)
+        r = ol.oracle_greedy(b, ol.make_params(4, 1, 2, 1, mask_variant=variant), threads=4, want_text=True)
+        f = ol.ref_greedy(b, 4, 1, 2, 1, threads=4, mask_variant=variant)
+        assert r["cost"].tolist() == f["cost"].tolist()
+        assert r["text"] == f["text"]
+        base = ol.oracle_greedy(b, ol.make_params(4, 1, 2, 1), threads=4)
+        assert int((base["cost"] != r["cost"]).sum()) > 100      # the variants really are different aligners
