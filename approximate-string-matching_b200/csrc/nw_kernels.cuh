@@ -239,10 +239,10 @@ struct NwCounterArgs {
 };
 
 #ifndef GASMA_NW_MINBLOCKS
-#define GASMA_NW_MINBLOCKS 1
+#define GASMA_NW_MINBLOCKS 12   // caps the registers at 80 (12 CTAs of 64 threads per SM): measured 0.587 ms vs 0.601 uncapped
 #endif
 template <int W, int T, int MODE>
-__global__ void __launch_bounds__(T, GASMA_NW_MINBLOCKS)
+__global__ void __launch_bounds__(T, ((W <= 2 ? GASMA_NW_MINBLOCKS : (W == 3 ? 10 : 8)) * 64) / T)   // stated for 64-thread CTAs; wider planes need more registers
 nw_band_kernel(const uint8_t* __restrict__ reads, const uint32_t* __restrict__ read_off, const uint8_t* __restrict__ refs,
                const uint32_t* __restrict__ ref_off, long long n, const int32_t* bound, int32_t* penalty,
                uint16_t* __restrict__ ops_stage, int ops_stride, uint32_t* __restrict__ nops_out,
