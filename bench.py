@@ -83,6 +83,35 @@ def lib_sha(pkg):
     return h.hexdigest()[:16]
 
 
+def ncu_figures(pkg, leg):
+    """Per-launch DRAM bytes / executed instructions of the leg's dominant kernel from profiles/traffic.json -- only if
+    they were taken from the very library that is loaded (SHA-1 match); otherwise None.  Written by
+    tools/update_traffic.py from a metrics-only ncu pass of this bench command (tools/profile_round.sh)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f)
+        if t.get("library_sha1") != lib_sha(pkg):
+            return None
+        return t["legs"].get(leg)
+    except Exception:
+        return None
+
+
+def attach_ncu(roof, fig, k_ms, sm_count, sm_mhz):
+    """roofline.traffic + the issue-slot view of the same launch (instructions from ncu, time from the live run)."""
+    if not fig:
+        roof["traffic_note"] = "no ncu figures for this library build in profiles/traffic.json (SHA-1 mismatch): traffic left null"
+        return
+    roof["traffic"] = fig["traffic_bytes"]
+    roof["ncu"] = {k: fig[k] for k in ("kernel", "issue_active_pct", "alu_pipe_pct", "avg_active_threads", "warp_instructions",
+                                       "dram_read_bytes", "dram_write_bytes", "source")}
+    if sm_mhz:
+        peak = sm_count * 4 * sm_mhz * 1e6          # 4 schedulers per SM, one warp instruction per clock each
+        ach = fig["warp_instructions"] / (k_ms * 1e-3)
+        roof["issue"] = {"bound": "issue slots (4 schedulers/SM)", "achieved": ach / 1e9, "peak": peak / 1e9, "unit": "G warp-instr/s",
+                         "frac": ach / peak, "note": "utilisation of the instructions the kernel executes, not a fraction of an algorithmic minimum"}
+
+
 def workload_name(a):
     if a.profile == "illumina":
         return ("synthetic Illumina-profile %d bp reads (per base: 2.452%% mismatch, 0.0468%% insert, 0.0553%% delete), "
@@ -593,6 +622,10 @@ def run_b200(a):
             dist.destroy_process_group()
         return
     roof = head["roofline"]
+    sms = torch.cuda.get_device_properties(local).multi_processor_count
+    attach_ncu(roof, ncu_figures(pkg, "headline"), roof["kernel_ms"], sms, clocks.get("sm_mhz") if clocks else None)
+    if full is not None:
+        attach_ncu(full["roofline"], ncu_figures(pkg, "full_path"), full["roofline"]["kernel_ms"], sms, clocks.get("sm_mhz") if clocks else None)
     roof["note"] = ("integer bit-vector work: the kernel is bound by instruction issue, not by HBM; frac is reported against the "
                     "HBM roofline as the contract asks (profiles/ holds the ncu issue / pipe figures of this build)")
     line = {
