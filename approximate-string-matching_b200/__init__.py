@@ -46,6 +46,7 @@ EXPORTS = [
     "gasma_generate_ref_capacity", "gasma_generate_dev", "gasma_generate", "gasma_render_cigar",
     "gasma_benchmark_batch", "gasma_benchmark_batch_dev", "gasma_leap_batch", "gasma_leap_batch_dev",
     "gasma_greedy_batch_dev_noalloc", "gasma_set_mask_variant",
+    "gasma_pack2bit_stream", "gasma_pack2bit_stream_dev", "gasma_greedy_batch_packed", "gasma_greedy_batch_packed_dev",
 ]
 
 _lib = None
@@ -85,6 +86,10 @@ def lib():
         getattr(L, name).argtypes = [vp, vp, vp, vp, vp, i64, vp, vp, i64, vp]
     for name in ("gasma_nw_batch", "gasma_nw_batch_dev"):
         getattr(L, name).argtypes = [vp, vp, vp, vp, vp, i64, vp, vp, vp, i64, vp]
+    for name in ("gasma_pack2bit_stream", "gasma_pack2bit_stream_dev"):
+        getattr(L, name).argtypes = [vp, vp, i64, vp, vp]
+    for name in ("gasma_greedy_batch_packed", "gasma_greedy_batch_packed_dev"):
+        getattr(L, name).argtypes = [vp, vp, vp, vp, vp, vp, vp, i64, vp, vp, i64, vp]
     L.gasma_metrics_dev.argtypes = [vp, vp, vp, i64] + [vp] * 8
     L.gasma_generate_ref_capacity.argtypes = [C.POINTER(GenConfig), i64]
     L.gasma_generate_ref_capacity.restype = i64
@@ -140,9 +145,10 @@ class Aligner:
         self.device = device
 
     def close(self):
-        if getattr(self, "_ctx", None) and self._ctx.value:
-            self._L.gasma_destroy(self._ctx)
-            self._ctx = C.c_void_p()
+        ctx = getattr(self, "_ctx", None)
+        if ctx is not None and ctx.value:
+            self._L.gasma_destroy(ctx)
+            self._ctx = None
 
     __del__ = close
 
@@ -211,6 +217,38 @@ class Aligner:
         if want_ops:
             out["n_ops"] = int(out["op_off"][n])
         return out
+
+    # -- packed input (2-bit streams: one uint16 per 16 characters and plane, see include/gasma_b200.h) ----------------
+    def pack2bit_stream(self, seqs, total=None):
+        total = len(seqs) if total is None else total
+        nw = (total + 15) // 16
+        p0, p1 = np.zeros(nw, np.uint16), np.zeros(nw, np.uint16)
+        self._check(self._L.gasma_pack2bit_stream(self._ctx, _np_ptr(seqs), total, _np_ptr(p0), _np_ptr(p1)))
+        return p0, p1
+
+    def pack2bit_stream_dev(self, d_seqs, total, d_p0, d_p1):
+        self._check(self._L.gasma_pack2bit_stream_dev(self._ctx, _dev_ptr(d_seqs), total, _dev_ptr(d_p0), _dev_ptr(d_p1)))
+
+    def greedy_batch_packed(self, r0, r1, read_off, f0, f1, ref_off, want_ops=True, ops_cap=None, out=None):
+        n = len(read_off) - 1
+        if out is None:
+            out = {"cost": np.empty(n, np.int32)}
+            if want_ops:
+                out["ops"] = np.empty(ops_cap if ops_cap is not None else max(16, 24 * n), np.uint16)
+                out["op_off"] = np.empty(n + 1, np.uint32)
+        ops = out.get("ops") if want_ops else None
+        op_off = out.get("op_off") if want_ops else None
+        self._check(self._L.gasma_greedy_batch_packed(self._ctx, _np_ptr(r0), _np_ptr(r1), _np_ptr(read_off), _np_ptr(f0), _np_ptr(f1),
+                                                      _np_ptr(ref_off), n, _np_ptr(out["cost"]), _np_ptr(ops),
+                                                      0 if ops is None else len(ops), _np_ptr(op_off)))
+        if want_ops:
+            out["n_ops"] = int(out["op_off"][n])
+        return out
+
+    def greedy_batch_packed_dev(self, d_r0, d_r1, d_read_off, d_f0, d_f1, d_ref_off, n, d_cost, d_ops=None, d_op_off=None):
+        self._check(self._L.gasma_greedy_batch_packed_dev(self._ctx, _dev_ptr(d_r0), _dev_ptr(d_r1), _dev_ptr(d_read_off), _dev_ptr(d_f0),
+                                                          _dev_ptr(d_f1), _dev_ptr(d_ref_off), n, _dev_ptr(d_cost), _dev_ptr(d_ops),
+                                                          0 if d_ops is None else d_ops.numel(), _dev_ptr(d_op_off)))
 
     def leap_batch(self, reads, read_off, refs, ref_off):
         """LEAP comparator penalties (benchmark::_run_LEAP); INT32_MIN where no lane converges."""

@@ -41,6 +41,11 @@ struct gasma_ctx {
     int greedy_warps = 0;       // warps per CTA of the thread-per-pair greedy kernel: 0 = most resident warps (env GASMA_GREEDY_WARPS: 2, 4, 8)
     bool counter_clean = false;  // the greedy kernel's chunk counter is 0 (left so by scan_tiles_kernel of the previous batch)
     int auto_warps = 0;         // the choice made for the current (W, lanes); reset by derive()
+    // packed input of the launch being enqueued (gasma_greedy_batch_packed): plane-1 streams of reads / refs; the
+    // plane-0 streams travel in the reads / refs arguments.  Null = ASCII input.  Set and cleared by the packed entry points.
+    const uint16_t* pk_r1 = nullptr;
+    const uint16_t* pk_f1 = nullptr;
+    DevBuf d_r1, d_f1;          // device mirrors of the plane-1 streams (host-pointer packed call)
     int mask_variant = 0;       // gasma_set_mask_variant: 0 flip_short_hurdles(1), 1 flip_short_hurdles(2), 2 + flip_short_matches(1)
     int correction = 0;         // gasma_set_correction: widened band of the reference's -DCORRECTION build
     int max_delta = 0;          // largest |ref_len - read_len| the widened band has lane slots for
@@ -50,6 +55,7 @@ struct gasma_ctx {
     // the kernels of slice i
     static constexpr int kSlices = 16;  // most slices a call is cut into
     int slices = 8;                     // slices actually used (env GASMA_SLICES)
+    bool slices_from_env = false;
     bool trace = false;                 // env GASMA_TRACE: per-call timing of the host-pointer path on stderr
     cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr, ev_t2 = nullptr;
     cudaStream_t copy_in = nullptr, copy_out = nullptr;
@@ -164,7 +170,8 @@ int launch_greedy_t(gasma_ctx* ctx, const uint8_t* reads, const uint32_t* roff, 
     if (grid * WARPS > chunks) grid = (chunks + WARPS - 1) / WARPS;
     if (!ctx->counter_clean) CU(cudaMemsetAsync(chunk_counter, 0, 4, ctx->stream));
     kern<<<(unsigned)grid, 32 * WARPS, smem, ctx->stream>>>(ctx->kp, reads, roff, refs, foff, (long long)n, cost, rows, stage, stride,
-                                                          nops, chunk_counter, ctx->refill_threshold, status, steps, tsums);
+                                                          nops, chunk_counter, ctx->refill_threshold, status, steps, tsums,
+                                                          ctx->pk_r1, ctx->pk_f1);
     CU(cudaGetLastError());
     ctx->launches++;
     return GASMA_OK;
@@ -311,7 +318,7 @@ int gasma_create(const gasma_params* params, int device, gasma_ctx** out) {
     c->trace = getenv("GASMA_TRACE") != nullptr;
     if (const char* env = getenv("GASMA_SLICES")) {             // pipeline depth of the host-pointer calls; same results
         const int v = atoi(env);
-        if (v >= 1 && v <= gasma_ctx::kSlices) c->slices = v;
+        if (v >= 1 && v <= gasma_ctx::kSlices) { c->slices = v; c->slices_from_env = true; }
     }
     derive(c);
     if (greedy_tile_threads(c) == 0) {
@@ -349,7 +356,7 @@ void gasma_destroy(gasma_ctx* c) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     DevBuf* bufs[] = {&c->g_sums[0], &c->g_sums[1], &c->ops_rows, &c->ops_stage, &c->nops, &c->tile_sums, &c->tile_bases, &c->misc, &c->d_reads, &c->d_refs,
                       &c->d_read_off, &c->d_ref_off, &c->d_cost, &c->d_ops, &c->d_op_off, &c->d_p0, &c->d_p1, &c->gen_len, &c->d_bound, &c->nw_deferred, &c->nw_tb, &c->nw_pool_hi, &c->nw_pool_tb,
-                      &c->bm_hard, &c->bm_gops, &c->bm_goff, &c->bm_nops, &c->bm_noff, &c->bm_gcost, &c->bm_nwpen, &c->bm_counters, &c->bm_answers, &c->bm_nstage, &c->bm_nnops};
+                      &c->bm_hard, &c->bm_gops, &c->bm_goff, &c->bm_nops, &c->bm_noff, &c->bm_gcost, &c->bm_nwpen, &c->bm_counters, &c->bm_answers, &c->bm_nstage, &c->bm_nnops, &c->d_r1, &c->d_f1};
     for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
     if (c->h_misc) cudaFreeHost(c->h_misc);
     for (auto& kind : c->ev) for (auto& pair : kind) for (auto& ev : pair) if (ev) cudaEventDestroy(ev);
@@ -518,6 +525,8 @@ int greedy_dev_impl(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_read_
         }
         return GASMA_OK;
     }
+    if (ctx->pk_r1 && ctx->W > 4)
+        return fail(ctx, GASMA_E_UNSUPPORTED, "packed input covers max_length <= 256 (one alignment per thread)");
     const int warps = greedy_tile_threads(ctx) / 32;
     const int64_t ntiles = (n + kCsrTile - 1) / kCsrTile;
     const int stride = 2 * ctx->params.max_length + 8;
@@ -587,15 +596,18 @@ int check_offsets(gasma_ctx* ctx, const uint32_t* off, int64_t n, const char* wh
 // copy_out (D2H); the CSR op array is shared by all slices, op_off continues across them on the device.
 int greedy_batch_pipelined_body(gasma_ctx* ctx, const char* reads, const uint32_t* read_off, const char* refs,
                                 const uint32_t* ref_off, int64_t n, int32_t* cost, gasma_cigar_op* ops, int64_t ops_cap,
-                                uint32_t* op_off);
+                                uint32_t* op_off, const uint16_t* reads_p1, const uint16_t* refs_p1);
 
 // Every error exit of the pipelined call goes through here: copies from / into the caller's buffers may still be
 // queued on the copy streams, and the per-tile op counts may be half accumulated.  Drain all three streams and put
 // the context back into its clean state before the caller gets its buffers back.
+// reads_p1 / refs_p1 != nullptr: packed input -- reads / refs are the HOST plane-0 streams (uint16 per 16 characters),
+// these the plane-1 streams (gasma_greedy_batch_packed); the offsets are the same CSR offsets in characters.
 int greedy_batch_pipelined(gasma_ctx* ctx, const char* reads, const uint32_t* read_off, const char* refs,
                            const uint32_t* ref_off, int64_t n, int32_t* cost, gasma_cigar_op* ops, int64_t ops_cap,
-                           uint32_t* op_off) {
-    const int rc = greedy_batch_pipelined_body(ctx, reads, read_off, refs, ref_off, n, cost, ops, ops_cap, op_off);
+                           uint32_t* op_off, const uint16_t* reads_p1 = nullptr, const uint16_t* refs_p1 = nullptr) {
+    const int rc = greedy_batch_pipelined_body(ctx, reads, read_off, refs, ref_off, n, cost, ops, ops_cap, op_off, reads_p1, refs_p1);
+    ctx->pk_r1 = ctx->pk_f1 = nullptr;
     if (rc != GASMA_OK && rc != GASMA_E_CAPACITY) {
         const std::string keep = ctx->err;
         cudaStreamSynchronize(ctx->copy_in);
@@ -616,8 +628,11 @@ int greedy_batch_pipelined(gasma_ctx* ctx, const char* reads, const uint32_t* re
 
 int greedy_batch_pipelined_body(gasma_ctx* ctx, const char* reads, const uint32_t* read_off, const char* refs,
                                 const uint32_t* ref_off, int64_t n, int32_t* cost, gasma_cigar_op* ops, int64_t ops_cap,
-                                uint32_t* op_off) {
-    const int S = ctx->slices;
+                                uint32_t* op_off, const uint16_t* reads_p1, const uint16_t* refs_p1) {
+    const bool packed = reads_p1 != nullptr;
+    // packed input is 4x smaller and comes as four arrays: with 8 slices its copies are ~2.5 MB each and the per-copy
+    // overhead shows (measured per 1 M pairs: 4 slices 2.04 ms, 8: 2.21, 12: 2.52, 16: 2.96); GASMA_SLICES overrides
+    const int S = packed && !ctx->slices_from_env ? 4 : ctx->slices;
     const size_t ob = (size_t)(n + 1) * 4;
     int64_t edge[gasma_ctx::kSlices + 1];
     // The call ends one slice's kernels + result copies after the last input byte has arrived, so the last two slices
@@ -656,8 +671,22 @@ int greedy_batch_pipelined_body(gasma_ctx* ctx, const char* reads, const uint32_
             return fail(ctx, GASMA_E_ARG, "offsets are not non-decreasing around pair %lld", (long long)edge[i]);
     for (int i = 0; i < S; ++i) {
         const size_t r0 = read_off[edge[i]], r1 = read_off[edge[i + 1]], f0 = ref_off[edge[i]], f1 = ref_off[edge[i + 1]];
-        if (r1 > r0) CU(cudaMemcpyAsync(d_reads + r0, reads + r0, r1 - r0, cudaMemcpyHostToDevice, ctx->copy_in));
-        if (f1 > f0) CU(cudaMemcpyAsync(d_refs + f0, refs + f0, f1 - f0, cudaMemcpyHostToDevice, ctx->copy_in));
+        if (!packed) {
+            if (r1 > r0) CU(cudaMemcpyAsync(d_reads + r0, reads + r0, r1 - r0, cudaMemcpyHostToDevice, ctx->copy_in));
+            if (f1 > f0) CU(cudaMemcpyAsync(d_refs + f0, refs + f0, f1 - f0, cudaMemcpyHostToDevice, ctx->copy_in));
+        } else {
+            // the slice's chunk range of all four streams (2 bytes per 16 characters); a chunk shared with the
+            // neighbouring slice is simply copied by both
+            const size_t rc0 = 2 * (r0 >> 4), rc1 = 2 * ((r1 + 15) >> 4), fc0 = 2 * (f0 >> 4), fc1 = 2 * ((f1 + 15) >> 4);
+            if (rc1 > rc0) {
+                CU(cudaMemcpyAsync(d_reads + rc0, reads + rc0, rc1 - rc0, cudaMemcpyHostToDevice, ctx->copy_in));
+                CU(cudaMemcpyAsync((char*)ctx->d_r1.p + rc0, (const char*)reads_p1 + rc0, rc1 - rc0, cudaMemcpyHostToDevice, ctx->copy_in));
+            }
+            if (fc1 > fc0) {
+                CU(cudaMemcpyAsync(d_refs + fc0, refs + fc0, fc1 - fc0, cudaMemcpyHostToDevice, ctx->copy_in));
+                CU(cudaMemcpyAsync((char*)ctx->d_f1.p + fc0, (const char*)refs_p1 + fc0, fc1 - fc0, cudaMemcpyHostToDevice, ctx->copy_in));
+            }
+        }
         CU(cudaEventRecord(ctx->ev_in[i], ctx->copy_in));
     }
     if (ctx->trace) CU(cudaEventRecord(ctx->ev_t1, ctx->copy_in));
@@ -667,6 +696,7 @@ int greedy_batch_pipelined_body(gasma_ctx* ctx, const char* reads, const uint32_
         if (vrc) return vrc;
     }
     CU(cudaMemsetAsync(misc + 8 + ctx->base_parity, 0, 4, ctx->stream));   // running op total the first slice starts from
+    if (packed) { ctx->pk_r1 = (const uint16_t*)ctx->d_r1.p; ctx->pk_f1 = (const uint16_t*)ctx->d_f1.p; }
     for (int i = 0; i < S; ++i) {
         const int64_t lo = edge[i], cnt = edge[i + 1] - edge[i];
         if (cnt == 0) { CU(cudaEventRecord(ctx->ev_off[i], ctx->copy_out)); continue; }
@@ -701,7 +731,7 @@ int greedy_batch_pipelined_body(gasma_ctx* ctx, const char* reads, const uint32_
         cudaEventElapsedTime(&all_ms, ctx->ev_t0, ctx->ev_t2);
         const double wall = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - wall0).count();
         fprintf(stderr, "[gasma] pipelined call: %d slices, H2D %.3f ms (%.1f GB/s), first copy -> last offsets on host %.3f ms, wall %.3f ms\n",
-                S, h2d_ms, (double)(read_off[n] + ref_off[n] + 2 * ob) / h2d_ms / 1e6, all_ms, wall);
+                S, h2d_ms, (double)((packed ? (read_off[n] + ref_off[n]) / 4 : read_off[n] + ref_off[n]) + 2 * ob) / h2d_ms / 1e6, all_ms, wall);
     }
     if (overflow)
         return fail(ctx, GASMA_E_CAPACITY, "ops buffer holds %lld ops, %lld needed", (long long)ops_cap, (long long)op_off[n]);
@@ -808,6 +838,101 @@ int gasma_greedy_batch(gasma_ctx* ctx, const char* reads, const uint32_t* read_o
     rc = greedy_dev_impl(ctx, (const char*)ctx->d_reads.p, (const uint32_t*)ctx->d_read_off.p, (const char*)ctx->d_refs.p,
                          (const uint32_t*)ctx->d_ref_off.p, n, (int32_t*)ctx->d_cost.p,
                          ops ? (gasma_cigar_op*)ctx->d_ops.p : nullptr, ops_cap, ops ? (uint32_t*)ctx->d_op_off.p : nullptr);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(cost, ctx->d_cost.p, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    if (ops) CU(cudaMemcpyAsync(op_off, ctx->d_op_off.p, ob, cudaMemcpyDeviceToHost, ctx->stream));
+    if ((rc = gasma_synchronize(ctx))) return rc;
+    if (ops) {
+        const int64_t total = op_off[n];
+        if (total > ops_cap) return fail(ctx, GASMA_E_CAPACITY, "ops buffer holds %lld ops, %lld needed", (long long)ops_cap, (long long)total);
+        if (total) CU(cudaMemcpyAsync(ops, ctx->d_ops.p, (size_t)total * 2, cudaMemcpyDeviceToHost, ctx->stream));
+        CU(cudaStreamSynchronize(ctx->stream));
+    }
+    return GASMA_OK;
+}
+
+// ---- packed input: 2-bit streams ---------------------------------------------------------------
+int gasma_pack2bit_stream_dev(gasma_ctx* ctx, const char* d_seqs, int64_t total_chars, uint16_t* d_plane0, uint16_t* d_plane1) {
+    if (!ctx) return GASMA_E_ARG;
+    if (total_chars < 0 || total_chars >= ((int64_t)1 << 32) || !d_plane0 || !d_plane1) return fail(ctx, GASMA_E_ARG, "bad argument");
+    if (!aligned16(d_seqs)) return fail(ctx, GASMA_E_ARG, "sequence buffer must be 16-byte aligned");
+    CU(cudaSetDevice(ctx->device));
+    if (total_chars == 0) return GASMA_OK;
+    const int64_t nchunks = (total_chars + 15) / 16;
+    int64_t grid = (nchunks + 255) / 256;
+    if (grid > (int64_t)ctx->sm_count * 16) grid = (int64_t)ctx->sm_count * 16;
+    pack2bit_stream_kernel<<<(unsigned)grid, 256, 0, ctx->stream>>>((const uint8_t*)d_seqs, (uint32_t)total_chars, d_plane0, d_plane1);
+    CU(cudaGetLastError());
+    ctx->launches++;
+    return GASMA_OK;
+}
+
+int gasma_pack2bit_stream(gasma_ctx* ctx, const char* seqs, int64_t total_chars, uint16_t* plane0, uint16_t* plane1) {
+    if (!ctx) return GASMA_E_ARG;
+    if (total_chars < 0 || total_chars >= ((int64_t)1 << 32) || !plane0 || !plane1 || (total_chars && !seqs)) return fail(ctx, GASMA_E_ARG, "bad argument");
+    if (total_chars == 0) return GASMA_OK;
+    CU(cudaSetDevice(ctx->device));
+    const size_t sb = (size_t)((total_chars + 15) / 16) * 2;
+    int rc;
+    if ((rc = reserve(ctx, ctx->d_reads, (size_t)total_chars + 16))) return rc;
+    if ((rc = reserve(ctx, ctx->d_p0, sb))) return rc;
+    if ((rc = reserve(ctx, ctx->d_p1, sb))) return rc;
+    CU(cudaMemcpyAsync(ctx->d_reads.p, seqs, (size_t)total_chars, cudaMemcpyHostToDevice, ctx->stream));
+    if ((rc = gasma_pack2bit_stream_dev(ctx, (const char*)ctx->d_reads.p, total_chars, (uint16_t*)ctx->d_p0.p, (uint16_t*)ctx->d_p1.p))) return rc;
+    CU(cudaMemcpyAsync(plane0, ctx->d_p0.p, sb, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaMemcpyAsync(plane1, ctx->d_p1.p, sb, cudaMemcpyDeviceToHost, ctx->stream));
+    return gasma_synchronize(ctx);
+}
+
+int gasma_greedy_batch_packed_dev(gasma_ctx* ctx, const uint16_t* d_read_p0, const uint16_t* d_read_p1, const uint32_t* d_read_off,
+                                  const uint16_t* d_ref_p0, const uint16_t* d_ref_p1, const uint32_t* d_ref_off, int64_t n_pairs,
+                                  int32_t* d_cost, gasma_cigar_op* d_ops, int64_t ops_cap, uint32_t* d_op_off) {
+    if (!ctx) return GASMA_E_ARG;
+    if (!d_read_p0 || !d_read_p1 || !d_ref_p0 || !d_ref_p1) return fail(ctx, GASMA_E_ARG, "null stream pointer");
+    ctx->pk_r1 = d_read_p1;
+    ctx->pk_f1 = d_ref_p1;
+    const int rc = greedy_dev_impl(ctx, (const char*)d_read_p0, d_read_off, (const char*)d_ref_p0, d_ref_off, n_pairs, d_cost, d_ops, ops_cap, d_op_off);
+    ctx->pk_r1 = ctx->pk_f1 = nullptr;
+    return rc;
+}
+
+int gasma_greedy_batch_packed(gasma_ctx* ctx, const uint16_t* read_p0, const uint16_t* read_p1, const uint32_t* read_off,
+                              const uint16_t* ref_p0, const uint16_t* ref_p1, const uint32_t* ref_off, int64_t n,
+                              int32_t* cost, gasma_cigar_op* ops, int64_t ops_cap, uint32_t* op_off) {
+    if (!ctx) return GASMA_E_ARG;
+    if (n < 0 || !read_off || !ref_off || !cost || !read_p0 || !read_p1 || !ref_p0 || !ref_p1) return fail(ctx, GASMA_E_ARG, "bad argument");
+    if ((ops != nullptr) != (op_off != nullptr)) return fail(ctx, GASMA_E_ARG, "ops and op_off must be given together");
+    if (ctx->W > 4) return fail(ctx, GASMA_E_UNSUPPORTED, "packed input covers max_length <= 256 (one alignment per thread)");
+    if (n == 0) { if (op_off) op_off[0] = 0; return GASMA_OK; }
+    int rc;
+    const bool pipelined = n >= 65536;
+    if (!pipelined) {
+        if ((rc = check_offsets(ctx, read_off, n, "read"))) return rc;
+        if ((rc = check_offsets(ctx, ref_off, n, "ref"))) return rc;
+    }
+    CU(cudaSetDevice(ctx->device));
+    const size_t rb = 2 * (((size_t)read_off[n] + 15) >> 4), fb = 2 * (((size_t)ref_off[n] + 15) >> 4), ob = (size_t)(n + 1) * 4;
+    if ((rc = reserve(ctx, ctx->d_reads, rb + 16))) return rc;
+    if ((rc = reserve(ctx, ctx->d_r1, rb + 16))) return rc;
+    if ((rc = reserve(ctx, ctx->d_refs, fb + 16))) return rc;
+    if ((rc = reserve(ctx, ctx->d_f1, fb + 16))) return rc;
+    if ((rc = reserve(ctx, ctx->d_read_off, ob))) return rc;
+    if ((rc = reserve(ctx, ctx->d_ref_off, ob))) return rc;
+    if ((rc = reserve(ctx, ctx->d_cost, (size_t)n * 4))) return rc;
+    if (ops) {
+        if ((rc = reserve(ctx, ctx->d_op_off, ob))) return rc;
+        if ((rc = reserve(ctx, ctx->d_ops, (size_t)(ops_cap > 0 ? ops_cap : 1) * 2))) return rc;
+    }
+    if (pipelined)
+        return greedy_batch_pipelined(ctx, (const char*)read_p0, read_off, (const char*)ref_p0, ref_off, n, cost, ops, ops_cap, op_off, read_p1, ref_p1);
+    if (rb) { CU(cudaMemcpyAsync(ctx->d_reads.p, read_p0, rb, cudaMemcpyHostToDevice, ctx->stream)); CU(cudaMemcpyAsync(ctx->d_r1.p, read_p1, rb, cudaMemcpyHostToDevice, ctx->stream)); }
+    if (fb) { CU(cudaMemcpyAsync(ctx->d_refs.p, ref_p0, fb, cudaMemcpyHostToDevice, ctx->stream)); CU(cudaMemcpyAsync(ctx->d_f1.p, ref_p1, fb, cudaMemcpyHostToDevice, ctx->stream)); }
+    CU(cudaMemcpyAsync(ctx->d_read_off.p, read_off, ob, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemcpyAsync(ctx->d_ref_off.p, ref_off, ob, cudaMemcpyHostToDevice, ctx->stream));
+    rc = gasma_greedy_batch_packed_dev(ctx, (const uint16_t*)ctx->d_reads.p, (const uint16_t*)ctx->d_r1.p, (const uint32_t*)ctx->d_read_off.p,
+                                       (const uint16_t*)ctx->d_refs.p, (const uint16_t*)ctx->d_f1.p, (const uint32_t*)ctx->d_ref_off.p, n,
+                                       (int32_t*)ctx->d_cost.p, ops ? (gasma_cigar_op*)ctx->d_ops.p : nullptr, ops_cap,
+                                       ops ? (uint32_t*)ctx->d_op_off.p : nullptr);
     if (rc) return rc;
     CU(cudaMemcpyAsync(cost, ctx->d_cost.p, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
     if (ops) CU(cudaMemcpyAsync(op_off, ctx->d_op_off.p, ob, cudaMemcpyDeviceToHost, ctx->stream));

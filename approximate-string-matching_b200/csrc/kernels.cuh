@@ -59,6 +59,38 @@ __device__ __forceinline__ bool stage_tile(const uint8_t* __restrict__ buf, uint
     return ok;
 }
 
+// The same for a batch that is ALREADY packed ("2-bit streams", gasma_pack2bit_stream): plane0 / plane1 hold one uint16
+// per 16 characters of the CSR buffer, i.e. exactly the layout stage_tile produces, so staging is a copy of the chunk
+// range.  Bits that belong to neighbouring strings inside a chunk are masked by the window extraction, as always.
+__device__ __forceinline__ bool stage_tile_packed(const uint16_t* __restrict__ plane0, const uint16_t* __restrict__ plane1,
+                                                  uint32_t base16, uint32_t end, uint16_t* stream0, uint16_t* stream1,
+                                                  int cap_chunks, int tid, int nthreads) {
+    int nchunks = (int)((end - base16 + 15u) >> 4);
+    const bool ok = nchunks <= cap_chunks;
+    if (!ok) nchunks = cap_chunks;
+    const uint32_t c0 = base16 >> 4;
+#pragma unroll 1
+    for (int c = tid; c < nchunks; c += nthreads) {
+        stream0[c] = plane0[c0 + c];
+        stream1[c] = plane1[c0 + c];
+    }
+    return ok;
+}
+
+// ASCII CSR buffer -> 2-bit streams (K1 for the packed entry points): one 16-byte chunk per thread, HBM-bound
+// (reads the bytes once, writes a quarter of them).  `total` = logical size of the buffer.
+__global__ void __launch_bounds__(256)
+pack2bit_stream_kernel(const uint8_t* __restrict__ seqs, uint32_t total, uint16_t* __restrict__ plane0, uint16_t* __restrict__ plane1) {
+    const uint32_t nchunks = (total + 15u) >> 4;
+    for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < nchunks; c += gridDim.x * blockDim.x) {
+        const uint4 q = load_chunk(seqs, 16u * c, total);
+        uint32_t p0, p1;
+        pack_chunk(q.x, q.y, q.z, q.w, p0, p1);
+        plane0[c] = (uint16_t)p0;
+        plane1[c] = (uint16_t)p1;
+    }
+}
+
 template <int W>
 __host__ __device__ constexpr int stream_chunks(int tile) { return tile * 4 * W + 2; }
 // uint16 elements per stream array incl. padding so that extract_plane / pair_init32 may read 2W+3 words from any start
@@ -93,7 +125,10 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
               int32_t* __restrict__ cost, uint16_t* __restrict__ ops_rows, uint16_t* __restrict__ ops_ovf, int ops_stride,
               uint32_t* __restrict__ nops_out, uint32_t* __restrict__ chunk_counter, int refill_threshold,
               uint32_t* __restrict__ status, unsigned long long* __restrict__ step_counter,
-              uint32_t* __restrict__ tile_sums) {   // optional: op count per kCsrTile pairs, accumulated here (input of compact_rows_kernel)
+              uint32_t* __restrict__ tile_sums,   // optional: op count per kCsrTile pairs, accumulated here (input of compact_rows_kernel)
+              // packed input (gasma_greedy_batch_packed): reads / refs then point at the plane-0 streams and these at the
+              // plane-1 streams of the two sides; null for ASCII input
+              const uint16_t* __restrict__ reads_p1, const uint16_t* __restrict__ refs_p1) {
     constexpr int BITS = 64 * W;
     constexpr int T = 32 * WARPS;
     constexpr int SE = stream_elems<W>(kPool);
@@ -155,11 +190,21 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
         } else if (pf == kOffsets) {
             const uint32_t r0 = __shfl_sync(0xffffffffu, nx_ro, 0) & ~127u, f0 = __shfl_sync(0xffffffffu, nx_fo, 0) & ~127u;
 #pragma unroll 1
-            for (uint32_t a = r0 + 128u * lane; a < nx_re; a += 128u * 32u)
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(reads + a));
+            if (reads_p1 == nullptr) {
 #pragma unroll 1
-            for (uint32_t a = f0 + 128u * lane; a < nx_fe; a += 128u * 32u)
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(refs + a));
+                for (uint32_t a = r0 + 128u * lane; a < nx_re; a += 128u * 32u)
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(reads + a));
+#pragma unroll 1
+                for (uint32_t a = f0 + 128u * lane; a < nx_fe; a += 128u * 32u)
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(refs + a));
+            } else if (lane < 4) {   // packed: 2 bits per character, a chunk's four stream ranges are a line or two each
+                const uint8_t* b = lane == 0 ? reads : (lane == 1 ? reinterpret_cast<const uint8_t*>(reads_p1)
+                                                                  : (lane == 2 ? refs : reinterpret_cast<const uint8_t*>(refs_p1)));
+                const uint32_t lo = (lane < 2 ? r0 : f0) >> 3, hi = (lane < 2 ? nx_re : nx_fe) >> 3;
+#pragma unroll 1
+                for (uint32_t a = lo & ~127u; a <= hi; a += 128u)
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(b + a));
+            }
             pf = kReady;
         }
     };
@@ -196,11 +241,18 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
                     rbase = __shfl_sync(0xffffffffu, pl_ro, 0) & ~15u;
                     fbase = __shfl_sync(0xffffffffu, pl_fo, 0) & ~15u;
                     pool_ok = true;
+                    if (reads_p1 == nullptr) {
 #pragma unroll 1
-                    for (int side = 0; side < 2; ++side)   // one instance of the pack code for both sides
-                        pool_ok &= stage_tile(side ? refs : reads, side ? fbase : rbase, side ? nx_fe : nx_re,
-                                              side ? ftotal : rtotal, side ? s_f0 : s_r0, side ? s_f1 : s_r1,
-                                              stream_chunks<W>(kPool), lane, 32);
+                        for (int side = 0; side < 2; ++side)   // one instance of the pack code for both sides
+                            pool_ok &= stage_tile(side ? refs : reads, side ? fbase : rbase, side ? nx_fe : nx_re,
+                                                  side ? ftotal : rtotal, side ? s_f0 : s_r0, side ? s_f1 : s_r1,
+                                                  stream_chunks<W>(kPool), lane, 32);
+                    } else {
+                        pool_ok &= stage_tile_packed(reinterpret_cast<const uint16_t*>(reads), reads_p1, rbase, nx_re, s_r0, s_r1,
+                                                     stream_chunks<W>(kPool), lane, 32);
+                        pool_ok &= stage_tile_packed(reinterpret_cast<const uint16_t*>(refs), refs_p1, fbase, nx_fe, s_f0, s_f1,
+                                                     stream_chunks<W>(kPool), lane, 32);
+                    }
                     __syncwarp();
                     pf = kNone;
                     advance();   // claim the chunk after this one right away

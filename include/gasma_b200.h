@@ -136,6 +136,27 @@ int gasma_greedy_batch_dev(gasma_ctx* ctx,
                            const char* d_refs, const uint32_t* d_ref_off, int64_t n_pairs,
                            int32_t* d_cost, gasma_cigar_op* d_ops, int64_t ops_cap, uint32_t* d_op_off);
 
+/* -- K2+K3 on pre-packed input ("2-bit streams") -------------------------------------------------- */
+/* The shape of the reference's own batch driver LEAP_SIMD/main.cpp:108-140, which converts its reads to 2-bit form
+ * BEFORE its timed loop: a caller that keeps reads packed moves 4x fewer bytes to the GPU (about 83 B per 150 bp pair
+ * instead of 308 B of ASCII) and the kernel skips K1.
+ * Packed form of a CSR string buffer: two bit streams with ONE BIT PER CHARACTER at the character's CSR position --
+ * plane0 bit i = (character i is C or T), plane1 bit i = (G or T), anything else 00 (sse3_convert2bit1's code,
+ * bit_convert.cpp:248) -- stored as uint16 words, word c = characters [16c, 16c+16), bit b = character 16c+b
+ * (LSB first).  ceil(total_chars / 16) words per plane; the CSR offsets stay the character offsets.
+ * gasma_pack2bit_stream converts a buffer; gasma_greedy_batch_packed is gasma_greedy_batch on such input (same
+ * outputs, bit for bit).  max_length <= 256. */
+int gasma_pack2bit_stream(gasma_ctx* ctx, const char* seqs, int64_t total_chars, uint16_t* plane0, uint16_t* plane1);
+int gasma_pack2bit_stream_dev(gasma_ctx* ctx, const char* d_seqs, int64_t total_chars, uint16_t* d_plane0, uint16_t* d_plane1);
+int gasma_greedy_batch_packed(gasma_ctx* ctx,
+                              const uint16_t* read_plane0, const uint16_t* read_plane1, const uint32_t* read_off,
+                              const uint16_t* ref_plane0, const uint16_t* ref_plane1, const uint32_t* ref_off, int64_t n_pairs,
+                              int32_t* cost, gasma_cigar_op* ops, int64_t ops_cap, uint32_t* op_off);
+int gasma_greedy_batch_packed_dev(gasma_ctx* ctx,
+                                  const uint16_t* d_read_plane0, const uint16_t* d_read_plane1, const uint32_t* d_read_off,
+                                  const uint16_t* d_ref_plane0, const uint16_t* d_ref_plane1, const uint32_t* d_ref_off, int64_t n_pairs,
+                                  int32_t* d_cost, gasma_cigar_op* d_ops, int64_t ops_cap, uint32_t* d_op_off);
+
 /* -- the greedy step without any allocation ------------------------------------------------------- */
 /* No counterpart in the reference; added for callers that cannot call
  * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same inputs, outputs

@@ -325,3 +325,33 @@ def test_gpu_mask_variants(pkg, ol, golden, variant):
         al.close()
     with pytest.raises(pkg.GasmaError):
         pkg.Aligner(max_length=512).set_mask_variant(1)
+
+
+@pytest.mark.parametrize("W", [1, 2, 3, 4])
+def test_gpu_packed_input_equals_ascii_input(pkg, ol, W):
+    """gasma_pack2bit_stream + gasma_greedy_batch_packed (2-bit streams in, 4x fewer bytes over the link) give exactly
+    what gasma_greedy_batch gives on the ASCII form of the same batch -- small (one copy) and large (pipelined slices)
+    batches, ragged lengths, non-ACGT bytes; and the streams themselves equal the oracle's packing bit for bit."""
+    rng = np.random.default_rng(7300 + W)
+    al = pkg.Aligner(k=4, max_length=64 * W)
+    for n, alphabet in ((3000, b"ACGT"), (70000, b"ACGT"), (2000, b"ACGTNacgt")):
+        b = ol.random_batch(rng, n, 0, 64 * W, 0.3, 0.3, 50, alphabet=alphabet)
+        r0, r1 = al.pack2bit_stream(b.reads)
+        f0, f1 = al.pack2bit_stream(b.refs)
+        # stream bit i = plane bit of character i (checked against the oracle's per-string packing on a few strings)
+        for i in rng.integers(0, b.n, 40):
+            lo, hi = int(b.read_off[i]), int(b.read_off[i + 1])
+            p0, p1 = ol.oracle_pack(b.reads[lo:hi].tobytes(), W)
+            bits0 = np.unpackbits(r0.view(np.uint8), bitorder="little")[lo:hi]
+            want0 = np.unpackbits(p0.view(np.uint8), bitorder="little")[:hi - lo]
+            assert np.array_equal(bits0, want0)
+            bits1 = np.unpackbits(r1.view(np.uint8), bitorder="little")[lo:hi]
+            assert np.array_equal(bits1, np.unpackbits(p1.view(np.uint8), bitorder="little")[:hi - lo])
+        a = al.greedy_batch(b.reads, b.read_off, b.refs, b.ref_off)
+        p = al.greedy_batch_packed(r0, r1, b.read_off, f0, f1, b.ref_off)
+        assert np.array_equal(a["cost"], p["cost"])
+        assert np.array_equal(a["op_off"], p["op_off"])
+        assert np.array_equal(a["ops"][:a["n_ops"]], p["ops"][:p["n_ops"]])
+        r = ol.oracle_greedy(b, ol.make_params(4, 1, 1, 1, W, 1), threads=8)
+        assert np.array_equal(p["cost"], r["cost"]) and np.array_equal(p["ops"][:p["n_ops"]], r["ops"])
+    al.close()
