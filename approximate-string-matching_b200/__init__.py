@@ -47,6 +47,7 @@ EXPORTS = [
     "gasma_benchmark_batch", "gasma_benchmark_batch_dev", "gasma_leap_batch", "gasma_leap_batch_dev",
     "gasma_greedy_batch_dev_noalloc", "gasma_set_mask_variant",
     "gasma_pack2bit_stream", "gasma_pack2bit_stream_dev", "gasma_greedy_batch_packed", "gasma_greedy_batch_packed_dev",
+    "gasma_allreduce_counters", "gasma_allreduce_counters_host", "gasma_nccl_version",
 ]
 
 _lib = None
@@ -90,6 +91,9 @@ def lib():
         getattr(L, name).argtypes = [vp, vp, i64, vp, vp]
     for name in ("gasma_greedy_batch_packed", "gasma_greedy_batch_packed_dev"):
         getattr(L, name).argtypes = [vp, vp, vp, vp, vp, vp, vp, i64, vp, vp, i64, vp]
+    L.gasma_allreduce_counters.argtypes = [vp, i32, vp, i32]
+    L.gasma_allreduce_counters_host.argtypes = [vp, i32, vp, i32]
+    L.gasma_nccl_version.argtypes = []
     L.gasma_metrics_dev.argtypes = [vp, vp, vp, i64] + [vp] * 8
     L.gasma_generate_ref_capacity.argtypes = [C.POINTER(GenConfig), i64]
     L.gasma_generate_ref_capacity.restype = i64
@@ -102,6 +106,17 @@ def lib():
         getattr(L, name).argtypes = [vp, vp, vp, vp, vp, i64, vp]
     _lib = L
     return L
+
+
+def allreduce_counters(aligners, counter_tensors):
+    """gasma_allreduce_counters: the in-place NCCL sum of per-device uint64 counter arrays (torch CUDA tensors, one per
+    aligner, each on its aligner's device)."""
+    n = len(aligners)
+    ctxs = (C.c_void_p * n)(*[a._ctx.value for a in aligners])
+    ptrs = (C.c_void_p * n)(*[t.data_ptr() for t in counter_tensors])
+    rc = lib().gasma_allreduce_counters(ctxs, n, ptrs, counter_tensors[0].numel())
+    if rc != 0:
+        raise GasmaError(rc, lib().gasma_last_error(aligners[0]._ctx).decode())
 
 
 def _np_ptr(a):

@@ -17,6 +17,7 @@ NVCC_FLAGS = [
     # libstdc++ is only available as a static archive in this image: keep its symbols private so they do
     # not interpose with the libstdc++.so.6 that python extensions load
     "-Xlinker", "-Bsymbolic", "-Xlinker", "--exclude-libs,ALL",
+    "-ldl",         # NCCL is bound at run time with dlopen (csrc/nccl_entry.inl)
     "--fmad=true",  # FP64 on the parity path uses explicit __dmul_rn/__dadd_rn, never contracted
 ]
 

@@ -45,6 +45,7 @@ struct gasma_ctx {
     // plane-0 streams travel in the reads / refs arguments.  Null = ASCII input.  Set and cleared by the packed entry points.
     const uint16_t* pk_r1 = nullptr;
     const uint16_t* pk_f1 = nullptr;
+    DevBuf nccl_words;          // scratch of gasma_allreduce_counters_host
     DevBuf d_r1, d_f1;          // device mirrors of the plane-1 streams (host-pointer packed call)
     int mask_variant = 0;       // gasma_set_mask_variant: 0 flip_short_hurdles(1), 1 flip_short_hurdles(2), 2 + flip_short_matches(1)
     int correction = 0;         // gasma_set_correction: widened band of the reference's -DCORRECTION build
@@ -356,7 +357,7 @@ void gasma_destroy(gasma_ctx* c) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     DevBuf* bufs[] = {&c->g_sums[0], &c->g_sums[1], &c->ops_rows, &c->ops_stage, &c->nops, &c->tile_sums, &c->tile_bases, &c->misc, &c->d_reads, &c->d_refs,
                       &c->d_read_off, &c->d_ref_off, &c->d_cost, &c->d_ops, &c->d_op_off, &c->d_p0, &c->d_p1, &c->gen_len, &c->d_bound, &c->nw_deferred, &c->nw_tb, &c->nw_pool_hi, &c->nw_pool_tb,
-                      &c->bm_hard, &c->bm_gops, &c->bm_goff, &c->bm_nops, &c->bm_noff, &c->bm_gcost, &c->bm_nwpen, &c->bm_counters, &c->bm_answers, &c->bm_nstage, &c->bm_nnops, &c->d_r1, &c->d_f1};
+                      &c->bm_hard, &c->bm_gops, &c->bm_goff, &c->bm_nops, &c->bm_noff, &c->bm_gcost, &c->bm_nwpen, &c->bm_counters, &c->bm_answers, &c->bm_nstage, &c->bm_nnops, &c->d_r1, &c->d_f1, &c->nccl_words};
     for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
     if (c->h_misc) cudaFreeHost(c->h_misc);
     for (auto& kind : c->ev) for (auto& pair : kind) for (auto& ev : pair) if (ev) cudaEventDestroy(ev);
@@ -997,3 +998,4 @@ int gasma_generate_dev(gasma_ctx* ctx, const gasma_gen_config* cfg, uint64_t fir
 #include "leap_entry.inl"
 #include "bench_entry.inl"
 #include "noalloc_entry.inl"
+#include "nccl_entry.inl"

@@ -14,6 +14,7 @@
 //     the unique optimum, the traceback tie-break (hence Coverage) is this repo's documented rule.
 #pragma once
 #include <algorithm>
+#include <array>
 #include <climits>
 #include <cstdint>
 #include <cstdio>
@@ -39,6 +40,7 @@ public:
                   int64_t batch_pairs = 1000000)
         : x(_x), o(_o), e(_e), k(_k), max_tests(max_test_num), use_SIMD(_use_SIMD), batch(batch_pairs) {
         if (devices.empty()) throw std::runtime_error("benchmark_gpu: no device given");
+        device_ids = devices;
         read.resize((size_t)max_tests);
         ref.resize((size_t)max_tests);
         answers.assign((size_t)max_tests, INT32_MIN);
@@ -135,7 +137,34 @@ public:
             for (std::thread& t : pool) t.join();
         }
         for (const std::string& err : errors) if (!err.empty()) throw std::runtime_error(err);
-        for (const tally& t : part) {   // the sum over GPUs: 5 integers per device
+        // The sum over GPUs (benchmark_utils.h:238,253-258): ONE NCCL all-reduce of the five counters over NVLink -- the
+        // path's only collective.  Where NCCL cannot be loaded the same five integers per device are added on the host.
+        bool distinct = true;   // NCCL wants one rank per device; contexts that share a device (tests) are summed on the host
+        for (size_t a = 0; a < G; ++a)
+            for (size_t b = a + 1; b < G; ++b) distinct = distinct && device_ids[a] != device_ids[b];
+        if (G > 1 && !distinct) counters_summed_by = "host (contexts share a device)";
+        if (G > 1 && distinct) {
+            std::vector<std::array<uint64_t, 5>> words(G);
+            std::vector<uint64_t*> ptrs(G);
+            for (size_t g = 0; g < G; ++g) {
+                words[g] = {part[g].total, part[g].nw, part[g].greedy, part[g].coverage, part[g].leap};
+                ptrs[g] = words[g].data();
+            }
+            const int rc = gasma_allreduce_counters_host(ctxs.data(), (int)G, ptrs.data(), 5);
+            if (rc == GASMA_OK) {
+                for (size_t g = 1; g < G; ++g)
+                    if (words[g] != words[0]) throw std::runtime_error("benchmark_gpu::run: ranks disagree after the all-reduce");
+                counters_summed_by = "NCCL " + std::to_string(gasma_nccl_version());
+                for (size_t g = 1; g < G; ++g) part[g].total = part[g].nw = part[g].greedy = part[g].coverage = part[g].leap = 0;
+                part[0].total = words[0][0]; part[0].nw = words[0][1]; part[0].greedy = words[0][2];
+                part[0].coverage = words[0][3]; part[0].leap = words[0][4];
+            } else if (rc == GASMA_E_UNSUPPORTED) {
+                counters_summed_by = "host (NCCL not installed)";
+            } else {
+                throw std::runtime_error(std::string("benchmark_gpu::run (NCCL): ") + gasma_last_error(ctxs[0]));
+            }
+        }
+        for (const tally& t : part) {
             total_tests += t.total; nw_correct += t.nw; greedy_correct += t.greedy; greedy_coverage += t.coverage;
             LEAP_correct += t.leap; greedy_ms += t.greedy_ms; nw_ms += t.nw_ms; LEAP_ms += t.leap_ms;
             have_LEAP = have_LEAP && t.have_leap;
@@ -159,6 +188,11 @@ public:
         printf("=> Greedy           | %.3f %%\n", (double)greedy_correct / t * 100);
         printf("[Coverage] (percentage of alignments covering all long consecutive matches)\n");
         printf("=> Greedy           | %.3f %%\n", (double)greedy_coverage / t * 100);
+        // everything above is the reference's report, line for line (:391-401); device timings in seconds read 0.000 at
+        // GPU speed, so the same figures follow in milliseconds
+        printf("[Device time, ms] Needleman-Wunsch %.3f | LEAP %.3f | Greedy %.3f", nw_ms, have_LEAP ? LEAP_ms : 0.0, greedy_ms);
+        if (ctxs.size() > 1) printf(" | %zu GPUs, counters summed by %s", ctxs.size(), counters_summed_by.c_str());
+        printf("\n");
     }
 
     // counters, for callers that sum them across GPUs / processes
@@ -215,6 +249,8 @@ private:
     static constexpr int kMaxLength = 128;   // MAX_LENGTH, GASMA/utils.h:23-25
     int x, o, e, k, max_tests;
     bool use_SIMD;
+    std::string counters_summed_by;   // several devices: "NCCL <version>" or "host (...)"
+    std::vector<int> device_ids;
     int64_t batch;
     std::vector<std::string> read, ref;
     std::vector<int> answers;

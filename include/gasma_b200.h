@@ -215,6 +215,22 @@ int gasma_metrics_dev(gasma_ctx* ctx, const char* d_reads, const uint32_t* d_rea
                       const int32_t* d_nw_penalty, const gasma_cigar_op* d_nw_ops, const uint32_t* d_nw_off,
                       const int32_t* d_answers, uint64_t* d_counters);
 
+/* -- the path's only collective -------------------------------------------------------------------- */
+/* Sums the counters of a run that was sharded over several GPUs of one box (benchmark_utils.h:238,253-258: total,
+ * nw_correct, greedy_correct, greedy_coverage): d_counters[i] = `count` uint64 words in the memory of ctxs[i]'s device
+ * (what gasma_benchmark_batch_dev / gasma_metrics_dev accumulate into); after the call EVERY array holds the sum over
+ * all contexts.  One ncclAllReduce(ncclSum, ncclUint64) per rank over NVLink / NVSwitch, enqueued on each context's
+ * stream behind the kernels that produced its counts; the call returns when all ranks are done.  One context per
+ * device; the communicators are built once per device list (ncclCommInitAll) and kept for the process.  NCCL is
+ * loaded at run time (libnccl.so.2, or $GASMA_NCCL_LIB): GASMA_E_UNSUPPORTED if it is not installed -- the sum of
+ * n_ctx x count integers on the host is then an exact substitute.  gasma_nccl_version() = NCCL's version code, 0 if
+ * it cannot be loaded. */
+int gasma_allreduce_counters(gasma_ctx* const* ctxs, int n_ctx, uint64_t* const* d_counters, int count);
+/* The same for counts held in HOST arrays (C++ callers without CUDA headers, host/benchmark_gpu.h): each array goes to
+ * its context's device, the device arrays are all-reduced, every host array comes back holding the total. */
+int gasma_allreduce_counters_host(gasma_ctx* const* ctxs, int n_ctx, uint64_t* const* counters, int count);
+int gasma_nccl_version(void);
+
 /* -- the whole benchmark body, batched ------------------------------------------------------------ */
 /* Replaces benchmark::run's loop over _run_benchmark (benchmark_utils.h:373-385, :231-259) for n pairs:
  * greedy (reset/run/get_cost/get_CIGAR), NW verifier (banded by the greedy penalty, exact), and the four

@@ -102,12 +102,15 @@ def test_benchmark_driver_sharded_over_devices(drivers, tmp_path):
 
     def report(*extra):
         txt = subprocess.run([exe, name, "--pairs", "20000", *extra], cwd=tmp_path, capture_output=True, text=True, check=True).stdout
-        return txt[txt.index("Total number of alignments"):txt.index("[Time]")] + txt[txt.index("[Accuracy]"):]
+        report.tail = txt[txt.index("[Device time, ms]"):]
+        return txt[txt.index("Total number of alignments"):txt.index("[Time]")] + txt[txt.index("[Accuracy]"):txt.index("[Device time, ms]")]
 
     one = report()
     assert report("--batch", "3000", "--devices", "0,0,0") == one
+    assert "counters summed by host (contexts share a device)" in report.tail
     if torch.cuda.device_count() >= 2:
         assert report("--batch", "3000", "--gpus", "2") == one
+        assert "2 GPUs, counters summed by NCCL 2" in report.tail      # the path's only collective, from C++
 
 
 def _mapper_inputs(tmp_path, n_reads=400, seed=11):
