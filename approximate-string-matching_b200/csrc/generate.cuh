@@ -29,9 +29,17 @@ struct Rng {
     }
     GASMA_HD uint32_t u32() { return (uint32_t)(next() >> 32); }
     GASMA_HD uint32_t below(uint32_t n) { return (uint32_t)(((uint64_t)u32() * n) >> 32); }
+    static GASMA_HD uint64_t mix(uint64_t z) {
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+        z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+        return z ^ (z >> 31);
+    }
+    // The stream of a pair starts at a HASHED point of the 2^64 cycle.  (Round 1 started pair p at seed*A + p*G + C with
+    // G the generator's own increment: pair p+1's stream was pair p's stream shifted by one draw, so neighbouring
+    // reads were shifted copies of each other -- not the independent simulated reads the workload is meant to be; it
+    // showed as +-9 % kernel time between batches of identical total work.)
     GASMA_HD void seed(uint64_t seed_, uint64_t pair) {
-        s = seed_ * 0xD1B54A32D192ED03ull + pair * 0x9E3779B97F4A7C15ull + 0x2545F4914F6CDD1Dull;
-        (void)next();
+        s = mix(mix(seed_ + 0x2545F4914F6CDD1Dull) ^ (pair * 0xD1B54A32D192ED03ull + 0x9E3779B97F4A7C15ull));
     }
 };
 

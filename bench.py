@@ -374,12 +374,15 @@ def greedy_leg(env, *, workload, length, error, profile, k, pairs, steps, warmup
         step(i)
     ev1.record(env.stream)
     env.barrier()
-    ms_total = env.max_over_ranks(ev0.elapsed_time(ev1))
+    ms_rank = ev0.elapsed_time(ev1)
+    ms_total = env.max_over_ranks(ms_rank)
     al.synchronize()
     env.load(False)
     launches = al.launch_count - launches0
     kernel_ms, kernel_launches = al.kernel_time_ms(0)
     k_ms = kernel_ms / max(kernel_launches, 1)
+    if os.environ.get("GASMA_BENCH_RANKS"):   # per-rank view of the leg on stderr (scaling diagnostics)
+        sys.stderr.write("[rank %d] %s: step %.4f ms, greedy kernel %.4f ms\n" % (env.rank, workload[:40], ms_rank / steps, k_ms))
 
     last = batches[(steps - 1) % len(batches)]
     ooff_last = int(d_ooff[-1].item()) & 0xFFFFFFFF

@@ -635,9 +635,15 @@ static uint64_t rng_next(rng_t* r) {
 }
 static uint32_t rng_u32(rng_t* r) { return (uint32_t)(rng_next(r) >> 32); }
 static uint32_t rng_below(rng_t* r, uint32_t n) { return (uint32_t)(((uint64_t)rng_u32(r) * n) >> 32); }
+static uint64_t rng_mix(uint64_t z) {
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+/* a pair's stream starts at a hashed point of the cycle, so that the streams of neighbouring pairs do not overlap
+ * (twin of Rng::seed in csrc/generate.cuh) */
 static void rng_seed(rng_t* r, uint64_t seed, uint64_t pair) {
-    r->s = seed * 0xD1B54A32D192ED03ull + pair * 0x9E3779B97F4A7C15ull + 0x2545F4914F6CDD1Dull;
-    (void)rng_next(r);
+    r->s = rng_mix(rng_mix(seed + 0x2545F4914F6CDD1Dull) ^ (pair * 0xD1B54A32D192ED03ull + 0x9E3779B97F4A7C15ull));
 }
 
 int go_gen_ref_capacity(const go_gen_config* c) {
