@@ -695,7 +695,7 @@ def run_b200(a):
                                           "ratio_resident": c0["value"] / c0["cpu_baseline"]["value"]}
     if world > 1:
         dist.destroy_process_group()
-    print(json.dumps(line))
+    emit_line(line)
     if not a.no_parity and not line["parity"]["ok"]:
         raise SystemExit("PARITY FAILURE: the timed outputs differ from the oracle (see the parity block)")
 
@@ -731,11 +731,28 @@ def run_reference(a):
             "dtype": "u64/SSE bit-vectors + int32 penalties", "data": "synthetic",
             "config": config_dict(a, ml), "cpu_baseline": base,
             "e2e": {"value": v, "unit": "alignments/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line))
+    emit_line(line)
+
+
+_REAL_STDOUT = None
+
+
+def emit_line(line):
+    """The ONE JSON line goes to the process's real stdout; everything libraries print on fd 1 while the run lasts
+    (NCCL's version banner under torchrun) was sent to stderr by __main__."""
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
 
 
 if __name__ == "__main__":
     args = parse()
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:
