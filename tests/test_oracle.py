@@ -305,3 +305,19 @@ def test_oracle_mask_variants_vs_reference_fresh(ol):
         assert r["text"] == f["text"]
         base = ol.oracle_greedy(b, ol.make_params(4, 1, 2, 1), threads=4)
         assert int((base["cost"] != r["cost"]).sum()) > 100      # the variants really are different aligners
+
+
+# ---- the synthetic workload generator (checker side; the device generator is compared with it in the GPU tests) ----
+def test_generator_streams_are_independent(ol):
+    """Neighbouring pairs must not replay each other's random draws (the first seeding did: pair p+1 was pair p one
+    draw later, so its read was pair p's read shifted by one character)."""
+    cfg = ol.gen_config(0x47415341 + 1, 150, 0.10)
+    b = ol.generate(cfg, 1_000_000, 64)
+    rows = [bytes(b.pair(i)[0]) for i in range(64)]
+    assert all(len(r) == 150 for r in rows)
+    for a, b in zip(rows, rows[1:]):
+        for shift in range(0, 9):
+            same = sum(1 for x, y in zip(a[shift:], b) if x == y) / (150 - shift)
+            same2 = sum(1 for x, y in zip(b[shift:], a) if x == y) / (150 - shift)
+            assert same < 0.5 and same2 < 0.5          # independent uniform strings agree on a quarter of the columns
+    assert len(set(rows)) == 64
