@@ -48,6 +48,7 @@ EXPORTS = [
     "gasma_greedy_batch_dev_noalloc", "gasma_set_mask_variant",
     "gasma_pack2bit_stream", "gasma_pack2bit_stream_dev", "gasma_greedy_batch_packed", "gasma_greedy_batch_packed_dev",
     "gasma_allreduce_counters", "gasma_allreduce_counters_host", "gasma_nccl_version",
+    "gasma_greedy_submit", "gasma_greedy_submit_packed", "gasma_greedy_wait",
 ]
 
 _lib = None
@@ -91,6 +92,9 @@ def lib():
         getattr(L, name).argtypes = [vp, vp, i64, vp, vp]
     for name in ("gasma_greedy_batch_packed", "gasma_greedy_batch_packed_dev"):
         getattr(L, name).argtypes = [vp, vp, vp, vp, vp, vp, vp, i64, vp, vp, i64, vp]
+    L.gasma_greedy_submit.argtypes = [vp, vp, vp, vp, vp, i64, vp, vp, i64, vp, C.POINTER(C.c_int)]
+    L.gasma_greedy_submit_packed.argtypes = [vp, vp, vp, vp, vp, vp, vp, i64, vp, vp, i64, vp, C.POINTER(C.c_int)]
+    L.gasma_greedy_wait.argtypes = [vp, i32]
     L.gasma_allreduce_counters.argtypes = [vp, i32, vp, i32]
     L.gasma_allreduce_counters_host.argtypes = [vp, i32, vp, i32]
     L.gasma_nccl_version.argtypes = []
@@ -158,6 +162,7 @@ class Aligner:
             raise GasmaError(rc, self._L.gasma_last_error(None).decode())
         self.W = max_length // 64
         self.device = device
+        self._in_flight = {}   # ticket -> arrays of a submitted call (kept alive until greedy_wait)
 
     def close(self):
         ctx = getattr(self, "_ctx", None)
@@ -264,6 +269,46 @@ class Aligner:
         self._check(self._L.gasma_greedy_batch_packed_dev(self._ctx, _dev_ptr(d_r0), _dev_ptr(d_r1), _dev_ptr(d_read_off), _dev_ptr(d_f0),
                                                           _dev_ptr(d_f1), _dev_ptr(d_ref_off), n, _dev_ptr(d_cost), _dev_ptr(d_ops),
                                                           0 if d_ops is None else d_ops.numel(), _dev_ptr(d_op_off)))
+
+    # -- asynchronous pair: two host-pointer calls in flight per context (include/gasma_b200.h) -------------------------
+    def _async_out(self, n, want_ops, ops_cap, out):
+        if out is None:
+            out = {"cost": np.empty(n, np.int32)}
+            if want_ops:
+                out["ops"] = np.empty(ops_cap if ops_cap is not None else max(16, 24 * n), np.uint16)
+                out["op_off"] = np.empty(n + 1, np.uint32)
+        return out, (out.get("ops") if want_ops else None), (out.get("op_off") if want_ops else None)
+
+    def greedy_submit(self, reads, read_off, refs, ref_off, want_ops=True, ops_cap=None, out=None):
+        """Starts gasma_greedy_batch on these arrays and returns a ticket; the arrays (inputs and `out`) must not be
+        touched until greedy_wait(ticket) has returned."""
+        n = len(read_off) - 1
+        out, ops, op_off = self._async_out(n, want_ops, ops_cap, out)
+        t = C.c_int(-1)
+        self._check(self._L.gasma_greedy_submit(self._ctx, _np_ptr(reads), _np_ptr(read_off), _np_ptr(refs), _np_ptr(ref_off), n,
+                                                _np_ptr(out["cost"]), _np_ptr(ops), 0 if ops is None else len(ops), _np_ptr(op_off),
+                                                C.byref(t)))
+        self._in_flight[t.value] = (out, n, want_ops, (reads, read_off, refs, ref_off))
+        return t.value
+
+    def greedy_submit_packed(self, r0, r1, read_off, f0, f1, ref_off, want_ops=True, ops_cap=None, out=None):
+        n = len(read_off) - 1
+        out, ops, op_off = self._async_out(n, want_ops, ops_cap, out)
+        t = C.c_int(-1)
+        self._check(self._L.gasma_greedy_submit_packed(self._ctx, _np_ptr(r0), _np_ptr(r1), _np_ptr(read_off), _np_ptr(f0), _np_ptr(f1),
+                                                       _np_ptr(ref_off), n, _np_ptr(out["cost"]), _np_ptr(ops),
+                                                       0 if ops is None else len(ops), _np_ptr(op_off), C.byref(t)))
+        self._in_flight[t.value] = (out, n, want_ops, (r0, r1, read_off, f0, f1, ref_off))
+        return t.value
+
+    def greedy_wait(self, ticket):
+        """Status of a submitted call (raises on error); returns its `out` dict."""
+        rc = self._L.gasma_greedy_wait(self._ctx, ticket)
+        out, n, want_ops, _keep = self._in_flight.pop(ticket, (None, 0, False, None))
+        self._check(rc)
+        if out is not None and want_ops:
+            out["n_ops"] = int(out["op_off"][n])
+        return out
 
     def leap_batch(self, reads, read_off, refs, ref_off):
         """LEAP comparator penalties (benchmark::_run_LEAP); INT32_MIN where no lane converges."""

@@ -18,6 +18,7 @@ NVCC_FLAGS = [
     # not interpose with the libstdc++.so.6 that python extensions load
     "-Xlinker", "-Bsymbolic", "-Xlinker", "--exclude-libs,ALL",
     "-ldl",         # NCCL is bound at run time with dlopen (csrc/nccl_entry.inl)
+    "-lpthread",    # host threads of the asynchronous call pair (csrc/async_entry.inl)
     "--fmad=true",  # FP64 on the parity path uses explicit __dmul_rn/__dadd_rn, never contracted
 ]
 

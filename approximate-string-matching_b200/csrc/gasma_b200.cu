@@ -31,7 +31,10 @@ struct DevBuf {
 
 }  // namespace
 
+struct gasma_async_state;   // async_entry.inl: the two in-flight slots of gasma_greedy_submit / gasma_greedy_wait
+
 struct gasma_ctx {
+    gasma_async_state* async = nullptr;
     gasma_params params;
     KParams kp;
     int W = 2;
@@ -86,6 +89,8 @@ struct gasma_ctx {
 };
 
 namespace {
+
+void async_destroy(gasma_ctx* ctx);   // async_entry.inl
 
 int fail(gasma_ctx* c, int code, const char* fmt, ...) {
     char buf[512];
@@ -353,6 +358,7 @@ int gasma_create(const gasma_params* params, int device, gasma_ctx** out) {
 
 void gasma_destroy(gasma_ctx* c) {
     if (!c) return;
+    async_destroy(c);
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     DevBuf* bufs[] = {&c->g_sums[0], &c->g_sums[1], &c->ops_rows, &c->ops_stage, &c->nops, &c->tile_sums, &c->tile_bases, &c->misc, &c->d_reads, &c->d_refs,
@@ -999,3 +1005,4 @@ int gasma_generate_dev(gasma_ctx* ctx, const gasma_gen_config* cfg, uint64_t fir
 #include "bench_entry.inl"
 #include "noalloc_entry.inl"
 #include "nccl_entry.inl"
+#include "async_entry.inl"

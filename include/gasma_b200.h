@@ -157,6 +157,28 @@ int gasma_greedy_batch_packed_dev(gasma_ctx* ctx,
                                   const uint16_t* d_ref_plane0, const uint16_t* d_ref_plane1, const uint32_t* d_ref_off, int64_t n_pairs,
                                   int32_t* d_cost, gasma_cigar_op* d_ops, int64_t ops_cap, uint32_t* d_op_off);
 
+/* -- the host-pointer greedy call as an asynchronous pair ---------------------------------------- */
+/* The reference's loop is synchronous (benchmark_utils.h:238-252: reset, run, get_cost per pair); a caller that
+ * streams batches through a GPU wants the link busy all the time, and a synchronous batch call ends with a tail
+ * (last kernels, results back, one host round trip for the CIGAR fetch) during which nothing is copied in.
+ * gasma_greedy_submit / gasma_greedy_submit_packed start gasma_greedy_batch / gasma_greedy_batch_packed on the
+ * given arguments and return at once with a ticket; gasma_greedy_wait(ticket) returns that call's status when it
+ * has ended (results are in the caller's buffers then, bit for bit those of the synchronous call).  Up to TWO calls
+ * may be in flight per context (each has its own device mirrors and streams: the context's device memory for
+ * mirrors doubles), a third submit fails with GASMA_E_UNSUPPORTED until one has been waited for.  All buffers of a
+ * submitted call, inputs included, belong to the library until its wait returns; pinned host memory keeps the
+ * copies asynchronous.  The context's band / widened-band / mask-variant settings at submit time apply.
+ * gasma_destroy waits for calls still in flight.  Synchronous calls on the same context may be mixed in freely. */
+int gasma_greedy_submit(gasma_ctx* ctx,
+                        const char* reads, const uint32_t* read_off,
+                        const char* refs, const uint32_t* ref_off, int64_t n_pairs,
+                        int32_t* cost, gasma_cigar_op* ops, int64_t ops_cap, uint32_t* op_off, int* ticket);
+int gasma_greedy_submit_packed(gasma_ctx* ctx,
+                               const uint16_t* read_plane0, const uint16_t* read_plane1, const uint32_t* read_off,
+                               const uint16_t* ref_plane0, const uint16_t* ref_plane1, const uint32_t* ref_off, int64_t n_pairs,
+                               int32_t* cost, gasma_cigar_op* ops, int64_t ops_cap, uint32_t* op_off, int* ticket);
+int gasma_greedy_wait(gasma_ctx* ctx, int ticket);
+
 /* -- the greedy step without any allocation ------------------------------------------------------- */
 /* No counterpart in the reference; added for callers that cannot call
  * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same inputs, outputs

@@ -355,3 +355,67 @@ def test_gpu_packed_input_equals_ascii_input(pkg, ol, W):
         r = ol.oracle_greedy(b, ol.make_params(4, 1, 1, 1, W, 1), threads=8)
         assert np.array_equal(p["cost"], r["cost"]) and np.array_equal(p["ops"][:p["n_ops"]], r["ops"])
     al.close()
+
+
+def test_gpu_async_submit_wait_pair(pkg, ol):
+    """gasma_greedy_submit / gasma_greedy_submit_packed / gasma_greedy_wait: two calls in flight give the synchronous
+    calls' results bit for bit (small one-copy and large pipelined batches, ASCII and packed, different settings per
+    round), a third submit is refused, unknown tickets are refused, errors of a submitted call arrive at its wait."""
+    rng = np.random.default_rng(9100)
+    al = pkg.Aligner(k=3, max_length=192)
+    batches = [ol.random_batch(rng, n, 0, 192, 0.25, 0.3, 50) for n in (70000, 3000, 90000, 500)]
+    sync = [al.greedy_batch(b.reads, b.read_off, b.refs, b.ref_off) for b in batches]
+    ref0 = ol.oracle_greedy(batches[0], ol.make_params(3, 1, 1, 1, 3, 1), threads=8)
+    assert np.array_equal(sync[0]["cost"], ref0["cost"]) and np.array_equal(sync[0]["ops"][:sync[0]["n_ops"]], ref0["ops"])
+
+    def same(a, b):
+        return (np.array_equal(a["cost"], b["cost"]) and np.array_equal(a["op_off"], b["op_off"])
+                and np.array_equal(a["ops"][:a["n_ops"]], b["ops"][:b["n_ops"]]))
+
+    # a rolling window of two calls over the four batches, three times round
+    order = [0, 1, 2, 3] * 3
+    pending = []
+    for i in order:
+        b = batches[i]
+        if len(pending) == 2:
+            t, j = pending.pop(0)
+            assert same(al.greedy_wait(t), sync[j])
+        pending.append((al.greedy_submit(b.reads, b.read_off, b.refs, b.ref_off), i))
+    # both slots busy now: a third submit is refused, and nothing about the two in flight changes
+    assert len(pending) == 2
+    with pytest.raises(pkg.GasmaError) as ei:
+        al.greedy_submit(batches[3].reads, batches[3].read_off, batches[3].refs, batches[3].ref_off)
+    assert ei.value.code == -6 and "in flight" in str(ei.value)
+    # a synchronous call on the parent may be mixed in while two are in flight
+    assert same(al.greedy_batch(batches[1].reads, batches[1].read_off, batches[1].refs, batches[1].ref_off), sync[1])
+    for t, j in pending:
+        assert same(al.greedy_wait(t), sync[j])
+    with pytest.raises(pkg.GasmaError) as ei:
+        al.greedy_wait(12345)
+    assert ei.value.code == -1
+
+    # packed input, and the parent's settings at submit time apply (band 5, mask variant 1)
+    al.set_band(5)
+    al.set_mask_variant(1)
+    b = batches[2]
+    want = al.greedy_batch(b.reads, b.read_off, b.refs, b.ref_off)
+    assert not np.array_equal(want["cost"], sync[2]["cost"])
+    r0, r1 = al.pack2bit_stream(b.reads)
+    f0, f1 = al.pack2bit_stream(b.refs)
+    t1 = al.greedy_submit_packed(r0, r1, b.read_off, f0, f1, b.ref_off)
+    t2 = al.greedy_submit(b.reads, b.read_off, b.refs, b.ref_off)
+    assert same(al.greedy_wait(t2), want) and same(al.greedy_wait(t1), want)
+    al.set_band(3)
+    al.set_mask_variant(0)
+
+    # an error inside a submitted call (a string longer than max_length) comes back from its wait, and the slot is free again
+    bad = ol.Batch.from_pairs([(b"ACGT" * 60, b"ACGT" * 60)])       # 240 > 192
+    t = al.greedy_submit(bad.reads, bad.read_off, bad.refs, bad.ref_off)
+    with pytest.raises(pkg.GasmaError) as ei:
+        al.greedy_wait(t)
+    assert ei.value.code == -2
+    t = al.greedy_submit(batches[1].reads, batches[1].read_off, batches[1].refs, batches[1].ref_off)
+    assert same(al.greedy_wait(t), sync[1])
+    # destroying a context with a call in flight waits for it
+    t = al.greedy_submit(batches[0].reads, batches[0].read_off, batches[0].refs, batches[0].ref_off)
+    al.close()
