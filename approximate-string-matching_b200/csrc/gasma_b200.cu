@@ -243,14 +243,14 @@ int greedy_tile_threads(const gasma_ctx* c) {   // 0 = configuration does not fi
     }
 }
 
-// one alignment per warp (max_length 512 / 1024)
-template <int W>
-int launch_greedy_warp(gasma_ctx* ctx, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, const uint32_t* foff,
-                       int64_t n, int32_t* cost, uint16_t* rows, uint16_t* stage, int stride, uint32_t* nops, uint32_t* pair_counter,
-                       uint32_t* status, unsigned long long* steps, uint32_t* tsums) {
+// one alignment per warp (max_length 512 / 1024); ITER = lane slots per thread
+template <int W, int ITER>
+int launch_greedy_warp_i(gasma_ctx* ctx, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, const uint32_t* foff,
+                         int64_t n, int32_t* cost, uint16_t* rows, uint16_t* stage, int stride, uint32_t* nops, uint32_t* pair_counter,
+                         uint32_t* status, unsigned long long* steps, uint32_t* tsums) {
     constexpr int WARPS = 4;
     const size_t smem = WARPS * ((WarpLayout<W>::bytes_per_warp(ctx->kp.nl) + 15) / 16 * 16);
-    auto kern = greedy_warp_kernel<W, WARPS>;
+    auto kern = greedy_warp_kernel<W, WARPS, ITER>;
     CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 32 * WARPS, smem));
@@ -263,6 +263,17 @@ int launch_greedy_warp(gasma_ctx* ctx, const uint8_t* reads, const uint32_t* rof
     CU(cudaGetLastError());
     ctx->launches++;
     return GASMA_OK;
+}
+
+template <int W>
+int launch_greedy_warp(gasma_ctx* ctx, const uint8_t* reads, const uint32_t* roff, const uint8_t* refs, const uint32_t* foff,
+                       int64_t n, int32_t* cost, uint16_t* rows, uint16_t* stage, int stride, uint32_t* nops, uint32_t* pair_counter,
+                       uint32_t* status, unsigned long long* steps, uint32_t* tsums) {
+    const int nl = ctx->kp.nl;   // lane slots per alignment: 2k+1 (+ max_delta with the widened band), at most 2 * MAX_K + 1
+    if (nl <= 32) return launch_greedy_warp_i<W, 1>(ctx, reads, roff, refs, foff, n, cost, rows, stage, stride, nops, pair_counter, status, steps, tsums);
+    if (nl <= 64) return launch_greedy_warp_i<W, 2>(ctx, reads, roff, refs, foff, n, cost, rows, stage, stride, nops, pair_counter, status, steps, tsums);
+    if (nl <= 128) return launch_greedy_warp_i<W, 4>(ctx, reads, roff, refs, foff, n, cost, rows, stage, stride, nops, pair_counter, status, steps, tsums);
+    return fail(ctx, GASMA_E_BAND, "%d lane slots per alignment exceed the warp kernel's 128", nl);
 }
 
 int check_status(gasma_ctx* ctx, uint32_t st) {

@@ -16,7 +16,10 @@ namespace gasma {
 template <int W>
 struct WarpLayout {
     static constexpr int NW = 2 * W;              // 32-bit words per lane
-    static constexpr int PITCH = NW + 1;          // odd pitch: threads reading the same word of 32 lanes hit 32 banks
+    // a lane row = one zero word, NW mask words, three zero words: the highway search reads word w-1 ... w+3 of its
+    // position without bounds tests.  Odd pitch: threads reading the same word of 32 lanes hit 32 banks
+    static constexpr int PAD_LO = 1, PAD_HI = 3;
+    static constexpr int PITCH = (NW + PAD_LO + PAD_HI) | 1;
     static constexpr int PLANE = NW + 2;          // plane words + zero padding for shifted reads
     static constexpr int STREAM = ((4 * W + 2) + 2 * 2 + 7) / 8 * 8;   // uint16 chunks of one string (+ window slack)
     __host__ __device__ static constexpr size_t bytes_per_warp(int nl) {   // nl = lane slots per alignment (KParams::nl)
@@ -24,29 +27,31 @@ struct WarpLayout {
     }
 };
 
-// candidate of the arg-max: key (heuristic, leap), lane, cached highway state
-struct WarpCand {
-    double h;       // significance heuristic, or the integer destination heuristic converted exactly
-    int leap, l;
-    uint64_t st;
-    bool valid;
-};
-// the reference keeps the FIRST lane (ascending) among equal (heuristic, leap) keys: strict '>' while scanning upwards
-__device__ __forceinline__ bool cand_better(const WarpCand& a, const WarpCand& b) {
-    if (a.valid != b.valid) return a.valid;
-    if (!a.valid) return false;
-    if (a.h != b.h) return a.h > b.h;
-    if (a.leap != b.leap) return a.leap > b.leap;
-    return a.l < b.l;
+// The closest highway at/after column sc (greedy.cuh:scan_highway, same results) on a zero-padded row: `row` points at
+// mask word 0, row[-1] and row[NW .. NW+2] are zero.  The shipped mask variant only (flip_short_hurdles(1)).
+template <int W>
+__device__ __forceinline__ void scan_highway_padded(const uint32_t* row, int sc, int de, int& sp, int& len) {
+    constexpr int NW = 2 * W, BITS = 64 * W;
+    const int w = sc >> 5, b = sc & 31;
+    if (w >= NW) { sp = imax(sc, BITS); len = BITS; return; }
+    const uint32_t om = row[w - 1], o0 = row[w], o1 = row[w + 1], o2 = row[w + 2], o3 = row[w + 3];
+    const uint32_t f0 = o0 & (funnel_l1(om, o0) | funnel_r1(o0, o1)), f1 = o1 & (funnel_l1(o0, o1) | funnel_r1(o1, o2)),
+                   f2 = o2 & (funnel_l1(o1, o2) | funnel_r1(o2, o3));
+    const uint32_t lo = __funnelshift_r(f0, f1, b), hi = __funnelshift_r(f1, f2, b);   // flipped lane bits [sc, sc+64)
+    const uint32_t zlo = ~lo, zhi = ~hi;
+    if ((zlo | zhi) == 0u) { scan_highway_loop<W, 0>(row, 1, sc, sp, len); return; }   // 64 hurdles in a row
+    const int fz = zlo ? ctz32(zlo) : 32 + ctz32(zhi);
+    const uint32_t tlo = fz < 32 ? (lo & (0xFFFFFFFFu << fz)) : 0u;
+    const uint32_t thi = fz < 32 ? hi : (hi & (0xFFFFFFFFu << (fz - 32)));
+    sp = sc + fz;
+    if ((tlo | thi) != 0u) len = (tlo ? ctz32(tlo) : 32 + ctz32(thi)) - fz;
+    else len = (sc + 64 >= BITS || sc + 64 > de) ? BITS : scan_highway_tail<W, 0>(row, 1, sc + 64, de, sp);
 }
-__device__ __forceinline__ WarpCand cand_shfl_xor(const WarpCand& c, int d) {
-    WarpCand r;
-    r.h = __shfl_xor_sync(0xffffffffu, c.h, d);
-    r.leap = __shfl_xor_sync(0xffffffffu, c.leap, d);
-    r.l = __shfl_xor_sync(0xffffffffu, c.l, d);
-    r.st = __shfl_xor_sync(0xffffffffu, c.st, d);
-    r.valid = __shfl_xor_sync(0xffffffffu, (int)c.valid, d) != 0;
-    return r;
+
+// order-preserving unsigned key of a double (sign bit flipped, negative values complemented; -0 folded into +0)
+__device__ __forceinline__ unsigned long long order_key(double h) {
+    const long long bits = __double_as_longlong(dadd(h, 0.0));
+    return (unsigned long long)bits ^ ((unsigned long long)(bits >> 63) | 0x8000000000000000ull);
 }
 
 // 32 bits of a uint16-chunk stream starting at bit `bit`, for plane word w of a string of `len` characters
@@ -57,7 +62,11 @@ __device__ __forceinline__ uint32_t stream_word(const uint32_t* stream32, int bi
     return keep >= 32 ? v : (keep <= 0 ? 0u : (v & (0xFFFFFFFFu >> (32 - keep))));
 }
 
-template <int W, int WARPS>
+
+// ITER = lane slots per thread (ceil(lane slots / 32)): the per-slot loops are unrolled and every thread keeps the
+// highway cache of its own lanes (and this step's switch cost) in registers between _update_highway_list and
+// _choose_best_highway; a copy in shared memory is what the warp reads the winner's cache from.
+template <int W, int WARPS, int ITER>
 __global__ void __launch_bounds__(32 * WARPS)
 greedy_warp_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __restrict__ read_off,
                    const uint8_t* __restrict__ refs, const uint32_t* __restrict__ ref_off, long long n,
@@ -72,11 +81,13 @@ greedy_warp_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t*
     const int k = P.k, nl_cap = P.nl, x = P.x, o = P.o, e = P.e;
     const bool GLOBAL = P.global != 0;
     unsigned char* mine = smem_raw + (size_t)warp * ((L::bytes_per_warp(nl_cap) + 15) / 16 * 16);
-    uint64_t* s_state = reinterpret_cast<uint64_t*>(mine);
-    uint32_t* s_lanes = reinterpret_cast<uint32_t*>(s_state + nl_cap);
+    uint64_t* s_state = reinterpret_cast<uint64_t*>(mine);       // [nl_cap]: every lane's cached highway, for the warp to read
+    uint32_t* s_lanes = reinterpret_cast<uint32_t*>(s_state + nl_cap);   // [nl_cap][PITCH], mask word 0 of a row at PAD_LO
     uint32_t* s_plane = s_lanes + (size_t)nl_cap * PITCH;        // [4][PLANE]: A0, A1, B0, B1
     uint16_t* s_stream = reinterpret_cast<uint16_t*>(s_plane + 4 * L::PLANE);   // [4][STREAM]
     for (int i = lane; i < 4 * L::STREAM; i += 32) s_stream[i] = 0;
+    for (int i = lane; i < nl_cap * PITCH; i += 32) s_lanes[i] = 0u;   // the rows' zero padding, written once
+    const uint32_t* my_row0 = s_lanes + (size_t)lane * PITCH + L::PAD_LO;   // mask word 0 of this thread's first lane
     const uint32_t rtotal = read_off[n], ftotal = ref_off[n];
     uint32_t st_bits = 0;
     unsigned long long steps_total = 0;
@@ -118,13 +129,21 @@ greedy_warp_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t*
         int lb = -k, ub = k;
         if (P.correction) { if (m <= nn) ub = nn - m + k; else lb = nn - m - k; }
         const int nl = ub - lb + 1;
+        const int l0 = lane + lb;                  // this thread's lanes: l0, l0 + 32, ...
+        uint64_t stv[ITER];                        // their cached highways
+        int sw_[ITER];                             // their switch cost in the current step
+#pragma unroll
+        for (int i = 0; i < ITER; ++i) {
+            stv[i] = st_pack(-1, 0, BITS, BITS);
+            sw_[i] = 0;
+        }
         for (int li = lane; li < nl; li += 32) {
             const int l = li + lb, a = iabs(l), aw = a >> 5, ab = a & 31;
             const uint32_t* X0 = s_plane + (l < 0 ? 0 : 2) * L::PLANE;   // the shifted string: read for l<0, ref for l>=0
             const uint32_t* X1 = X0 + L::PLANE;
             const uint32_t* Y0 = s_plane + (l < 0 ? 2 : 0) * L::PLANE;
             const uint32_t* Y1 = Y0 + L::PLANE;
-            uint32_t* row = s_lanes + (size_t)li * PITCH;
+            uint32_t* row = s_lanes + (size_t)li * PITCH + L::PAD_LO;
             // |l| <= MAX_K = 50, so aw <= 1 and the last word read is PLANE-1 (the planes carry two zero words on top);
             // each plane word is loaded once and slides from "upper" to "lower" half of the funnel shift
             uint32_t x0a = X0[aw], x1a = X1[aw];
@@ -133,7 +152,6 @@ greedy_warp_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t*
                 row[w] = (__funnelshift_r(x0a, x0b, ab) ^ Y0[w]) | (__funnelshift_r(x1a, x1b, ab) ^ Y1[w]);
                 x0a = x0b; x1a = x1b;
             }
-            s_state[li] = st_pack(-1, 0, BITS, BITS);
         }
         __syncwarp();
 
@@ -156,88 +174,95 @@ greedy_warp_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t*
         for (;;) {
             if (++steps > 4 * BITS + 16) { st_bits |= kStatusSteps; break; }
             const bool leap_cost = GLOBAL || !first;
-            // _update_highway_list (:291-352): every thread refreshes its own lanes and keeps its best candidates
+            // _update_highway_list (:291-352): every thread refreshes its own lanes and keeps its best candidate as an
+            // integer key: hk = the FP64 significance heuristic mapped to an unsigned of the same order, k2 = (leap, -lane).
+            // The reference keeps the FIRST lane (ascending) among equal (heuristic, leap): 63 - lane in the low bits.
+            // leap = -(switch costs) lies in (-2^22, 0] for penalties <= 1000, 63 - lane in [13, 113].
             bool reach_local = false;
-            WarpCand cs{0.0, 0, 0, 0ull, false}, cr{0.0, 0, 0, 0ull, false};
-            for (int li = lane; li < nl; li += 32) {
-                const int l = li + lb;
-                const uint32_t* row = s_lanes + (size_t)li * PITCH;
-                const int sc = cc + sfc(cl, l);
-                const int de = lane_destination(m, nn, l);
-                uint64_t stv = s_state[li];
-                int sp = st_sp(stv), len = st_len(stv), nsw = st_nsw(stv);
-                if (sp < sc) {
-                    nsw = iabs(l - cl);
-                    scan_highway<W>(row, 1, sc, de, sp, len);
-                    if (sp + len > de) { len = imax(0, de - sp); reach_local = true; }
+            unsigned long long hk = 0ull;   // 0 = no candidate
+            uint32_t k2 = 0u;
+#pragma unroll
+            for (int i = 0; i < ITER; ++i) {
+                if (lane + 32 * i < nl) {
+                    const int l = l0 + 32 * i;
+                    const uint32_t* row = my_row0 + (size_t)(32 * i) * PITCH;
+                    const int sc = cc + sfc(cl, l);
+                    int sp = st_sp(stv[i]), len = st_len(stv[i]), nsw = st_nsw(stv[i]);
+                    if (sp < sc) {
+                        const int de = lane_destination(m, nn, l);
+                        nsw = iabs(l - cl);
+                        scan_highway_padded<W>(row, sc, de, sp, len);
+                        if (sp + len > de) { len = imax(0, de - sp); reach_local = true; }
+                    }
+                    const int sw = leap_cost ? slp(cl, l, o, e) : 0;
+                    const int nh = pcb<W>(row, 1, sc, sp + len);
+                    sw_[i] = sw;
+                    stv[i] = st_pack(sp, len, nsw, nh);
+                    s_state[lane + 32 * i] = stv[i];
+                    const double h = dadd(dadd(dmul(P.ms, (double)len), dmul(P.mms, (double)nh)), dmul(P.ids, (double)nsw));
+                    const unsigned long long hki = order_key(h);
+                    const uint32_t k2i = ((uint32_t)((1 << 22) - sw) << 8) | (uint32_t)(63 - l);
+                    if (hki > hk || (hki == hk && k2i > k2)) { hk = hki; k2 = k2i; }
                 }
-                const int sw = leap_cost ? slp(cl, l, o, e) : 0;
-                const int nh = pcb<W>(row, 1, sc, sp + len);
-                stv = st_pack(sp, len, nsw, nh);
-                s_state[li] = stv;
-                const double h = dadd(dadd(dmul(P.ms, (double)len), dmul(P.mms, (double)nh)), dmul(P.ids, (double)nsw));
-                WarpCand c{h, -sw, l, stv, true};
-                if (cand_better(c, cs)) cs = c;
-                const int fsw = GLOBAL ? slp(l, dl, o, e) : 0;
-                WarpCand d{(double)(-sw - x * nh - fsw - x * (de - sp - len)), -sw - fsw, l, stv, true};
-                if (cand_better(d, cr)) cr = d;
             }
-            const bool reach = __ballot_sync(0xffffffffu, reach_local) != 0u;
-            const WarpCand mine = reach ? cr : cs;
-            // Warp arg-max of (heuristic, leap, -lane) in three integer max-reductions (REDUX) instead of five
-            // rounds of 7-register shuffles: the double is mapped to an unsigned key of the same order (sign bit
-            // flipped, negative values complemented; -0 folded into +0 first), its high and low words are reduced
-            // one after the other, then (leap, -lane) among the lanes that tie.  leap = -(switch costs) lies in
-            // (-2^22, 0] for penalties <= 1000, 63 - lane in [13, 113].
-            unsigned long long hk = 0ull;
-            if (mine.valid) {
-                const long long bits = __double_as_longlong(dadd(mine.h, 0.0));
-                hk = (unsigned long long)bits ^ ((unsigned long long)(bits >> 63) | 0x8000000000000000ull);
+            if (__ballot_sync(0xffffffffu, reach_local) != 0u) {
+                // a highway reaches its destination: the candidates are ranked by the destination heuristic instead
+                // (:327-347; rare -- normally the last step of an alignment)
+                hk = 0ull;
+                k2 = 0u;
+#pragma unroll
+                for (int i = 0; i < ITER; ++i) {
+                    if (lane + 32 * i < nl) {
+                        const int l = l0 + 32 * i, de = lane_destination(m, nn, l);
+                        const int fsw = GLOBAL ? slp(l, dl, o, e) : 0;
+                        const int hv = -sw_[i] - x * st_nh(stv[i]) - fsw - x * (de - st_sp(stv[i]) - st_len(stv[i]));
+                        const unsigned long long hki = order_key((double)hv);
+                        const uint32_t k2i = ((uint32_t)((1 << 22) - sw_[i] - fsw) << 8) | (uint32_t)(63 - l);
+                        if (hki > hk || (hki == hk && k2i > k2)) { hk = hki; k2 = k2i; }
+                    }
+                }
             }
+            // warp arg-max in three integer max-reductions (REDUX): high word, low word, then (leap, -lane) among the ties
             const uint32_t hk_hi = (uint32_t)(hk >> 32), hk_lo = (uint32_t)hk;
             const uint32_t m_hi = __reduce_max_sync(0xffffffffu, hk_hi);
             const uint32_t m_lo = __reduce_max_sync(0xffffffffu, hk_hi == m_hi ? hk_lo : 0u);
-            const bool tie = mine.valid && hk_hi == m_hi && hk_lo == m_lo;
-            const uint32_t k2 = tie ? (((uint32_t)(mine.leap + (1 << 22)) << 8) | (uint32_t)(63 - mine.l)) : 0u;
-            const uint32_t m2 = __reduce_max_sync(0xffffffffu, k2);
-            __syncwarp();   // every lane's refreshed state is visible before it is read back / _choose_best_highway reads it
-            WarpCand best;
-            best.l = 63 - (int)(m2 & 0xFFu);
-            best.st = s_state[best.l - lb];
-            const int bl = best.l;
-            if (st_len(best.st) <= 0) break;   // no usable highway (:358-360)
+            const uint32_t m2 = __reduce_max_sync(0xffffffffu, (hk != 0ull && hk_hi == m_hi && hk_lo == m_lo) ? k2 : 0u);
+            const int bl = 63 - (int)(m2 & 0xFFu);
+            __syncwarp();   // every lane's refreshed cache is visible
+            const uint64_t st_best = s_state[bl - lb];
+            if (st_len(st_best) <= 0) break;   // no usable highway (:358-360)
 
-            // _choose_best_highway (:368-401)
-            const int spb = st_sp(best.st);
-            int sT = x * st_nh(best.st) + (leap_cost ? slp(cl, bl, o, e) : 0), sI = sT, b = bl;
-            uint64_t st_b = best.st;
-            const uint32_t* ob = s_lanes + (size_t)(bl - lb) * PITCH;
-            for (int base = 0; base < nl; base += 32) {
-                const int li = base + lane, l = li + lb;
-                bool ok = li < nl && l != bl;
-                int tc = 0, ic = 0;
-                uint64_t stv = 0;
-                if (ok) {
-                    stv = s_state[li];
-                    const int sp = st_sp(stv), s_l = sfc(l, bl);
-                    ok = sp + s_l <= spb;
+            // _choose_best_highway (:368-401): lanes are visited in ascending order and taken if not worse on both
+            // counts; both bounds only ever go down, so a lane that fails them before its hurdle count is known is out
+            const int spb = st_sp(st_best);
+            int sT = x * st_nh(st_best) + (leap_cost ? slp(cl, bl, o, e) : 0), sI = sT, b = bl;
+            const uint32_t* ob = s_lanes + (size_t)(bl - lb) * PITCH + L::PAD_LO;
+#pragma unroll
+            for (int i = 0; i < ITER; ++i) {
+                if (32 * i < nl) {
+                    const int l = l0 + 32 * i;
+                    bool ok = lane + 32 * i < nl && l != bl;
+                    int tc = 0, ic = 0;
                     if (ok) {
-                        const int end = sp + st_len(stv);
-                        ic = (leap_cost ? slp(cl, l, o, e) : 0) + st_nh(stv);
-                        tc = ic + slp(l, bl, o, e) + imax(0, x * pcb<W>(ob, 1, s_l + end, spb));
+                        const int sp = st_sp(stv[i]), s_l = sfc(l, bl);
+                        ic = sw_[i] + st_nh(stv[i]);
+                        const int lo = ic + slp(l, bl, o, e);
+                        ok = sp + s_l <= spb && ic <= sI && lo <= sT;
+                        if (ok) tc = lo + imax(0, x * pcb<W>(ob, 1, s_l + sp + st_len(stv[i]), spb));
+                    }
+                    int after = -1;
+                    for (;;) {
+                        const uint32_t take = __ballot_sync(0xffffffffu, ok && lane > after && tc <= sT && ic <= sI);
+                        if (!take) break;
+                        after = __ffs((int)take) - 1;
+                        sT = __shfl_sync(0xffffffffu, tc, after);
+                        sI = __shfl_sync(0xffffffffu, ic, after);
+                        b = 32 * i + after + lb;
                     }
                 }
-                int after = -1;
-                for (;;) {
-                    const uint32_t take = __ballot_sync(0xffffffffu, ok && lane > after && tc <= sT && ic <= sI);
-                    if (!take) break;
-                    after = __ffs((int)take) - 1;
-                    sT = __shfl_sync(0xffffffffu, tc, after);
-                    sI = __shfl_sync(0xffffffffu, ic, after);
-                    b = base + after + lb;
-                }
             }
-            if (b != bl) st_b = s_state[b - lb];   // the taken lane's highway (its state was refreshed above)
+            const uint64_t st_b = b != bl ? s_state[b - lb] : st_best;   // the taken lane's highway
+            __syncwarp();   // read by everyone before the next step's owners overwrite it
             // _step (:412-433)
             pen += (leap_cost ? slp(cl, b, o, e) : 0) + x * st_nh(st_b);
             const int endb = st_sp(st_b) + st_len(st_b);
@@ -253,7 +278,7 @@ greedy_warp_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t*
             const int dc = in_band ? lane_destination(m, nn, dl) : -iabs(dl);
             if (cl != dl || cc < dc) {
                 int d = 0;
-                if (in_band) d = pcb<W>(s_lanes + (size_t)(dl - lb) * PITCH, 1, cc + sfc(cl, dl), dc);
+                if (in_band) d = pcb<W>(s_lanes + (size_t)(dl - lb) * PITCH + L::PAD_LO, 1, cc + sfc(cl, dl), dc);
                 pen += (GLOBAL ? slp(cl, dl, o, e) : 0) + imax(0, x * d);
                 update_cigar(dl, cl, d);
             }
