@@ -37,6 +37,20 @@ def stale():
     return any(os.path.getmtime(p) > t for p in SOURCES + HEADERS + [os.path.abspath(__file__)])
 
 
+def source_sha():
+    """SHA-1 (16 hex digits) over the CUDA sources, the public header and the compiler flags: identifies WHAT was built.
+    nvcc does not produce the same bytes twice, so the library file's own hash changes with every rebuild; profiles
+    taken from one build (profiles/traffic.json) are matched to a later build of the same sources by this hash."""
+    import hashlib
+    h = hashlib.sha1()
+    for path in sorted(SOURCES + HEADERS):
+        h.update(os.path.basename(path).encode() + b"\0")
+        with open(path, "rb") as f:
+            h.update(f.read())
+    h.update(" ".join(NVCC_FLAGS).encode())
+    return h.hexdigest()[:16]
+
+
 def build_library(force=False, verbose=False):
     """Compile the CUDA extension if sources are newer than the .so.  Returns the library path."""
     if not force and not stale():

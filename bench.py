@@ -85,16 +85,32 @@ def lib_sha(pkg):
     return h.hexdigest()[:16]
 
 
+def source_sha(pkg):
+    sys.path.insert(0, os.path.dirname(pkg.LIB_PATH))
+    try:
+        import build as gasma_build
+        return gasma_build.source_sha()
+    finally:
+        sys.path.pop(0)
+
+
 def ncu_figures(pkg, leg):
     """Per-launch DRAM bytes / executed instructions of the leg's dominant kernel from profiles/traffic.json -- only if
-    they were taken from the very library that is loaded (SHA-1 match); otherwise None.  Written by
+    they were taken from a build of the very sources the loaded library was built from (source-hash match); otherwise None.  Written by
     tools/update_traffic.py from a metrics-only ncu pass of this bench command (tools/profile_round.sh)."""
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
             t = json.load(f)
-        if t.get("library_sha1") != lib_sha(pkg):
+        # the same code = the same source hash (nvcc output is not byte-reproducible: the .so's own SHA-1 changes with
+        # every rebuild, so it only matches on the very file the capture ran on)
+        if t.get("source_sha1") != source_sha(pkg) and t.get("library_sha1") != lib_sha(pkg):
             return None
-        return t["legs"].get(leg)
+        fig = dict(t["legs"].get(leg) or {})
+        if not fig:
+            return None
+        fig["source_sha"] = t.get("source_sha1")
+        fig["library_sha1_at_capture"] = t.get("library_sha1")
+        return fig
     except Exception:
         return None
 
@@ -102,16 +118,18 @@ def ncu_figures(pkg, leg):
 def attach_ncu(roof, fig, k_ms, sm_count, sm_mhz):
     """roofline.traffic + the issue-slot view of the same launch (instructions from ncu, time from the live run)."""
     if not fig:
-        roof["traffic_note"] = "no ncu figures for this library build in profiles/traffic.json (SHA-1 mismatch): traffic left null"
+        roof["traffic_note"] = "no ncu figures for these sources in profiles/traffic.json (source hash mismatch): traffic left null"
         return
     roof["traffic"] = fig["traffic_bytes"]
     roof["ncu"] = {k: fig[k] for k in ("kernel", "issue_active_pct", "alu_pipe_pct", "avg_active_threads", "warp_instructions",
-                                       "dram_read_bytes", "dram_write_bytes", "source")}
+                                       "dram_read_bytes", "dram_write_bytes", "source", "source_sha", "library_sha1_at_capture")}
     if sm_mhz:
         peak = sm_count * 4 * sm_mhz * 1e6          # 4 schedulers per SM, one warp instruction per clock each
         ach = fig["warp_instructions"] / (k_ms * 1e-3)
         roof["issue"] = {"bound": "issue slots (4 schedulers/SM)", "achieved": ach / 1e9, "peak": peak / 1e9, "unit": "G warp-instr/s",
-                         "frac": ach / peak, "note": "utilisation of the instructions the kernel executes, not a fraction of an algorithmic minimum"}
+                         "frac": ach / peak, "source_sha": fig.get("source_sha"), "library_sha1_at_capture": fig.get("library_sha1_at_capture"),
+                         "note": "utilisation of the instructions the kernel executes, not a fraction of an algorithmic minimum; the "
+                                 "instruction count is ncu's for a build of the sources with this hash (= the loaded library's sources)"}
 
 
 def workload_name(a):

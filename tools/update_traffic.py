@@ -1,5 +1,7 @@
 #!/usr/bin/env python
-"""Per-kernel ncu figures of THIS library build -> profiles/traffic.json, keyed by the library's SHA-1.
+"""Per-kernel ncu figures of THIS library build -> profiles/traffic.json, keyed by the hash of the sources it was built
+from (build.source_sha(): nvcc's output is not byte-reproducible, so the .so's own SHA-1 -- recorded too -- changes with
+every rebuild of the same code).
 
     # on the GPU box (tools/profile_round.sh does this), after the plain bench run has exited 0:
     ncu --metrics $(python tools/update_traffic.py --metrics) --clock-control none -k regex:greedy_kernel -s 3 -c 4 \
@@ -7,8 +9,8 @@
     python tools/update_traffic.py gpurun_out/traffic_headline.csv headline
     (and the same with -k regex:nw_band_kernel, without --no-full-path, label full_path)
 
-bench.py prints roofline.traffic / roofline.issue only when the entry's SHA-1 equals the loaded library's, so the
-figures can never silently belong to another build.  One entry per (kernel template, grid size): the median launch."""
+bench.py prints roofline.traffic / roofline.issue only when the entry's source hash equals that of the tree the loaded
+library was built from, so the figures can never silently belong to other code.  One entry per (kernel template, grid size): the median launch."""
 import csv
 import hashlib
 import json
@@ -56,14 +58,17 @@ def main():
     lib = os.path.join(ROOT, "approximate-string-matching_b200", "libgasma_b200.so")
     label = sys.argv[2] if len(sys.argv) > 2 else "headline"
     sha = lib_sha(lib)
+    sys.path.insert(0, os.path.join(ROOT, "approximate-string-matching_b200"))
+    import build as gasma_build
+    src = gasma_build.source_sha()
     path = os.path.join(ROOT, "profiles", "traffic.json")
     try:
         with open(path) as f:
             entry = json.load(f)
     except Exception:
         entry = {}
-    if entry.get("library_sha1") != sha:      # figures of another build are dropped, never mixed
-        entry = {"library_sha1": sha, "legs": {}}
+    if entry.get("source_sha1") != src:       # figures of other sources are dropped, never mixed
+        entry = {"library_sha1": sha, "source_sha1": src, "legs": {}}
     key, ls = max(kernels.items(), key=lambda kv: len(kv[1]))     # the leg's dominant kernel = the one launched most
     med = lambda m: statistics.median(x[m] for x in ls if m in x)
     entry["legs"][label] = {
