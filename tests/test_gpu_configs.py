@@ -68,3 +68,21 @@ def test_config2_full_path_full_batch(pkg, ol):
     assert c[0] == c[1] == N and 0.44 * N < c[2] < 0.48 * N and 0.87 * N < c[3] < 0.895 * N
     assert 0.87 * N < int((leap == on["penalty"]).sum()) < 0.90 * N
     al.close()
+
+
+@pytest.mark.parametrize("k", [24, 50])
+def test_config4_long_reads_full_batch(pkg, ol, k):
+    """configs[4]: 1 kbp reads, error rate 0.15, k = 24 and k = 50 (MAX_K), one alignment per warp, at the batch size
+    bench.py times (100 k pairs): penalties and every CIGAR op against the checker."""
+    n = 100_000
+    al = pkg.Aligner(k=k, max_length=1024)
+    cfg = pkg.gen_config(SEED + (5 if k == 24 else 6), 1000, 0.15)     # the seeds and pair range of bench.py's legs
+    reads, roff, refs, foff = al.generate(cfg, 0, n)
+    out = al.greedy_batch(reads, roff, refs, foff, want_ops=True, ops_cap=n * 200)
+    b = ol.Batch(reads, roff, refs, foff)
+    ref = ol.oracle_greedy(b, ol.make_params(k, 1, 1, 1, 16, 1), threads=THREADS)
+    assert int((out["cost"] != ref["cost"]).sum()) == 0
+    assert np.array_equal(out["op_off"], ref["op_off"])
+    assert np.array_equal(out["ops"][:out["n_ops"]], ref["ops"])
+    assert 100 < float(out["cost"].mean()) < 130 and ref["steps"] / n > 15
+    al.close()
