@@ -43,7 +43,7 @@ def parse():
     ap.add_argument("--batches", type=int, default=4, help="distinct resident batches per GPU cycled through (kernel time "
                     "varies +-3.5 %% between batches of identical total work: a tail effect of the dynamic chunk queue)")
     ap.add_argument("--cpu-sample", type=int, default=0, help="pairs in the CPU baseline sample (0 = auto)")
-    ap.add_argument("--in-flight", type=int, default=3, help="batches in flight (contexts / streams) in the full-path leg; 1 = one at a time")
+    ap.add_argument("--in-flight", type=int, default=3, help="batches in flight (contexts / streams) in the in_flight passes of the headline and full-path legs; 1 = off")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-full-path", action="store_true", help="skip the greedy + NW verifier + counters leg")
     ap.add_argument("--no-configs", action="store_true", help="skip the short legs for the other BASELINE.json configs")
@@ -352,7 +352,7 @@ class Env:
 
 
 def greedy_leg(env, *, workload, length, error, profile, k, pairs, steps, warmup, seed, n_batches=2,
-               parity_pairs=None, cpu_seconds=0.0, want_parity=True):
+               parity_pairs=None, cpu_seconds=0.0, want_parity=True, in_flight=0):
     torch, pkg = env.torch, env.pkg
     ml = max_length_for(length, error if profile == "simulated" else 0.0)
     al = pkg.Aligner(k=k, max_length=ml, device=env.local)
@@ -410,6 +410,57 @@ def greedy_leg(env, *, workload, length, error, profile, k, pairs, steps, warmup
     # algorithmic bytes of one batch: m + n + 4 (cost) + 4 (CSR offset) + CIGAR bytes produced
     alg_bytes = rbytes + fbytes + 8 * n + 2 * ooff_last
     tot = env.sum_over_ranks([n, int(d_cost.sum(dtype=torch.int64).item()), ooff_last])
+    # ---- the same K steps with several batches in flight: one context (own scratch, own stream, own output buffers)
+    # per batch in flight, round-robin.  A greedy launch ends with a drain (a thread works on ~9 pairs per launch, the
+    # last one finishes alone) followed by the compaction kernel and the next launch's ramp-up; with the next batch
+    # already queued on another stream those gaps are filled.  `value` stays the one-batch-at-a-time number, which the
+    # kernel time and the roofline block belong to. ----
+    flight = None
+    if in_flight > 1:
+        streams = [env.stream] + [torch.cuda.Stream(device=dev) for _ in range(in_flight - 1)]
+        als = [al]
+        for s_ in streams[1:]:
+            x_ = pkg.Aligner(k=k, max_length=ml, device=env.local)
+            x_.set_stream(s_.cuda_stream)
+            als.append(x_)
+        outs = [(torch.empty_like(d_cost), torch.empty_like(d_ops), torch.empty_like(d_ooff)) for _ in als]
+
+        def fstep(i):
+            r, ro, f, fo = batches[i % len(batches)]
+            c_ = i % len(als)
+            als[c_].greedy_batch_dev(r, ro, f, fo, n, *outs[c_])
+
+        env.load(True)
+        for i in range(max(warmup, 2 * len(als))):
+            fstep(i)
+        torch.cuda.synchronize()
+        env.barrier()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record(env.stream)
+        for s_ in streams[1:]:
+            s_.wait_event(f0)
+        for i in range(steps):
+            fstep(i)
+        for s_ in streams[1:]:
+            e_ = torch.cuda.Event()
+            e_.record(s_)
+            env.stream.wait_event(e_)
+        f1.record(env.stream)
+        env.barrier()
+        f_ms = env.max_over_ranks(f0.elapsed_time(f1))
+        env.load(False)
+        for x_ in als:
+            x_.synchronize()
+        c_ = (steps - 1) % len(als)       # the last step ran the batch the sequential pass ended on: same outputs?
+        same = bool(torch.equal(outs[c_][0], d_cost) and torch.equal(outs[c_][2], d_ooff) and
+                    torch.equal(outs[c_][1][:ooff_last], d_ops[:ooff_last]))
+        flight = {"batches_in_flight": len(als), "value": env.world * n * steps / (f_ms * 1e-3), "unit": "alignments/s",
+                  "ms_per_step": f_ms / steps, "steps": steps, "outputs_equal_sequential": same,
+                  "note": "the same K steps handed round-robin to %d contexts, each on its own stream with its own scratch and "
+                          "output buffers (tools/two_stream_probe.py); kernel times overlap, so no roofline block belongs to it" % len(als)}
+        for x_ in als[1:]:
+            x_.close()
+        del outs
     peak, peak_src = measured_peak()
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9
     W = ml // 64
@@ -424,6 +475,8 @@ def greedy_leg(env, *, workload, length, error, profile, k, pairs, steps, warmup
                         "kernel": shape, "kernel_ms": k_ms, "kernel_share_of_step": k_ms / (ms_total / steps),
                         "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src},
            "counters": {"pairs": tot[0], "penalty_sum": tot[1], "cigar_ops": tot[2]}}
+    if flight is not None:
+        res["in_flight"] = flight
     state = {"al": al, "batches": batches, "last": last, "d_cost": d_cost, "d_ops": d_ops, "d_ooff": d_ooff, "ml": ml,
              "ops_per_pair": ops_per_pair, "n": n, "k": k, "alg_bytes": alg_bytes, "k_ms": k_ms}
     if env.rank == 0 and want_parity:
@@ -432,6 +485,9 @@ def greedy_leg(env, *, workload, length, error, profile, k, pairs, steps, warmup
         got = {"cost": d_cost[:np_n].cpu().numpy(), "op_off": d_ooff[:np_n + 1].cpu().numpy().view(np.uint32)}
         got["ops"] = d_ops[:int(got["op_off"][np_n])].cpu().numpy().view(np.uint16)
         res["parity"] = parity_greedy(hb, k, W, got, "device-resident output of the last timed step, pairs [0, %d) of the batch" % np_n)
+        if flight is not None:
+            res["parity"]["in_flight_outputs_equal_sequential"] = flight["outputs_equal_sequential"]
+            res["parity"]["ok"] = bool(res["parity"]["ok"] and flight["outputs_equal_sequential"])
     if env.rank == 0 and env.world == 1 and cpu_seconds > 0:
         res["cpu_baseline"] = cpu_greedy_baseline(device_batch_to_numpy(last, min(n, 400_000)), k, ml, target_seconds=cpu_seconds)
     return res, state
@@ -753,7 +809,7 @@ def run_b200(a):
     # ---- headline: BASELINE.json configs[1] (or whatever the flags name) ----
     head, st = greedy_leg(env, workload=workload_name(a), length=a.length, error=a.error, profile=a.profile, k=a.k, pairs=a.pairs,
                           steps=a.steps, warmup=a.warmup, seed=SEED + 1, n_batches=a.batches, parity_pairs=None,
-                          cpu_seconds=10.0 if want_cpu else 0.0, want_parity=not a.no_parity)
+                          cpu_seconds=10.0 if want_cpu else 0.0, want_parity=not a.no_parity, in_flight=a.in_flight)
     e2e, e2e_parity = e2e_leg(env, st, a.steps, a.warmup, want_parity=not a.no_parity)
     e2e["host_numa"] = {"node": numa[0], "cpus": numa[1]} if numa else None
     e2e_packed = e2e.pop("packed", None)
@@ -803,6 +859,9 @@ def run_b200(a):
         "config": config_dict(a, ml), "cache": head["cache"], "e2e": e2e, "gpu_launches": head["gpu_launches"], "clocks": clocks,
         "roofline": roof, "counters": head["counters"], "library_sha1": lib_sha(pkg),
     }
+    if "in_flight" in head:
+        line["in_flight"] = head["in_flight"]
+    line["source_sha"] = source_sha(pkg)
     if e2e_packed is not None:
         line["e2e_packed"] = e2e_packed
     if not a.no_parity:

@@ -62,5 +62,44 @@ def main():
             a.close()
 
 
+def greedy_only():
+    """The same question for the greedy-only step (headline workload: 150 bp, e = 0.10, CIGAR CSR out)."""
+    n = 1_000_000
+    dev = torch.device("cuda:0")
+    L, e, nb, rounds = 150, 0.10, 4, 6
+    gen = pkg.Aligner(k=3, max_length=192)
+    cfg = pkg.gen_config(0x47415341 + 1, L, e)
+    batches = []
+    for b in range(nb):
+        d_reads = torch.empty(n * L + 16, dtype=torch.uint8, device=dev)
+        d_refs = torch.empty(gen.generate_ref_capacity(cfg, n), dtype=torch.uint8, device=dev)
+        d_roff = torch.empty(n + 1, dtype=torch.int32, device=dev)
+        d_foff = torch.empty(n + 1, dtype=torch.int32, device=dev)
+        gen.generate_dev(cfg, b * n, n, d_reads, d_roff, d_refs, d_foff)
+        batches.append((d_reads, d_roff, d_refs, d_foff))
+    gen.synchronize()
+    for w in (1, 2, 3):
+        als = [pkg.Aligner(k=3, max_length=192) for _ in range(w)]
+        outs = [(torch.empty(n, dtype=torch.int32, device=dev), torch.empty(n * 104, dtype=torch.int16, device=dev),
+                 torch.empty(n + 1, dtype=torch.int32, device=dev)) for _ in range(w)]
+        for i in range(2 * w):
+            als[i % w].greedy_batch_dev(*batches[i % nb], n, *outs[i % w])
+        for a in als:
+            a.synchronize()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for i in range(nb * rounds):
+            als[i % w].greedy_batch_dev(*batches[i % nb], n, *outs[i % w])
+        for a in als:
+            a.synchronize()
+        dt = time.perf_counter() - t0
+        print("greedy only, %d context(s): %.4f ms per batch, %.1f M alignments/s" % (w, 1e3 * dt / (nb * rounds), nb * rounds * n / dt / 1e6))
+        for a in als:
+            a.close()
+
+
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == "greedy":
+        greedy_only()
+    else:
+        main()
