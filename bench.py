@@ -86,12 +86,13 @@ def lib_sha(pkg):
 
 
 def source_sha(pkg):
-    sys.path.insert(0, os.path.dirname(pkg.LIB_PATH))
-    try:
-        import build as gasma_build
-        return gasma_build.source_sha()
-    finally:
-        sys.path.pop(0)
+    """Hash of the sources in this tree (approximate-string-matching_b200/build.py:source_sha)."""
+    import importlib.util
+    path = os.path.join(os.path.dirname(os.path.abspath(pkg.__file__)), "build.py")
+    spec = importlib.util.spec_from_file_location("gasma_b200_build", path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod.source_sha()
 
 
 def ncu_figures(pkg, leg):
@@ -103,7 +104,9 @@ def ncu_figures(pkg, leg):
             t = json.load(f)
         # the same code = the same source hash (nvcc output is not byte-reproducible: the .so's own SHA-1 changes with
         # every rebuild, so it only matches on the very file the capture ran on)
-        if t.get("source_sha1") != source_sha(pkg) and t.get("library_sha1") != lib_sha(pkg):
+        in_tree = os.path.dirname(os.path.abspath(pkg.LIB_PATH)) == os.path.dirname(os.path.abspath(pkg.__file__))
+        # (a library from elsewhere -- GASMA_B200_LIB, the A/B variants -- was not built from this tree's sources)
+        if not (in_tree and t.get("source_sha1") == source_sha(pkg)) and t.get("library_sha1") != lib_sha(pkg):
             return None
         fig = dict(t["legs"].get(leg) or {})
         if not fig:

@@ -1,4 +1,4 @@
-for rep in 1 2; do
+for rep in ${REPS:-1 2}; do
 for lib in "$@"; do
   GASMA_B200_LIB=$PWD/$lib python bench.py --steps 20 --warmup 3 --no-cpu-baseline --no-parity 2>/dev/null | python -c "
 import sys,json

@@ -58,8 +58,10 @@ def main():
     lib = os.path.join(ROOT, "approximate-string-matching_b200", "libgasma_b200.so")
     label = sys.argv[2] if len(sys.argv) > 2 else "headline"
     sha = lib_sha(lib)
-    sys.path.insert(0, os.path.join(ROOT, "approximate-string-matching_b200"))
-    import build as gasma_build
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("gasma_b200_build", os.path.join(ROOT, "approximate-string-matching_b200", "build.py"))
+    gasma_build = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(gasma_build)
     src = gasma_build.source_sha()
     path = os.path.join(ROOT, "profiles", "traffic.json")
     try:
