@@ -1017,3 +1017,6 @@ int gasma_generate_dev(gasma_ctx* ctx, const gasma_gen_config* cfg, uint64_t fir
 #include "noalloc_entry.inl"
 #include "nccl_entry.inl"
 #include "async_entry.inl"
+#if GASMA_TIMELINE
+extern "C" int gasma_debug_timeline(unsigned long long* out) { return (int)cudaMemcpyFromSymbol(out, gasma::g_tl, sizeof(unsigned long long) * 4 * 8192); }
+#endif

@@ -48,12 +48,6 @@ __device__ __forceinline__ void scan_highway_padded(const uint32_t* row, int sc,
     else len = (sc + 64 >= BITS || sc + 64 > de) ? BITS : scan_highway_tail<W, 0>(row, 1, sc + 64, de, sp);
 }
 
-// order-preserving unsigned key of a double (sign bit flipped, negative values complemented; -0 folded into +0)
-__device__ __forceinline__ unsigned long long order_key(double h) {
-    const long long bits = __double_as_longlong(dadd(h, 0.0));
-    return (unsigned long long)bits ^ ((unsigned long long)(bits >> 63) | 0x8000000000000000ull);
-}
-
 // 32 bits of a uint16-chunk stream starting at bit `bit`, for plane word w of a string of `len` characters
 __device__ __forceinline__ uint32_t stream_word(const uint32_t* stream32, int bit, int len, int w) {
     const int pos = bit + 32 * w, idx = pos >> 5, sh = pos & 31;

@@ -2,9 +2,16 @@
 // scan/compaction kernels that turn per-pair CIGAR staging rows into one CSR array.
 // Built only for sm_100a (see build.py); no other architecture, no CPU path.
 #pragma once
+#ifndef GASMA_TIMELINE
+#define GASMA_TIMELINE 0   // 1: diagnostic build with per-warp time stamps (tools/timeline_probe.py)
+#endif
+#ifndef GASMA_COOP_TAIL
+#define GASMA_COOP_TAIL 4   // open pairs per warp at which the end game takes over (0 = off)
+#endif
 #include "common.cuh"
 #include "pack.cuh"
 #include "greedy.cuh"
+#include "greedy_coop.cuh"
 
 namespace gasma {
 
@@ -117,9 +124,14 @@ __host__ __device__ constexpr size_t greedy_smem_bytes(int warps, int nl) {   //
            + 64;
 }
 
+#if GASMA_TIMELINE
+// diagnostic build only (tools/timeline_probe.py): per warp -- start, queue seen dry, last hand-out, exit (globaltimer ns)
+__device__ unsigned long long g_tl[4][8192];
+__device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+#endif
 // FLIP: the aligner's mask variant (greedy.cuh:flip_word), 0 = the reference as shipped
 template <int W, int WARPS, bool CORR, int FLIP = 0>
-__global__ void __launch_bounds__(32 * WARPS, CORR ? 1 : (WARPS == 8 ? 3 : (WARPS == 4 ? 5 : (WARPS == 2 ? 11 : 1))))
+__global__ void __launch_bounds__(32 * WARPS, CORR ? 1 : (WARPS == 8 ? 3 : (WARPS == 4 ? (W <= 2 ? 6 : 5) : (WARPS == 2 ? 11 : 1))))
 greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __restrict__ read_off,
               const uint8_t* __restrict__ refs, const uint32_t* __restrict__ ref_off, long long n,
               int32_t* __restrict__ cost, uint16_t* __restrict__ ops_rows, uint16_t* __restrict__ ops_ovf, int ops_stride,
@@ -149,6 +161,10 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
     for (int i = lane; i < SE; i += 32) { s_r0[i] = 0; s_r1[i] = 0; s_f0[i] = 0; s_f1[i] = 0; }
     __syncwarp();
 
+#if GASMA_TIMELINE
+    const int wid = (blockIdx.x * WARPS + warp) & 8191;
+    if (lane == 0) { g_tl[0][wid] = gtime(); g_tl[1][wid] = 0; g_tl[2][wid] = 0; }
+#endif
     const LaneStore<W> S{s_lanes + tid, s_state + tid, T};
     const uint32_t nchunks = (uint32_t)((n + kPool - 1) / kPool);
     const uint32_t rtotal = read_off[n], ftotal = ref_off[n];
@@ -178,7 +194,13 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
             pf = kClaimed;
         } else if (pf == kClaimed) {
             nx_chunk = __shfl_sync(0xffffffffu, nx_chunk, 0);
-            if (nx_chunk >= nchunks) { pf = kDone; return; }
+            if (nx_chunk >= nchunks) {
+                pf = kDone;
+#if GASMA_TIMELINE
+                if (lane == 0) g_tl[1][wid] = gtime();
+#endif
+                return;
+            }
             const long long p0n = (long long)nx_chunk * kPool;
             nx_count = (int)((n - p0n) < (long long)kPool ? (n - p0n) : (long long)kPool);
             const int i = lane < nx_count ? lane : nx_count;
@@ -286,6 +308,9 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
                     active = true;
                 }
             }
+#if GASMA_TIMELINE
+            if (lane == 0 && pool_next < pool_count) g_tl[2][wid] = gtime();
+#endif
             pool_next = imin(pool_count, pool_next + n_idle);
             __syncwarp();
         }
@@ -317,7 +342,40 @@ greedy_kernel(KParams P, const uint8_t* __restrict__ reads, const uint32_t* __re
             const uint32_t sum = __reduce_add_sync(peers, fin_n);
             if ((peers & ((1u << lane) - 1u)) == 0u) atomicAdd(tile_sums + fin_tile, sum);
         }
+#if GASMA_COOP_TAIL
+        // nothing left to hand out and only a few pairs still open in this warp: the end game below finishes them
+        if (pf == kDone && pool_next == pool_count && __popc(__ballot_sync(0xffffffffu, active)) <= GASMA_COOP_TAIL) break;
+#endif
     }
+#if GASMA_COOP_TAIL
+    // ---- end game (greedy_coop.cuh): the warp finishes its open pairs one after the other, its threads spread over
+    // the pair's lanes; a pair with more than 32 lanes is finished by its owner alone ----
+    for (uint32_t todo = __ballot_sync(0xffffffffu, active); todo != 0u; todo &= todo - 1u) {
+        const int owner = __ffs((int)todo) - 1;
+        const bool fits = CORR ? __shfl_sync(0xffffffffu, ps.ub - ps.lb, owner) < 32 : 2 * P.k + 1 <= 32;
+        if (fits) {
+            const LaneStore<W> So{s_lanes + (tid - lane + owner), s_state + (tid - lane + owner), T};
+            while (!pair_step_coop<W, CORR, FLIP>(P, So, owner, lane, ps, sink, st)) {}
+            __syncwarp();
+        }
+        if (lane == owner) {
+            if (!fits)
+                while (!pair_step<W, CORR, FLIP>(P, S, ps, sink, st)) {}
+            pair_finish<W, CORR>(P, S, ps, sink);
+            sink.finish();
+            cost[my_p] = ps.cost;
+            if (nops_out) nops_out[my_p] = (uint32_t)sink.n;
+            if (tile_sums && sink.n) atomicAdd(tile_sums + (uint32_t)(my_p >> kCsrTileShift), (uint32_t)sink.n);
+            if (sink.n > ops_stride) st |= kStatusSteps;
+            steps_done += (uint32_t)ps.steps;
+            active = false;
+        }
+        __syncwarp();
+    }
+#endif
+#if GASMA_TIMELINE
+    if (lane == 0) g_tl[3][wid] = gtime();
+#endif
     // one atomic per warp, and only when there is something to report
     const uint32_t wst = __reduce_or_sync(0xffffffffu, st);
     if (wst && lane == 0) atomicOr(status, wst);
