@@ -419,3 +419,23 @@ def test_gpu_async_submit_wait_pair(pkg, ol):
     # destroying a context with a call in flight waits for it
     t = al.greedy_submit(batches[0].reads, batches[0].read_off, batches[0].refs, batches[0].ref_off)
     al.close()
+
+
+@pytest.mark.parametrize("W", [1, 3])
+def test_gpu_end_game_boundaries(pkg, ol, W):
+    """The greedy kernel's end game (greedy_coop.cuh) finishes a warp's last open pairs with one thread per lane when the
+    pair has at most 32 lanes, and leaves them to their owner otherwise: band widths on both sides of that limit
+    (k = 0, 15, 16), batches of 1 ... a few pools (where nearly every pair ends in the end game), GLOBAL and SEMI_GLOBAL,
+    many-step pairs (high error rates), against the checker op for op."""
+    rng = np.random.default_rng(4400 + W)
+    for k in (0, 1, 15, 16):
+        for g in (1, 0):
+            al = pkg.Aligner(k=k, x=1, o=2, e=1, max_length=64 * W, alignment_type=1 - g)
+            for n in (1, 2, 33, 130, 1500):
+                b = ol.random_batch(rng, n, 1, 64 * W, 0.45, 0.4, 50)
+                out, _ = _run(pkg, al, b)
+                r = ol.oracle_greedy(b, ol.make_params(k, 1, 2, 1, W, g), threads=4)
+                assert out["cost"].tolist() == r["cost"].tolist(), (k, g, n)
+                assert out["op_off"].tolist() == r["op_off"].tolist(), (k, g, n)
+                assert out["ops"][:out["n_ops"]].tolist() == r["ops"].tolist(), (k, g, n)
+            al.close()
