@@ -2,7 +2,7 @@
 """Where the time of ONE greedy launch goes: per-warp timeline (start, queue seen dry, last hand-out, exit).
 
     tools/build_variant.sh timeline -DGASMA_TIMELINE=1
-    GASMA_B200_LIB=$PWD/_build/ab/timeline.so python tools/timeline_probe.py [pairs]
+    GASMA_B200_LIB=$PWD/_build/ab/timeline.so python tools/timeline_probe.py [pairs [length error max_length]]
 
 The instrumented build (kernels.cuh, GASMA_TIMELINE: four globaltimer stamps per warp in a __device__ array, read back
 through gasma_debug_timeline) is for this probe only; the shipped library is built without it."""
@@ -12,12 +12,15 @@ ROOT = "/root/repo" if os.path.exists("/root/repo/bench.py") else os.getcwd()
 spec = importlib.util.spec_from_file_location("gasma_b200", os.path.join(ROOT, "approximate-string-matching_b200", "__init__.py"))
 pkg = importlib.util.module_from_spec(spec); sys.modules["gasma_b200"] = pkg; spec.loader.exec_module(pkg)
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 1_000_000
+LEN = int(sys.argv[2]) if len(sys.argv) > 2 else 150
+ERR = float(sys.argv[3]) if len(sys.argv) > 3 else 0.10
+ML = int(sys.argv[4]) if len(sys.argv) > 4 else 192
 dev = torch.device("cuda:0")
-al = pkg.Aligner(k=3, max_length=192)
-cfg = pkg.gen_config(0x47415341 + 1, 150, 0.10)
+al = pkg.Aligner(k=3, max_length=ML)
+cfg = pkg.gen_config(0x47415341 + 1, LEN, ERR)
 bs = []
 for b in range(2):
-    d_reads = torch.empty(n * 150 + 16, dtype=torch.uint8, device=dev)
+    d_reads = torch.empty(n * LEN + 16, dtype=torch.uint8, device=dev)
     d_refs = torch.empty(al.generate_ref_capacity(cfg, n), dtype=torch.uint8, device=dev)
     d_roff = torch.empty(n + 1, dtype=torch.int32, device=dev); d_foff = torch.empty(n + 1, dtype=torch.int32, device=dev)
     al.generate_dev(cfg, b * n, n, d_reads, d_roff, d_refs, d_foff); bs.append((d_reads, d_roff, d_refs, d_foff))
